@@ -1,0 +1,203 @@
+/* sxmc_b200.h -- C ABI of libsxmc_b200.so: the B200 (sm_100a) device layer that replaces
+ * hemi underneath sxmc's per-step likelihood hot path.
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to the
+ * mastbaum/sxmc tree).  Plain pointers and sizes only; no C++ or torch types.  All
+ * functions return 0 on success and a non-zero SXMC_E* code on failure;
+ * sxmc_last_error() returns the message (argument-validation messages are the
+ * reference's own pdfz::Error strings, so the C++ shim can rethrow them verbatim).
+ *
+ * There is no CPU fallback: every compute entry point fails with SXMC_ECUDA when no
+ * CUDA device is usable.
+ */
+#ifndef SXMC_B200_H
+#define SXMC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SXMC_OK 0
+#define SXMC_EINVAL 1  /* argument validation failed (a pdfz::Error in the reference) */
+#define SXMC_ECUDA 2   /* CUDA runtime / driver failure, or no device */
+#define SXMC_ESTATE 3  /* call sequence error (e.g. eval before buffers are bound) */
+#define SXMC_ENCCL 4   /* NCCL failure */
+
+/* numeric values of pdfz::Systematic::Type (src/pdfz.h:111-116) */
+#define SXMC_SYST_SHIFT 0
+#define SXMC_SYST_SCALE 1
+#define SXMC_SYST_RESOLUTION_SCALE 2
+#define SXMC_SYST_CTSCALE 3
+
+#define SXMC_MAX_NFIELDS 10   /* pdfz::MAX_NFIELDS, src/pdfz.cpp:17 */
+#define SXMC_MAX_SYST 8       /* systematics per PDF */
+#define SXMC_MAX_NPARS 4      /* coefficients per systematic */
+#define SXMC_MAX_PARAMETERS 256
+
+typedef struct sxmc_hist sxmc_hist;     /* one pdfz::EvalHist (src/pdfz.h:402-574) */
+typedef struct sxmc_chain sxmc_chain;   /* one MCMC object + its chain state (src/mcmc.h:36-138) */
+typedef struct sxmc_comm sxmc_comm;     /* NCCL communicator for sample-sharded fits */
+
+/* ---- library ---------------------------------------------------------------------- */
+const char* sxmc_last_error(void);
+const char* sxmc_version(void);
+/* cudaSetDevice + capability check (compute capability 10.x required). */
+int sxmc_init(int device);
+int sxmc_device_synchronize(void);
+
+/* ---- device buffers: the device half of hemi::Array<T>
+ *      (contrib/hemi/hemi/array.h:21-267; allocate :211-226, copies :137-149, :228-260) --- */
+int sxmc_buf_alloc(size_t bytes, void** dev_out);
+int sxmc_buf_free(void* dev);
+int sxmc_buf_upload(void* dev, const void* host, size_t bytes);     /* copyHostToDevice */
+int sxmc_buf_download(void* host, const void* dev, size_t bytes);   /* copyDeviceToHost */
+int sxmc_buf_zero(void* dev, size_t bytes);
+/* pinned host staging (hemi::Array(n, usePinned=true), array.h:25-37) */
+int sxmc_host_alloc(size_t bytes, void** host_out);
+int sxmc_host_free(void* host);
+
+/* ---- pdfz::EvalHist ---------------------------------------------------------------- */
+/* pdfz::Eval::Eval + EvalHist::EvalHist (src/pdfz.cpp:57-97, :179-236).  `samples` is the
+ * reference's host AoS array (nfloats = nsamples*nfields floats, row-major); it is copied
+ * to the device and owned by the handle.  The n* arguments carry the vector sizes the
+ * reference validates.  Errors (SXMC_EINVAL) carry the reference's messages. */
+int sxmc_hist_create(const float* samples, size_t nfloats, int nfields, int nobservables,
+                     const double* lower, int nlower, const double* upper, int nupper,
+                     const int* nbins, int nnbins, unsigned dataset, sxmc_hist** out);
+/* EvalHist::~EvalHist (src/pdfz.cpp:239-242) */
+int sxmc_hist_destroy(sxmc_hist* h);
+/* Eval::AddSystematic (src/pdfz.cpp:126-174).  `pars` are GLOBAL coefficient indices into
+ * the bound parameter buffer (src/config.cpp:118-120), copied at call time. */
+int sxmc_hist_add_systematic(sxmc_hist* h, int type, int obs, int extra_field, int npars,
+                             const short* pars);
+/* EvalHist::SetEvalPoints (src/pdfz.cpp:245-302): host rows of nobservables+1 floats. */
+int sxmc_hist_set_eval_points(sxmc_hist* h, const float* points, size_t nfloats);
+/* Eval::SetPDFValueBuffer / SetNormalizationBuffer / SetParameterBuffer
+ * (src/pdfz.cpp:105-124): borrowed DEVICE pointers, re-pointable at any time. */
+int sxmc_hist_set_pdf_buffer(sxmc_hist* h, float* dev, long offset, long stride);
+int sxmc_hist_set_norm_buffer(sxmc_hist* h, unsigned* dev, long offset);
+int sxmc_hist_set_param_buffer(sxmc_hist* h, const double* dev, long offset, long stride);
+/* EvalHist::EvalAsync (src/pdfz.cpp:441-488): zero + transform + bin (+ eval_pdf) enqueued
+ * on the handle's stream;  EvalHist::EvalFinished (:491-495): stream synchronise. */
+int sxmc_hist_eval_async(sxmc_hist* h, int do_eval_pdf);
+int sxmc_hist_eval_finished(sxmc_hist* h);
+/* The `for all pdfs: EvalAsync(); for all pdfs: EvalFinished()` idiom of
+ * src/mcmc.cpp:264-271 as ONE batched launch over all handles (first handle's stream). */
+int sxmc_hists_eval_async(sxmc_hist* const* hs, int n, int do_eval_pdf);
+/* Host-buffer convenience used for end-to-end timing: uploads `params` (nparams doubles),
+ * evaluates all handles in one batched launch with their norm slots in one device array and
+ * their pdf values signal-major (src/mcmc.cpp:236-237 layout), copies both back.
+ * pdf_out may be NULL (=> EvalAsync(false)). */
+int sxmc_hists_eval_host(sxmc_hist* const* hs, int n, const double* params, int nparams,
+                         long param_offset, unsigned* norms_out, float* pdf_out);
+/* introspection (the reference's protected members, src/pdfz.h:558-573) */
+int sxmc_hist_total_nbins(const sxmc_hist* h);
+double sxmc_hist_bin_volume(const sxmc_hist* h);
+size_t sxmc_hist_nsamples(const sxmc_hist* h);
+size_t sxmc_hist_neval_points(const sxmc_hist* h);
+int sxmc_hist_get_bins(sxmc_hist* h, unsigned* host_out);          /* bins->hostPtr() */
+int sxmc_hist_get_read_bins(sxmc_hist* h, int* host_out);          /* read_bins->hostPtr() */
+/* EvalHist::GetSamples (src/pdfz.h:542-556): original order, original AoS layout. */
+int sxmc_hist_get_samples(sxmc_hist* h, float* host_out);
+/* layout control: samples are stored as bin-sorted, lane-interleaved SoA columns, built
+ * lazily on the first evaluation (the reference's first-call Optimize(), src/pdfz.cpp:442-444).
+ * sort=0 keeps the caller's sample order (used to measure what sorting buys). */
+int sxmc_hist_set_layout(sxmc_hist* h, int sort);
+int sxmc_hist_prepare(sxmc_hist* h);
+/* tuning knobs of the binning launch (EvalHist::OptimizeBin analogue, src/pdfz.cpp:630-727):
+ * smem_hist_max_bins: histograms up to this many bins are privatised in shared memory;
+ * blocks_per_sm <= 0 keeps the default. */
+int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_generic);
+/* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
+ * recorded on the launching stream when timing is enabled. */
+int sxmc_enable_kernel_timing(int on);
+int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);
+
+/* ---- nll_kernels: standalone NLL of a materialised lut (MCMC::nll, src/mcmc.cpp:390-415:
+ *      nll_event_chunks -> nll_event_reduce -> nll_total).  All pointers are DEVICE
+ *      pointers except the two outputs. ------------------------------------------------ */
+int sxmc_nll_eval(const float* lut_dev, size_t nevents, size_t nsignals,
+                  const double* pars_dev, size_t nparameters, size_t nsources,
+                  const double* means_dev, const double* sigmas_dev,
+                  const double* nexpected_dev, const unsigned* n_mc_dev,
+                  const short* source_id_dev, const unsigned* norms_dev,
+                  double* nll_out_host, double* event_sum_out_host);
+
+/* ---- MCMC (src/mcmc.h:36-138) ------------------------------------------------------- */
+typedef struct {
+  int nsources;                 /* MCMC::nsources */
+  int nsignals;                 /* MCMC::nsignals */
+  int nparameters;              /* nsources + sum(systematics[i].npars), src/mcmc.cpp:47-54 */
+  int nobservables;
+  const double* parameter_means;   /* [nparameters] src/mcmc.cpp:60-80 */
+  const double* parameter_sigma;   /* [nparameters] */
+  const int* parameter_fixed;      /* [nparameters] */
+  int systematics_fixed;           /* src/mcmc.cpp:67-72 */
+  int nsystematics;                /* systematics.size() (:264 guard) */
+  sxmc_hist* const* pdfs;          /* [nsignals] signals[i].histogram */
+  const double* nexpected;         /* [nsignals] */
+  const unsigned* n_mc;            /* [nsignals] */
+  const short* source_id;          /* [nsignals] */
+} sxmc_chain_config;
+
+/* MCMC::MCMC (src/mcmc.cpp:28-130).  The handles are borrowed. */
+int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out);
+int sxmc_chain_destroy(sxmc_chain* c);
+/* Philox4x32-10 seed (replaces init_device_rngs / gRandom->SetSeed, src/mcmc.cpp:118-128);
+ * `stream_id` separates independent chains of an ensemble (experiment index). */
+int sxmc_chain_set_seed(sxmc_chain* c, uint64_t seed, uint64_t stream_id);
+/* Test hook: draw the chain's random numbers from host tapes (standard normals, U(0,1))
+ * instead of Philox, in the reference's CPU call order (src/nll_kernels.cpp:45,65).
+ * NULL/0 returns to Philox. */
+int sxmc_chain_set_tapes(sxmc_chain* c, const double* normals, size_t n_normals,
+                         const double* uniforms, size_t n_uniforms);
+/* Optional sample-sharded mode: histograms are summed over the communicator after binning. */
+int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm);
+/* MCMC::operator() (src/mcmc.cpp:143-387).  `data` = host rows of nobservables+1 floats.
+ * The whole loop runs device-resident; sync_interval is accepted for signature parity
+ * (the device chain buffer holds every step, so there is no periodic drain).
+ * On return *nrows_out = rows left in the likelihood-space ntuple
+ * (steps [2*burnin, nsteps) unless debug_mode). */
+int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
+                   float burnin_fraction, int debug_mode, unsigned sync_interval,
+                   long* nrows_out);
+/* the ntuple rows: nparameters+1 floats each (src/nll_kernels.cpp:78-84) */
+int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows);
+int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out);
+/* device time of the step loop of the last run (the interval the reference times,
+ * src/mcmc.cpp:259-380), from CUDA events on the chain's stream. */
+int sxmc_chain_loop_ms(sxmc_chain* c, float* ms_out);
+/* number of kernel launches (graph kernel nodes included) issued by the last run */
+int sxmc_chain_launches(sxmc_chain* c, long* launches_out);
+/* per-step trace of the proposed-point NLL (nsteps doubles), enabled before run */
+int sxmc_chain_enable_trace(sxmc_chain* c, int on);
+int sxmc_chain_read_trace(sxmc_chain* c, double* nll_trace_out, double* proposed_out,
+                          unsigned nsteps);
+/* Re-evaluate PDFs (unless systematics_fixed... always when `rebin`) and the NLL at a host
+ * parameter vector after data were set by a run or by sxmc_chain_set_data: the replay hook
+ * for per-step NLL parity. */
+int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats);
+int sxmc_chain_nll_at(sxmc_chain* c, const double* pars, int rebin, double* nll_out,
+                      double* event_sum_out);
+/* norms / lut of the last evaluation (host copies) */
+int sxmc_chain_get_norms(sxmc_chain* c, unsigned* norms_out);
+int sxmc_chain_get_lut(sxmc_chain* c, float* lut_out);
+int sxmc_chain_get_bins(sxmc_chain* c, unsigned* bins_out);   /* [nsignals][total_nbins] */
+/* chain execution mode: 0 = CUDA graph of the per-step kernel sequence (default),
+ * 1 = plain stream launches (debugging / profiling). */
+int sxmc_chain_set_mode(sxmc_chain* c, int mode);
+
+/* ---- multi-GPU (no reference counterpart) ------------------------------- */
+int sxmc_comm_unique_id(void* id128_out);                 /* ncclGetUniqueId, 128 bytes */
+int sxmc_comm_create(const void* id128, int nranks, int rank, sxmc_comm** out);
+int sxmc_comm_destroy(sxmc_comm* comm);
+/* in-place uint32 sum over ranks of a device array (used by tests and by the chain) */
+int sxmc_comm_allreduce_u32(sxmc_comm* comm, unsigned* dev, size_t count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SXMC_B200_H */

@@ -111,7 +111,9 @@ void oracle_bin_samples(const float* data, long nsamples, int nfields, int nobs,
     }
     for (iobs = 0; iobs < nobs; iobs++) {
       double element = field_buffer[iobs];
-      if (element < lower[iobs] || element >= upper[iobs]) { in_pdf_domain = 0; break; }
+      /* NaN: the reference's two compares are false and (int)NaN indexes out of bounds
+       * (undefined; -ftrapv aborts).  Defined here, and in the CUDA path, as outside. */
+      if (element != element || element < lower[iobs] || element >= upper[iobs]) { in_pdf_domain = 0; break; }
       bin_id += (int)((element - lower[iobs]) * bin_scale[iobs]) * bin_stride[iobs];
     }
     if (in_pdf_domain) {
@@ -142,7 +144,7 @@ void oracle_set_eval_points(const float* points, long npoints, int nobs,
     int bin_id = 0;
     for (iobs = 0; iobs < nobs; iobs++) {
       double element = points[(nobs + 1) * ipoint + iobs];
-      if (element < lower[iobs] || element >= upper[iobs]) { in_pdf_domain = 0; break; }
+      if (element != element || element < lower[iobs] || element >= upper[iobs]) { in_pdf_domain = 0; break; }
       bin_id += (int)((element - lower[iobs]) * bin_scale[iobs]) * bin_stride[iobs];
     }
     if (points[(nobs + 1) * ipoint + nobs] != dataset) bin_id = -2;

@@ -1,0 +1,578 @@
+// bin_kernels.cu -- systematic transform + N-D binning (replaces zero_hist + bin_samples,
+// reference src/pdfz.cpp:334-408), SetEvalPoints (:245-302) and eval_pdf (:411-436) as
+// hand-written sm_100a CUDA.
+//
+// Bit-exactness contract: every double operation that feeds a bin index is done with the
+// explicit round-to-nearest intrinsics (__dadd_rn/__dmul_rn: never contracted into FMA), in
+// the order the reference's CPU build performs them (x86-64 g++ -O2 emits no FMA).  The TU
+// is also compiled with -fmad=false.
+#include "common.cuh"
+#include "kernels.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+namespace sxmc {
+
+// =========================================================================================
+// shared helpers
+// =========================================================================================
+
+// Per-launch geometry (identical for every job of a fast-path launch), passed by value so it
+// sits in the constant bank and costs no registers.
+struct Geo {
+  double lo[3], hi[3], sc[3];
+  int st[3];
+  int total_nbins;
+};
+
+struct SystRt {       // one systematic, resolved for the current parameter vector
+  int type, obs, extra, npars;
+  double c0;          // 0.0 + par0 * pow(x,0)   (src/pdfz.cpp:310-314 with i = 0)
+  double c1, c2, c3;  // raw coefficients of x, x^2, x^3
+  double onep;        // 1 + p, valid when npars == 1 (SCALE / CTSCALE, src/pdfz.cpp:320,323)
+};
+
+__device__ __forceinline__ void resolve_syst(const BinJob& job, int k, SystRt& s, bool slots) {
+  const SystDesc& d = job.syst[k];
+  s.type = d.type;
+  s.obs = slots ? d.obs_slot : d.obs;
+  s.extra = slots ? d.extra_slot : d.extra;
+  s.npars = d.npars;
+  double c[SXMC_MAX_NPARS] = {0, 0, 0, 0};
+  for (int i = 0; i < d.npars && i < SXMC_MAX_NPARS; ++i)
+    c[i] = job.params[(long long)d.pidx[i] * job.param_stride];
+  s.c0 = __dadd_rn(0.0, __dmul_rn(c[0], 1.0));
+  s.c1 = c[1]; s.c2 = c[2]; s.c3 = c[3];
+  s.onep = __dadd_rn(1.0, s.c0);
+}
+
+// p = sum_i par_i * pow(x, i) accumulated left to right (src/pdfz.cpp:310-314).
+// pow(x,0)=1 and pow(x,1)=x are exact; pow(x,2.0)==x*x for glibc; i=3 uses the
+// device pow (<=1 ulp-level difference from glibc possible; documented in DESIGN.md).
+__device__ __forceinline__ double syst_poly(const SystRt& s, double x) {
+  double p = s.c0;
+  if (s.npars > 1) {
+    p = __dadd_rn(p, __dmul_rn(s.c1, x));
+    if (s.npars > 2) {
+      p = __dadd_rn(p, __dmul_rn(s.c2, __dmul_rn(x, x)));
+      if (s.npars > 3) p = __dadd_rn(p, __dmul_rn(s.c3, pow(x, 3.0)));
+    }
+  }
+  return p;
+}
+
+// src/pdfz.cpp:316-330
+__device__ __forceinline__ double syst_apply_one(const SystRt& s, double x, double t) {
+  const double p = syst_poly(s, x);
+  switch (s.type) {
+    case SXMC_SYST_SHIFT: return __dadd_rn(x, p);
+    case SXMC_SYST_SCALE: return __dmul_rn(x, __dadd_rn(1.0, p));
+    case SXMC_SYST_CTSCALE:
+      return __dadd_rn(1.0, __dmul_rn(__dadd_rn(x, -1.0), __dadd_rn(1.0, p)));
+    case SXMC_SYST_RESOLUTION_SCALE: return __dadd_rn(x, __dmul_rn(p, __dadd_rn(x, -t)));
+  }
+  return x;
+}
+
+// Run-length aggregation of histogram updates: a thread walks a sorted run, so `b` changes
+// rarely; one atomic per run instead of one per sample.
+struct RunAcc {
+  int cur;
+  unsigned cnt;
+  unsigned norm;
+};
+
+template <bool SMEM>
+__device__ __forceinline__ void run_flush(RunAcc& r, unsigned* hist, int total_nbins) {
+  if (r.cur >= 0) {
+    r.norm += r.cnt;                       // in-domain count (src/pdfz.cpp:401-403)
+    if (r.cur < total_nbins) atomicAdd(hist + r.cur, r.cnt);
+  }
+}
+
+template <bool SMEM>
+__device__ __forceinline__ void run_push(RunAcc& r, int b, unsigned* hist, int total_nbins) {
+  if (b != r.cur) {
+    run_flush<SMEM>(r, hist, total_nbins);
+    r.cur = b;
+    r.cnt = 0;
+  }
+  r.cnt += 1;
+}
+
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+
+// =========================================================================================
+// fast kernel: NOBS <= 3 observables, NS <= MAX_SLOTS register-resident columns
+// =========================================================================================
+
+// All systematics of a fast launch have a single coefficient (npars <= 1): p is the same for
+// every sample, resolved once per segment into SystRt::c0 / onep.
+template <int NS>
+__device__ __forceinline__ void apply_syst_slots(double (&f)[NS][4], const SystRt& s) {
+#pragma unroll
+  for (int o = 0; o < NS; ++o) {
+    if (s.obs != o) continue;
+    if (s.type == SXMC_SYST_RESOLUTION_SCALE) {
+#pragma unroll
+      for (int e = 0; e < NS; ++e) {
+        if (s.extra != e) continue;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          f[o][k] = __dadd_rn(f[o][k], __dmul_rn(s.c0, __dadd_rn(f[o][k], -f[e][k])));
+      }
+    } else if (s.type == SXMC_SYST_SHIFT) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) f[o][k] = __dadd_rn(f[o][k], s.c0);
+    } else if (s.type == SXMC_SYST_SCALE) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) f[o][k] = __dmul_rn(f[o][k], s.onep);
+    } else {  // CTSCALE
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        f[o][k] = __dadd_rn(1.0, __dmul_rn(__dadd_rn(f[o][k], -1.0), s.onep));
+    }
+  }
+}
+
+// flat bin of one transformed sample, -1 when outside the PDF domain (src/pdfz.cpp:386-398).
+// NaN compares false on both tests => outside (the reference's (int)NaN is undefined).
+template <int NOBS>
+__device__ __forceinline__ int flat_bin(const double (&x)[NOBS], const Geo& g) {
+  bool in = true;
+  int b = 0;
+#pragma unroll
+  for (int o = 0; o < NOBS; ++o) {
+    in = in && (x[o] >= g.lo[o]) && (x[o] < g.hi[o]);
+    const int i = __double2int_rz(__dmul_rn(__dadd_rn(x[o], -g.lo[o]), g.sc[o]));
+    b += (NOBS == 1 ? i : i * g.st[o]);
+  }
+  return in ? b : -1;
+}
+
+template <int NOBS, int NS, bool SMEM, int U>
+__global__ void __launch_bounds__(BIN_THREADS)
+bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __restrict__ btile_prefix,
+                int njobs, const Geo geo) {
+  extern __shared__ unsigned s_hist[];
+  __shared__ SystRt s_syst[SXMC_MAX_SYST];
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const unsigned long long total = btile_prefix[njobs];
+  unsigned long long t0 = total * blockIdx.x / gridDim.x;
+  const unsigned long long t1 = total * (blockIdx.x + 1ull) / gridDim.x;
+  if (t0 >= t1) return;
+  int j = 0;
+  while (btile_prefix[j + 1] <= t0) ++j;
+
+  while (t0 < t1) {
+    const BinJob& job = jobs[j];
+    const unsigned long long jbeg = btile_prefix[j], jend = btile_prefix[j + 1];
+    const unsigned long long tend = t1 < jend ? t1 : jend;
+    const int nsyst = job.nsyst;
+    if (threadIdx.x < nsyst) resolve_syst(job, threadIdx.x, s_syst[threadIdx.x], true);
+    if (SMEM)
+      for (int b = threadIdx.x; b < geo.total_nbins; b += BIN_THREADS) s_hist[b] = 0;
+    __syncthreads();
+
+    unsigned* hist = SMEM ? s_hist : job.bins;
+    const float4* col[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c)
+      col[c] = reinterpret_cast<const float4*>(job.cols[job.slot_field[c]]);
+    const unsigned long long nwt = job.nwtiles;
+
+    RunAcc acc;
+    acc.norm = 0;
+    for (unsigned long long bt = t0; bt < tend; ++bt) {
+      const unsigned long long wt = (bt - jbeg) * BIN_WARPS + warp;
+      if (wt >= nwt) continue;
+      acc.cur = -1;
+      acc.cnt = 0;
+      const unsigned long long base = wt * (WT_ROWS * 32ull) + lane;
+#pragma unroll 1
+      for (int q0 = 0; q0 < WT_ROWS; q0 += U) {
+        float4 v[NS][U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int c = 0; c < NS; ++c) v[c][u] = ldg_stream(col[c] + base + (q0 + u) * 32);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          double f[NS][4];
+#pragma unroll
+          for (int c = 0; c < NS; ++c) {
+            f[c][0] = (double)v[c][u].x; f[c][1] = (double)v[c][u].y;
+            f[c][2] = (double)v[c][u].z; f[c][3] = (double)v[c][u].w;
+          }
+          for (int k = 0; k < nsyst; ++k) apply_syst_slots<NS>(f, s_syst[k]);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            double x[NOBS];
+#pragma unroll
+            for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
+            run_push<SMEM>(acc, flat_bin<NOBS>(x, geo), hist, geo.total_nbins);
+          }
+        }
+      }
+      run_flush<SMEM>(acc, hist, geo.total_nbins);
+    }
+
+    const unsigned wnorm = __reduce_add_sync(0xffffffffu, acc.norm);
+    if (lane == 0 && wnorm) atomicAdd(job.norm, wnorm);
+    if (SMEM) {
+      __syncthreads();
+      for (int b = threadIdx.x; b < geo.total_nbins; b += BIN_THREADS) {
+        const unsigned c = s_hist[b];
+        if (c) atomicAdd(job.bins + b, c);
+      }
+    }
+    __syncthreads();   // s_syst / s_hist are rewritten by the next segment
+    t0 = tend;
+    ++j;
+  }
+}
+
+// =========================================================================================
+// generic kernel: any nobs/nfields <= 10, any systematics; per-sample interpreter
+// =========================================================================================
+template <bool SMEM>
+__global__ void __launch_bounds__(BIN_THREADS)
+bin_generic_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __restrict__ btile_prefix,
+                   int njobs, int smem_bins) {
+  extern __shared__ unsigned s_hist[];
+  __shared__ SystRt s_syst[SXMC_MAX_SYST];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const unsigned long long total = btile_prefix[njobs];
+  unsigned long long t0 = total * blockIdx.x / gridDim.x;
+  const unsigned long long t1 = total * (blockIdx.x + 1ull) / gridDim.x;
+  if (t0 >= t1) return;
+  int j = 0;
+  while (btile_prefix[j + 1] <= t0) ++j;
+
+  while (t0 < t1) {
+    const BinJob& job = jobs[j];
+    const unsigned long long jbeg = btile_prefix[j], jend = btile_prefix[j + 1];
+    const unsigned long long tend = t1 < jend ? t1 : jend;
+    const int nsyst = job.nsyst, nobs = job.nobs, nfields = job.nfields;
+    const int total_nbins = job.total_nbins;
+    const bool use_smem = SMEM && total_nbins <= smem_bins;
+    if (threadIdx.x < nsyst) resolve_syst(job, threadIdx.x, s_syst[threadIdx.x], false);
+    if (use_smem)
+      for (int b = threadIdx.x; b < total_nbins; b += BIN_THREADS) s_hist[b] = 0;
+    __syncthreads();
+    unsigned* hist = use_smem ? s_hist : job.bins;
+
+    RunAcc acc;
+    acc.norm = 0;
+    for (unsigned long long bt = t0; bt < tend; ++bt) {
+      const unsigned long long wt = (bt - jbeg) * BIN_WARPS + warp;
+      if (wt >= job.nwtiles) continue;
+      acc.cur = -1;
+      acc.cnt = 0;
+      for (int i = 0; i < LANE_RUN; ++i) {
+        const unsigned long long off =
+            ((wt * WT_ROWS + (unsigned)(i >> 2)) * 32ull + lane) * 4ull + (i & 3);
+        double f[SXMC_MAX_NFIELDS];
+        for (int c = 0; c < nfields; ++c) f[c] = (double)__ldg(job.cols[c] + off);
+        for (int k = 0; k < nsyst; ++k) {
+          const SystRt& s = s_syst[k];
+          f[s.obs] = syst_apply_one(s, f[s.obs], f[s.extra]);
+        }
+        bool in = true;
+        int b = 0;
+        for (int o = 0; o < nobs; ++o) {
+          const double x = f[o];
+          if (!(x >= job.lower[o]) || !(x < job.upper[o])) { in = false; break; }
+          b += __double2int_rz(__dmul_rn(__dadd_rn(x, -job.lower[o]), job.scale[o])) * job.stride[o];
+        }
+        run_push<SMEM>(acc, in ? b : -1, hist, total_nbins);
+      }
+      run_flush<SMEM>(acc, hist, total_nbins);
+    }
+    const unsigned wnorm = __reduce_add_sync(0xffffffffu, acc.norm);
+    if (lane == 0 && wnorm) atomicAdd(job.norm, wnorm);
+    if (use_smem) {
+      __syncthreads();
+      for (int b = threadIdx.x; b < total_nbins; b += BIN_THREADS) {
+        const unsigned c = s_hist[b];
+        if (c) atomicAdd(job.bins + b, c);
+      }
+    }
+    __syncthreads();
+    t0 = tend;
+    ++j;
+  }
+}
+
+// =========================================================================================
+// launch dispatch
+// =========================================================================================
+typedef void (*FastKernel)(const BinJob*, const unsigned long long*, int, const Geo);
+
+template <int NOBS, int NS, bool SMEM>
+static FastKernel pick_fast_u() {
+  constexpr int U = (NS <= 2) ? 4 : 2;
+  return bin_fast_kernel<NOBS, NS, SMEM, U>;
+}
+
+template <bool SMEM>
+static FastKernel pick_fast(int nobs, int ns) {
+  switch (nobs * 10 + ns) {
+    case 11: return pick_fast_u<1, 1, SMEM>();
+    case 12: return pick_fast_u<1, 2, SMEM>();
+    case 13: return pick_fast_u<1, 3, SMEM>();
+    case 22: return pick_fast_u<2, 2, SMEM>();
+    case 23: return pick_fast_u<2, 3, SMEM>();
+    case 24: return pick_fast_u<2, 4, SMEM>();
+    case 33: return pick_fast_u<3, 3, SMEM>();
+    case 34: return pick_fast_u<3, 4, SMEM>();
+    case 35: return pick_fast_u<3, 5, SMEM>();
+  }
+  return nullptr;
+}
+
+bool bin_fast_supported(int nobs, int nslots) {
+  return pick_fast<false>(nobs, nslots) != nullptr;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+int launch_bin(const BinLaunch& L, cudaStream_t stream) {
+  if (L.total_btiles == 0) return SXMC_OK;
+  const size_t smem = L.smem_hist ? sizeof(unsigned) * (size_t)L.max_total_nbins : 0;
+  const void* fn = nullptr;
+  FastKernel fk = nullptr;
+  if (L.fast) {
+    fk = L.smem_hist ? pick_fast<true>(L.nobs, L.nslots) : pick_fast<false>(L.nobs, L.nslots);
+    if (!fk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
+    fn = (const void*)fk;
+  } else {
+    fn = L.smem_hist ? (const void*)bin_generic_kernel<true> : (const void*)bin_generic_kernel<false>;
+  }
+  if (smem > 48 * 1024)
+    SXMC_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, BIN_THREADS, smem));
+  if (occ < 1) occ = 1;
+  if (L.blocks_per_sm > 0 && L.blocks_per_sm < occ) occ = L.blocks_per_sm;
+  unsigned long long grid = (unsigned long long)num_sms() * occ;
+  if (grid > L.total_btiles) grid = L.total_btiles;
+  if (L.fast) {
+    Geo g;
+    for (int i = 0; i < 3; ++i) {
+      g.lo[i] = L.lower[i]; g.hi[i] = L.upper[i]; g.sc[i] = L.scale[i]; g.st[i] = L.stride[i];
+    }
+    g.total_nbins = L.max_total_nbins;
+    fk<<<(unsigned)grid, BIN_THREADS, smem, stream>>>(L.jobs_dev, L.prefix_dev, L.njobs, g);
+  } else if (L.smem_hist) {
+    bin_generic_kernel<true><<<(unsigned)grid, BIN_THREADS, smem, stream>>>(
+        L.jobs_dev, L.prefix_dev, L.njobs, L.max_total_nbins);
+  } else {
+    bin_generic_kernel<false><<<(unsigned)grid, BIN_THREADS, 0, stream>>>(
+        L.jobs_dev, L.prefix_dev, L.njobs, 0);
+  }
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
+// =========================================================================================
+// layout preparation: sort key, gather into the tiled SoA layout
+// =========================================================================================
+__device__ __forceinline__ unsigned ordered_bits(float v) {
+  unsigned u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// key = (nominal flat bin with every coordinate clamped into the histogram) << 32 |
+//       order-preserving bits of the primary field (the observable the first systematic moves)
+__global__ void make_keys_kernel(const float* __restrict__ aos, unsigned long long n, int nfields,
+                                 int nobs, PrepGeo g, int primary, unsigned long long* keys,
+                                 unsigned* idx) {
+  const unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* row = aos + i * nfields;
+  unsigned long long b = 0;
+  for (int o = 0; o < nobs; ++o) {
+    const double x = (double)row[o];
+    int k = g.nbins[o] - 1;   // NaN and >= upper go last
+    if (x < g.upper[o]) {
+      k = __double2int_rz((x - g.lower[o]) * g.scale[o]);
+      if (!(x >= g.lower[o])) k = 0;
+      if (k > g.nbins[o] - 1) k = g.nbins[o] - 1;
+      if (k < 0) k = 0;
+    }
+    b += (unsigned long long)k * (unsigned)g.stride[o];
+  }
+  keys[i] = (b << 32) | ordered_bits(row[primary]);
+  idx[i] = (unsigned)i;
+}
+
+__global__ void iota_kernel(unsigned* idx, unsigned long long n) {
+  const unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (i < n) idx[i] = (unsigned)i;
+}
+
+// sorted position s -> tiled position (see common.cuh)
+__host__ __device__ __forceinline__ unsigned long long tiled_offset(unsigned long long s) {
+  const unsigned long long wt = s / WT_SAMPLES;
+  const unsigned r = (unsigned)(s % WT_SAMPLES);
+  const unsigned lane = r / LANE_RUN, i = r % LANE_RUN;
+  return ((wt * WT_ROWS + (i >> 2)) * 32ull + lane) * 4ull + (i & 3);
+}
+
+__global__ void gather_tiled_kernel(const float* __restrict__ aos, const unsigned* __restrict__ idx,
+                                    unsigned long long n, unsigned long long npad, int nfields,
+                                    int nobs, float* cols, unsigned long long col_pitch,
+                                    unsigned* perm_out) {
+  const unsigned long long s = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (s >= npad) return;
+  const unsigned long long off = tiled_offset(s);
+  if (s < n) {
+    const unsigned src = idx[s];
+    if (perm_out) perm_out[s] = src;
+    for (int f = 0; f < nfields; ++f) cols[f * col_pitch + off] = aos[(unsigned long long)src * nfields + f];
+  } else {
+    // padding: +inf observables are outside every domain under every transform
+    for (int f = 0; f < nfields; ++f)
+      cols[f * col_pitch + off] = f < nobs ? __int_as_float(0x7f800000) : 0.0f;
+  }
+}
+
+// inverse of gather_tiled: original-order AoS rows (EvalHist::GetSamples)
+__global__ void scatter_aos_kernel(const float* __restrict__ cols, unsigned long long col_pitch,
+                                   const unsigned* __restrict__ perm, unsigned long long n,
+                                   int nfields, float* aos) {
+  const unsigned long long s = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const unsigned long long off = tiled_offset(s);
+  const unsigned dst = perm[s];
+  for (int f = 0; f < nfields; ++f) aos[(unsigned long long)dst * nfields + f] = cols[f * col_pitch + off];
+}
+
+int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,
+                   const PrepGeo& g, int primary, bool sort, float* cols_dev,
+                   unsigned long long col_pitch, unsigned* perm_dev, cudaStream_t stream) {
+  const unsigned long long npad = col_pitch;
+  if (n >= (1ull << 32)) { set_error("prepare_layout: more than 2^32-1 samples in one PDF"); return SXMC_EINVAL; }
+  unsigned* idx = nullptr;
+  unsigned long long* keys = nullptr;
+  unsigned* idx_alt = nullptr;
+  unsigned long long* keys_alt = nullptr;
+  void* tmp = nullptr;
+  const unsigned nblk = (unsigned)((n + 255) / 256);
+  int rc = SXMC_OK;
+  if (n > 0) {
+    SXMC_CUDA(cudaMalloc(&idx, sizeof(unsigned) * n));
+    if (sort) {
+      SXMC_CUDA(cudaMalloc(&keys, sizeof(unsigned long long) * n));
+      SXMC_CUDA(cudaMalloc(&keys_alt, sizeof(unsigned long long) * n));
+      SXMC_CUDA(cudaMalloc(&idx_alt, sizeof(unsigned) * n));
+      make_keys_kernel<<<nblk, 256, 0, stream>>>(aos_dev, n, nfields, nobs, g, primary, keys, idx);
+      cub::DoubleBuffer<unsigned long long> dk(keys, keys_alt);
+      cub::DoubleBuffer<unsigned> dv(idx, idx_alt);
+      size_t tmp_bytes = 0;
+      int end_bit = 32;
+      while (end_bit < 64 && (g.total_nbins >> (end_bit - 32)) != 0) ++end_bit;
+      SXMC_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (long long)n, 0, end_bit, stream));
+      SXMC_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+      SXMC_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, (long long)n, 0, end_bit, stream));
+      if (dv.Current() != idx) { unsigned* t = idx; idx = idx_alt; idx_alt = t; }
+    } else {
+      iota_kernel<<<nblk, 256, 0, stream>>>(idx, n);
+    }
+  }
+  if (npad > 0) {
+    const unsigned nb2 = (unsigned)((npad + 255) / 256);
+    gather_tiled_kernel<<<nb2, 256, 0, stream>>>(aos_dev, idx, n, npad, nfields, nobs, cols_dev,
+                                                 col_pitch, perm_dev);
+  }
+  cudaError_t e = cudaStreamSynchronize(stream);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  cudaFree(idx); cudaFree(keys); cudaFree(keys_alt); cudaFree(idx_alt); cudaFree(tmp);
+  if (e != cudaSuccess) rc = cuda_fail(e, "prepare_layout", __FILE__, __LINE__);
+  return rc;
+}
+
+int unprepare_to_aos(const float* cols_dev, unsigned long long col_pitch, const unsigned* perm_dev,
+                     unsigned long long n, int nfields, float* aos_dev, cudaStream_t stream) {
+  if (n == 0) return SXMC_OK;
+  scatter_aos_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(cols_dev, col_pitch, perm_dev,
+                                                                      n, nfields, aos_dev);
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
+// =========================================================================================
+// SetEvalPoints (src/pdfz.cpp:245-302) and eval_pdf (src/pdfz.cpp:411-436)
+// =========================================================================================
+__global__ void read_bins_kernel(const float* __restrict__ points, long long npoints, int nobs,
+                                 PrepGeo g, unsigned dataset, int* __restrict__ read_bins) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= npoints) return;
+  const float* row = points + i * (nobs + 1);
+  bool in = true;
+  int b = 0;
+  for (int o = 0; o < nobs; ++o) {
+    const double x = (double)row[o];
+    if (!(x >= g.lower[o]) || !(x < g.upper[o])) { in = false; break; }
+    b += __double2int_rz(__dmul_rn(__dadd_rn(x, -g.lower[o]), g.scale[o])) * g.stride[o];
+  }
+  // `points[idx] != this->dataset`: float vs unsigned compares in float (:290-293)
+  if (row[nobs] != (float)dataset) b = -2;
+  read_bins[i] = in ? b : -1;
+}
+
+int launch_read_bins(const float* points_dev, long long npoints, int nobs, const PrepGeo& g,
+                     unsigned dataset, int* read_bins_dev, cudaStream_t stream) {
+  if (npoints <= 0) return SXMC_OK;
+  read_bins_kernel<<<(unsigned)((npoints + 255) / 256), 256, 0, stream>>>(points_dev, npoints, nobs, g,
+                                                                          dataset, read_bins_dev);
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
+__global__ void eval_pdf_kernel(const EvalPdfJob* __restrict__ jobs, int njobs) {
+  const EvalPdfJob job = jobs[blockIdx.y];
+  // bin_norm = *norm * bin_volume  (unsigned -> double, :417)
+  const double bin_norm = __dmul_rn((double)*job.norm, job.bin_volume);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < job.npoints;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int b = job.read_bins[i];
+    float v;
+    if (b == -2) v = 0.0f;
+    else if (b < 0) v = __int_as_float(0x7fc00000);
+    else if (b >= job.total_nbins) v = 0.0f;   // reference reads past the array (undefined)
+    else v = (float)((double)job.bins[b] / bin_norm);
+    job.out[job.stride * i] = v;
+  }
+}
+
+int launch_eval_pdf(const EvalPdfJob* jobs_dev, int njobs, long long max_points, cudaStream_t stream) {
+  if (njobs <= 0 || max_points <= 0) return SXMC_OK;
+  long long gx = (max_points + 255) / 256;
+  if (gx > 1024) gx = 1024;
+  dim3 grid((unsigned)gx, (unsigned)njobs);
+  eval_pdf_kernel<<<grid, 256, 0, stream>>>(jobs_dev, njobs);
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
+}  // namespace sxmc

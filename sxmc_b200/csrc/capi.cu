@@ -1,0 +1,1138 @@
+// capi.cu -- the extern "C" layer of libsxmc_b200.so (declared in include/sxmc_b200.h):
+// handles, argument validation with the reference's pdfz::Error messages, layout
+// preparation, batched launches, the device-resident MCMC loop (CUDA graph) and NCCL glue.
+#include "common.cuh"
+#include "kernels.h"
+
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+namespace sxmc {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d in `%s`", (int)e, cudaGetErrorString(e), file,
+           line, what);
+  g_error = buf;
+  return SXMC_ECUDA;
+}
+
+static int g_smem_hist_max_bins = 8192;
+static int g_blocks_per_sm = 0;
+static int g_force_generic = 0;
+static int g_timing = 0;
+static float g_last_bin_ms = -1.f, g_last_nll_ms = -1.f;
+static bool g_init_done = false;
+
+static int ensure_init() {
+  if (g_init_done) return SXMC_OK;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    set_error("no usable CUDA device: libsxmc_b200 has no CPU fallback");
+    cudaGetLastError();
+    return SXMC_ECUDA;
+  }
+  int dev = 0, major = 0;
+  SXMC_CUDA(cudaGetDevice(&dev));
+  SXMC_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) {
+    set_error("libsxmc_b200 is built for sm_100a (Blackwell B200) only");
+    return SXMC_ECUDA;
+  }
+  g_init_done = true;
+  return SXMC_OK;
+}
+
+// A batch of binning jobs staged in pinned host memory and mirrored on the device.
+struct Batch {
+  BinJob* host = nullptr;          // pinned
+  BinJob* dev = nullptr;
+  unsigned long long* prefix_host = nullptr;   // pinned
+  unsigned long long* prefix_dev = nullptr;
+  EvalPdfJob* ep_host = nullptr;   // pinned
+  EvalPdfJob* ep_dev = nullptr;
+  int cap = 0;
+  BinLaunch launch;
+  long long max_points = 0;
+  int n_ep = 0;
+
+  int reserve(int n) {
+    if (n <= cap) return SXMC_OK;
+    release();
+    SXMC_CUDA(cudaMallocHost(&host, sizeof(BinJob) * n));
+    SXMC_CUDA(cudaMalloc(&dev, sizeof(BinJob) * n));
+    SXMC_CUDA(cudaMallocHost(&prefix_host, sizeof(unsigned long long) * (n + 1)));
+    SXMC_CUDA(cudaMalloc(&prefix_dev, sizeof(unsigned long long) * (n + 1)));
+    SXMC_CUDA(cudaMallocHost(&ep_host, sizeof(EvalPdfJob) * n));
+    SXMC_CUDA(cudaMalloc(&ep_dev, sizeof(EvalPdfJob) * n));
+    cap = n;
+    return SXMC_OK;
+  }
+  void release() {
+    if (host) cudaFreeHost(host);
+    if (dev) cudaFree(dev);
+    if (prefix_host) cudaFreeHost(prefix_host);
+    if (prefix_dev) cudaFree(prefix_dev);
+    if (ep_host) cudaFreeHost(ep_host);
+    if (ep_dev) cudaFree(ep_dev);
+    host = nullptr; dev = nullptr; prefix_host = nullptr; prefix_dev = nullptr;
+    ep_host = nullptr; ep_dev = nullptr; cap = 0;
+  }
+};
+
+}  // namespace sxmc
+
+using namespace sxmc;
+
+struct sxmc_hist {
+  int nfields = 0, nobs = 0;
+  unsigned dataset = 0;
+  std::vector<double> lower, upper;
+  std::vector<int> nbins, stride;
+  int total_nbins = 0;
+  double bin_volume = 0;
+  size_t nsamples = 0;
+  float* aos_dev = nullptr;             // caller's rows until the tiled layout is built
+  float* cols_dev = nullptr;            // nfields columns of col_pitch floats
+  unsigned long long col_pitch = 0;     // nwtiles * WT_SAMPLES
+  unsigned long long nwtiles = 0;
+  unsigned* perm_dev = nullptr;         // sorted position -> original row
+  bool prepared = false;
+  bool sort = true;
+  int primary = -1;
+  unsigned* bins_dev = nullptr;
+  int* read_bins_dev = nullptr;
+  size_t npoints = 0;
+  float* pdf_dev = nullptr; long pdf_offset = 0, pdf_stride = 1;
+  unsigned* norm_dev = nullptr; long norm_offset = 0;
+  const double* param_dev = nullptr; long param_offset = 0, param_stride = 1;
+  std::vector<SystDesc> systs;
+  cudaStream_t stream = nullptr;
+  Batch batch;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+namespace sxmc {
+
+static void fill_prep_geo(const sxmc_hist* h, PrepGeo& g) {
+  memset(&g, 0, sizeof g);
+  for (int i = 0; i < h->nobs; ++i) {
+    g.lower[i] = h->lower[i];
+    g.upper[i] = h->upper[i];
+    g.scale[i] = h->nbins[i] / (h->upper[i] - h->lower[i]);   // src/pdfz.cpp:365-368
+    g.nbins[i] = h->nbins[i];
+    g.stride[i] = h->stride[i];
+  }
+  g.total_nbins = h->total_nbins;
+}
+
+static int wanted_primary(const sxmc_hist* h) {
+  if (!h->systs.empty() && h->systs[0].obs < h->nfields) return h->systs[0].obs;
+  return 0;
+}
+
+#define SXMC_TRY(expr) do { int _rc = (expr); if (_rc) return _rc; } while (0)
+#define SXMC_INVAL(msg) do { set_error(msg); return SXMC_EINVAL; } while (0)
+
+// Undo the tiled layout: the caller's rows, in their original order, back in aos_dev.
+static int recover_rows(sxmc_hist* h) {
+  const unsigned long long n = h->nsamples;
+  if (n > 0) {
+    SXMC_CUDA(cudaMalloc(&h->aos_dev, sizeof(float) * n * h->nfields));
+    SXMC_TRY(unprepare_to_aos(h->cols_dev, h->col_pitch, h->perm_dev, n, h->nfields, h->aos_dev, h->stream));
+    SXMC_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  cudaFree(h->cols_dev); h->cols_dev = nullptr;
+  cudaFree(h->perm_dev); h->perm_dev = nullptr;
+  h->prepared = false;
+  return SXMC_OK;
+}
+
+// Build (or rebuild) the sorted, tiled SoA layout.
+static int ensure_prepared(sxmc_hist* h) {
+  const int primary = wanted_primary(h);
+  if (h->prepared && (!h->sort || primary == h->primary)) return SXMC_OK;
+  const unsigned long long n = h->nsamples;
+  if (h->prepared) SXMC_TRY(recover_rows(h));   // systematics changed the sort key
+  h->nwtiles = (n + WT_SAMPLES - 1) / WT_SAMPLES;
+  h->col_pitch = h->nwtiles * WT_SAMPLES;
+  if (h->col_pitch > 0) {
+    SXMC_CUDA(cudaMalloc(&h->cols_dev, sizeof(float) * h->col_pitch * h->nfields));
+    SXMC_CUDA(cudaMalloc(&h->perm_dev, sizeof(unsigned) * n));
+  }
+  PrepGeo g;
+  fill_prep_geo(h, g);
+  int rc = prepare_layout(h->aos_dev, n, h->nfields, h->nobs, g, primary, h->sort, h->cols_dev,
+                          h->col_pitch, h->perm_dev, h->stream);
+  if (rc) return rc;
+  cudaFree(h->aos_dev);
+  h->aos_dev = nullptr;
+  h->primary = primary;
+  h->prepared = true;
+  return SXMC_OK;
+}
+
+// Fill one BinJob for handle h writing into (bins, norm) and reading (params, stride).
+static int fill_job(sxmc_hist* h, BinJob& job, unsigned* bins, unsigned* norm, const double* params,
+                    long long param_stride) {
+  int rc = ensure_prepared(h);
+  if (rc) return rc;
+  memset(&job, 0, sizeof job);
+  for (int f = 0; f < h->nfields; ++f) job.cols[f] = h->cols_dev + (size_t)f * h->col_pitch;
+  job.nwtiles = h->nwtiles;
+  job.bins = bins;
+  job.norm = norm;
+  job.params = params;
+  job.param_stride = param_stride;
+  job.total_nbins = h->total_nbins;
+  job.nobs = h->nobs;
+  job.nfields = h->nfields;
+  job.nsyst = (int)h->systs.size();
+  for (int i = 0; i < h->nobs; ++i) {
+    job.lower[i] = h->lower[i];
+    job.upper[i] = h->upper[i];
+    job.scale[i] = h->nbins[i] / (h->upper[i] - h->lower[i]);
+    job.stride[i] = h->stride[i];
+  }
+  // register slots: observables first, then every other field a systematic touches
+  int slot_of[SXMC_MAX_NFIELDS];
+  for (int f = 0; f < SXMC_MAX_NFIELDS; ++f) slot_of[f] = -1;
+  int ns = 0;
+  bool overflow = false;
+  for (int o = 0; o < h->nobs; ++o) {
+    if (ns < MAX_SLOTS) { job.slot_field[ns] = o; slot_of[o] = ns; }
+    else overflow = true;
+    ++ns;
+  }
+  for (size_t k = 0; k < h->systs.size(); ++k) {
+    SystDesc d = h->systs[k];
+    const int need[2] = {d.obs, d.type == SXMC_SYST_RESOLUTION_SCALE ? d.extra : d.obs};
+    for (int t = 0; t < 2; ++t) {
+      if (slot_of[need[t]] < 0) {
+        if (ns < MAX_SLOTS) { job.slot_field[ns] = need[t]; slot_of[need[t]] = ns; }
+        else overflow = true;
+        ++ns;
+      }
+    }
+    d.obs_slot = (short)std::max(0, slot_of[d.obs]);
+    d.extra_slot = (short)(d.type == SXMC_SYST_RESOLUTION_SCALE ? std::max(0, slot_of[d.extra]) : 0);
+    job.syst[k] = d;
+  }
+  job.nslots = overflow ? MAX_SLOTS + 1 : ns;
+  return SXMC_OK;
+}
+
+// Decide the launch shape for a filled batch of n jobs.
+static void plan_launch(Batch& b, int n) {
+  BinLaunch& L = b.launch;
+  memset(&L, 0, sizeof L);
+  L.jobs_dev = b.dev;
+  L.prefix_dev = b.prefix_dev;
+  L.njobs = n;
+  unsigned long long total = 0;
+  b.prefix_host[0] = 0;
+  bool uniform = true;
+  int max_bins = 0, max_slots = 0;
+  bool poly = false;
+  for (int j = 0; j < n; ++j) {
+    const BinJob& job = b.host[j];
+    total += (job.nwtiles + BIN_WARPS - 1) / BIN_WARPS;
+    b.prefix_host[j + 1] = total;
+    max_bins = std::max(max_bins, job.total_nbins);
+    max_slots = std::max(max_slots, job.nslots);
+    const BinJob& j0 = b.host[0];
+    if (job.nobs != j0.nobs || job.total_nbins != j0.total_nbins) uniform = false;
+    for (int o = 0; uniform && o < job.nobs; ++o)
+      if (job.lower[o] != j0.lower[o] || job.upper[o] != j0.upper[o] || job.scale[o] != j0.scale[o] ||
+          job.stride[o] != j0.stride[o])
+        uniform = false;
+    for (int k = 0; k < job.nsyst; ++k)
+      if (job.syst[k].npars > 1) poly = true;   // per-sample polynomials go through the generic kernel
+  }
+  L.total_btiles = total;
+  L.max_total_nbins = max_bins;
+  L.nobs = n ? b.host[0].nobs : 0;
+  L.nslots = max_slots;
+  L.fast = n > 0 && uniform && !poly && !g_force_generic && L.nobs <= 3 &&
+           bin_fast_supported(L.nobs, max_slots);
+  if (L.fast) {
+    // every job of a fast launch uses the same slot count (columns it does not need are
+    // simply re-reads of observable 0)
+    for (int j = 0; j < n; ++j) {
+      BinJob& job = b.host[j];
+      for (int s = job.nslots; s < max_slots; ++s) job.slot_field[s] = 0;
+      job.nslots = max_slots;
+    }
+    for (int o = 0; o < L.nobs; ++o) {
+      L.lower[o] = b.host[0].lower[o]; L.upper[o] = b.host[0].upper[o];
+      L.scale[o] = b.host[0].scale[o]; L.stride[o] = b.host[0].stride[o];
+    }
+  }
+  L.smem_hist = max_bins <= g_smem_hist_max_bins;
+  L.blocks_per_sm = g_blocks_per_sm;
+}
+
+static int upload_batch(Batch& b, int n, cudaStream_t stream) {
+  SXMC_CUDA(cudaMemcpyAsync(b.dev, b.host, sizeof(BinJob) * n, cudaMemcpyHostToDevice, stream));
+  SXMC_CUDA(cudaMemcpyAsync(b.prefix_dev, b.prefix_host, sizeof(unsigned long long) * (n + 1),
+                            cudaMemcpyHostToDevice, stream));
+  if (b.n_ep > 0)
+    SXMC_CUDA(cudaMemcpyAsync(b.ep_dev, b.ep_host, sizeof(EvalPdfJob) * b.n_ep, cudaMemcpyHostToDevice, stream));
+  return SXMC_OK;
+}
+
+}  // namespace sxmc
+
+extern "C" {
+
+const char* sxmc_last_error(void) { return g_error.c_str(); }
+const char* sxmc_version(void) { return "sxmc_b200 0.1 (sm_100a)"; }
+
+int sxmc_init(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    set_error("no usable CUDA device: libsxmc_b200 has no CPU fallback");
+    return SXMC_ECUDA;
+  }
+  SXMC_CUDA(cudaSetDevice(device));
+  g_init_done = false;
+  return ensure_init();
+}
+
+int sxmc_device_synchronize(void) {
+  SXMC_TRY(ensure_init());
+  SXMC_CUDA(cudaDeviceSynchronize());
+  return SXMC_OK;
+}
+
+int sxmc_buf_alloc(size_t bytes, void** dev_out) {
+  SXMC_TRY(ensure_init());
+  SXMC_CUDA(cudaMalloc(dev_out, bytes ? bytes : 1));
+  return SXMC_OK;
+}
+int sxmc_buf_free(void* dev) { if (dev) SXMC_CUDA(cudaFree(dev)); return SXMC_OK; }
+int sxmc_buf_upload(void* dev, const void* host, size_t bytes) {
+  if (bytes) SXMC_CUDA(cudaMemcpy(dev, host, bytes, cudaMemcpyHostToDevice));
+  return SXMC_OK;
+}
+int sxmc_buf_download(void* host, const void* dev, size_t bytes) {
+  if (bytes) SXMC_CUDA(cudaMemcpy(host, dev, bytes, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+int sxmc_buf_zero(void* dev, size_t bytes) {
+  if (bytes) SXMC_CUDA(cudaMemset(dev, 0, bytes));
+  return SXMC_OK;
+}
+int sxmc_host_alloc(size_t bytes, void** host_out) {
+  SXMC_TRY(ensure_init());
+  SXMC_CUDA(cudaMallocHost(host_out, bytes ? bytes : 1));
+  return SXMC_OK;
+}
+int sxmc_host_free(void* host) { if (host) SXMC_CUDA(cudaFreeHost(host)); return SXMC_OK; }
+
+int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_generic) {
+  if (smem_hist_max_bins >= 0) g_smem_hist_max_bins = std::min(smem_hist_max_bins, 56 * 1024);
+  g_blocks_per_sm = blocks_per_sm;
+  g_force_generic = force_generic;
+  return SXMC_OK;
+}
+int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
+int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms) {
+  if (bin_ms) *bin_ms = g_last_bin_ms;
+  if (nll_ms) *nll_ms = g_last_nll_ms;
+  return SXMC_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// EvalHist
+// ---------------------------------------------------------------------------------------
+int sxmc_hist_create(const float* samples, size_t nfloats, int nfields, int nobservables,
+                     const double* lower, int nlower, const double* upper, int nupper,
+                     const int* nbins, int nnbins, unsigned dataset, sxmc_hist** out) {
+  if (!out) SXMC_INVAL("sxmc_hist_create: out is NULL");
+  *out = nullptr;
+  // Eval::Eval checks, in the reference's order and wording (src/pdfz.cpp:63-81)
+  if (nfields <= 0 || nfloats % (size_t)nfields != 0)
+    SXMC_INVAL("Length of samples array is not divisible by number of fields.");
+  if (nobservables == 0) SXMC_INVAL("Number of observables in PDF is zero.");
+  if (nobservables > nfields)
+    SXMC_INVAL("Number of observables cannot be greater than number of fields.");
+  if (nupper != nobservables)
+    SXMC_INVAL("Number of upper bounds must be same as number of observables.");
+  if (nlower != nobservables)
+    SXMC_INVAL("Number of lower bounds must be same as number of observables.");
+  // EvalHist::EvalHist checks (src/pdfz.cpp:189-195)
+  if (nnbins != nobservables)
+    SXMC_INVAL("Size of nbins array must be same as number of observables.");
+  if (nfields > SXMC_MAX_NFIELDS)
+    SXMC_INVAL("Exceeded maximum number of fields per sample. Edit MAX_NFIELDS in pdfz.cpp to fix this!");
+  if (nobservables < 0) SXMC_INVAL("Number of observables is negative.");
+
+  sxmc_hist* h = new sxmc_hist;
+  h->nfields = nfields;
+  h->nobs = nobservables;
+  h->dataset = dataset;
+  h->lower.assign(lower, lower + nobservables);
+  h->upper.assign(upper, upper + nobservables);
+  h->nbins.assign(nbins, nbins + nobservables);
+  h->stride.assign(nobservables, 1);
+  h->bin_volume = 1.0f;   // src/pdfz.cpp:201-204
+  for (int i = 0; i < nobservables; ++i) h->bin_volume *= (upper[i] - lower[i]) / nbins[i];
+  for (int i = nobservables - 2; i >= 0; --i) h->stride[i] = nbins[i + 1] * h->stride[i + 1];
+  long long total = (long long)h->stride[0] * nbins[0];
+  for (int i = 0; i < nobservables; ++i) if (nbins[i] < 0) total = 0;
+  if (total == 0) { delete h; SXMC_INVAL("Cannot make histogram with zero bins."); }
+  if (total > 0x7fffffffLL) { delete h; SXMC_INVAL("Histogram has more than 2^31-1 bins."); }
+  h->total_nbins = (int)total;
+  h->nsamples = nfloats / (size_t)nfields;
+
+  int rc = ensure_init();
+  if (rc) { delete h; return rc; }
+  cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMalloc(&h->bins_dev, sizeof(unsigned) * (size_t)h->total_nbins);
+  if (e == cudaSuccess) e = cudaMemset(h->bins_dev, 0, sizeof(unsigned) * (size_t)h->total_nbins);
+  if (e == cudaSuccess && nfloats > 0) {
+    e = cudaMalloc(&h->aos_dev, sizeof(float) * nfloats);
+    if (e == cudaSuccess) e = cudaMemcpy(h->aos_dev, samples, sizeof(float) * nfloats, cudaMemcpyHostToDevice);
+  }
+  if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+  if (e != cudaSuccess) { sxmc_hist_destroy(h); return cuda_fail(e, "sxmc_hist_create", __FILE__, __LINE__); }
+  *out = h;
+  return SXMC_OK;
+}
+
+int sxmc_hist_destroy(sxmc_hist* h) {
+  if (!h) return SXMC_OK;
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  cudaFree(h->aos_dev); cudaFree(h->cols_dev); cudaFree(h->perm_dev);
+  cudaFree(h->bins_dev); cudaFree(h->read_bins_dev);
+  h->batch.release();
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return SXMC_OK;
+}
+
+int sxmc_hist_add_systematic(sxmc_hist* h, int type, int obs, int extra_field, int npars,
+                             const short* pars) {
+  if (!h) SXMC_INVAL("sxmc_hist_add_systematic: NULL handle");
+  if (type < 0 || type > 3) SXMC_INVAL("Unknown systematic type");   // src/pdfz.cpp:170
+  if ((int)h->systs.size() >= SXMC_MAX_SYST) SXMC_INVAL("Too many systematics on one PDF (SXMC_MAX_SYST).");
+  if (npars < 0 || npars > SXMC_MAX_NPARS) SXMC_INVAL("Too many coefficients in one systematic (SXMC_MAX_NPARS).");
+  if (obs < 0 || obs >= h->nfields) SXMC_INVAL("Systematic observable index is not a field of the samples.");
+  if (type == SXMC_SYST_RESOLUTION_SCALE && (extra_field < 0 || extra_field >= h->nfields))
+    SXMC_INVAL("Systematic truth-field index is not a field of the samples.");
+  SystDesc d;
+  memset(&d, 0, sizeof d);
+  d.type = (short)type;
+  d.obs = (short)obs;
+  d.extra = (short)(type == SXMC_SYST_RESOLUTION_SCALE ? extra_field : 0);
+  d.npars = (short)npars;
+  for (int i = 0; i < npars; ++i) d.pidx[i] = pars[i];
+  h->systs.push_back(d);
+  return SXMC_OK;
+}
+
+int sxmc_hist_set_eval_points(sxmc_hist* h, const float* points, size_t nfloats) {
+  if (!h) SXMC_INVAL("sxmc_hist_set_eval_points: NULL handle");
+  if (nfloats % (size_t)(h->nobs + 1) != 0)
+    SXMC_INVAL("Number of entries in evaluation points array not divisible by number of observables.");
+  const size_t np = nfloats / (size_t)(h->nobs + 1);
+  cudaFree(h->read_bins_dev);
+  h->read_bins_dev = nullptr;
+  h->npoints = np;
+  SXMC_CUDA(cudaMalloc(&h->read_bins_dev, sizeof(int) * (np ? np : 1)));
+  if (np == 0) return SXMC_OK;
+  float* pts = nullptr;
+  SXMC_CUDA(cudaMalloc(&pts, sizeof(float) * nfloats));
+  cudaError_t e = cudaMemcpyAsync(pts, points, sizeof(float) * nfloats, cudaMemcpyHostToDevice, h->stream);
+  int rc = SXMC_OK;
+  if (e == cudaSuccess) {
+    PrepGeo g;
+    fill_prep_geo(h, g);
+    rc = launch_read_bins(pts, (long long)np, h->nobs, g, h->dataset, h->read_bins_dev, h->stream);
+    e = cudaStreamSynchronize(h->stream);
+  }
+  cudaFree(pts);
+  if (e != cudaSuccess) return cuda_fail(e, "sxmc_hist_set_eval_points", __FILE__, __LINE__);
+  return rc;
+}
+
+int sxmc_hist_set_pdf_buffer(sxmc_hist* h, float* dev, long offset, long stride) {
+  h->pdf_dev = dev; h->pdf_offset = offset; h->pdf_stride = stride; return SXMC_OK;
+}
+int sxmc_hist_set_norm_buffer(sxmc_hist* h, unsigned* dev, long offset) {
+  h->norm_dev = dev; h->norm_offset = offset; return SXMC_OK;
+}
+int sxmc_hist_set_param_buffer(sxmc_hist* h, const double* dev, long offset, long stride) {
+  h->param_dev = dev; h->param_offset = offset; h->param_stride = stride; return SXMC_OK;
+}
+
+int sxmc_hist_set_layout(sxmc_hist* h, int sort) {
+  const bool want = sort != 0;
+  if (h->prepared && h->sort != want) SXMC_TRY(recover_rows(h));
+  h->sort = want;
+  return SXMC_OK;
+}
+int sxmc_hist_prepare(sxmc_hist* h) { return ensure_prepared(h); }
+
+static int hists_eval_on(sxmc_hist* const* hs, int n, int do_eval_pdf, cudaStream_t stream, Batch& b) {
+  SXMC_TRY(ensure_init());
+  SXMC_TRY(b.reserve(n));
+  b.n_ep = 0;
+  b.max_points = 0;
+  for (int j = 0; j < n; ++j) {
+    sxmc_hist* h = hs[j];
+    if (!h->norm_dev) { set_error("EvalAsync: no normalization buffer bound"); return SXMC_ESTATE; }
+    if (!h->systs.empty() && !h->param_dev) { set_error("EvalAsync: no parameter buffer bound"); return SXMC_ESTATE; }
+    SXMC_TRY(fill_job(h, b.host[j], h->bins_dev, h->norm_dev + h->norm_offset,
+                      h->param_dev ? h->param_dev + h->param_offset : nullptr, h->param_stride));
+    // zero_hist (src/pdfz.cpp:334-346)
+    SXMC_CUDA(cudaMemsetAsync(h->bins_dev, 0, sizeof(unsigned) * (size_t)h->total_nbins, stream));
+    SXMC_CUDA(cudaMemsetAsync(h->norm_dev + h->norm_offset, 0, sizeof(unsigned), stream));
+    if (do_eval_pdf && h->read_bins_dev && h->npoints > 0) {   // :474 guard
+      if (!h->pdf_dev) { set_error("EvalAsync: no PDF value buffer bound"); return SXMC_ESTATE; }
+      EvalPdfJob& e = b.ep_host[b.n_ep++];
+      e.read_bins = h->read_bins_dev;
+      e.bins = h->bins_dev;
+      e.norm = h->norm_dev + h->norm_offset;
+      e.out = h->pdf_dev + h->pdf_offset;
+      e.stride = h->pdf_stride;
+      e.npoints = (long long)h->npoints;
+      e.bin_volume = h->bin_volume;
+      e.total_nbins = h->total_nbins;
+      b.max_points = std::max(b.max_points, e.npoints);
+    }
+  }
+  plan_launch(b, n);
+  SXMC_TRY(upload_batch(b, n, stream));
+  SXMC_TRY(launch_bin(b.launch, stream));
+  SXMC_TRY(launch_eval_pdf(b.ep_dev, b.n_ep, b.max_points, stream));
+  return SXMC_OK;
+}
+
+int sxmc_hist_eval_async(sxmc_hist* h, int do_eval_pdf) {
+  if (!h) SXMC_INVAL("sxmc_hist_eval_async: NULL handle");
+  sxmc_hist* one[1] = {h};
+  return hists_eval_on(one, 1, do_eval_pdf, h->stream, h->batch);
+}
+int sxmc_hist_eval_finished(sxmc_hist* h) {
+  SXMC_CUDA(cudaStreamSynchronize(h->stream));
+  return SXMC_OK;
+}
+int sxmc_hists_eval_async(sxmc_hist* const* hs, int n, int do_eval_pdf) {
+  if (n <= 0) return SXMC_OK;
+  // handles evaluated individually may still be running on their own streams
+  for (int j = 1; j < n; ++j) SXMC_CUDA(cudaStreamSynchronize(hs[j]->stream));
+  return hists_eval_on(hs, n, do_eval_pdf, hs[0]->stream, hs[0]->batch);
+}
+
+int sxmc_hist_total_nbins(const sxmc_hist* h) { return h->total_nbins; }
+double sxmc_hist_bin_volume(const sxmc_hist* h) { return h->bin_volume; }
+size_t sxmc_hist_nsamples(const sxmc_hist* h) { return h->nsamples; }
+size_t sxmc_hist_neval_points(const sxmc_hist* h) { return h->npoints; }
+int sxmc_hist_get_bins(sxmc_hist* h, unsigned* host_out) {
+  SXMC_CUDA(cudaStreamSynchronize(h->stream));
+  SXMC_CUDA(cudaMemcpy(host_out, h->bins_dev, sizeof(unsigned) * (size_t)h->total_nbins, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+int sxmc_hist_get_read_bins(sxmc_hist* h, int* host_out) {
+  if (h->npoints) SXMC_CUDA(cudaMemcpy(host_out, h->read_bins_dev, sizeof(int) * h->npoints, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+int sxmc_hist_get_samples(sxmc_hist* h, float* host_out) {
+  const size_t nf = h->nsamples * (size_t)h->nfields;
+  if (nf == 0) return SXMC_OK;
+  if (!h->prepared) {
+    SXMC_CUDA(cudaMemcpy(host_out, h->aos_dev, sizeof(float) * nf, cudaMemcpyDeviceToHost));
+    return SXMC_OK;
+  }
+  float* tmp = nullptr;
+  SXMC_CUDA(cudaMalloc(&tmp, sizeof(float) * nf));
+  int rc = unprepare_to_aos(h->cols_dev, h->col_pitch, h->perm_dev, h->nsamples, h->nfields, tmp, h->stream);
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  if (e == cudaSuccess) e = cudaMemcpy(host_out, tmp, sizeof(float) * nf, cudaMemcpyDeviceToHost);
+  cudaFree(tmp);
+  if (e != cudaSuccess) return cuda_fail(e, "sxmc_hist_get_samples", __FILE__, __LINE__);
+  return rc;
+}
+
+}  // extern "C"
+
+// =========================================================================================
+// NCCL glue (dlopen'd so that single-GPU use has no NCCL dependency)
+// =========================================================================================
+namespace sxmc {
+typedef struct { char internal[128]; } nccl_unique_id;
+typedef void* nccl_comm_t;
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(nccl_unique_id*) = nullptr;
+  int (*CommInitRank)(nccl_comm_t*, int, nccl_unique_id, int) = nullptr;
+  int (*CommDestroy)(nccl_comm_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+static int load_nccl() {
+  if (g_nccl.lib) return SXMC_OK;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  void* lib = nullptr;
+  for (const char* n : names) { lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (lib) break; }
+  if (!lib) { set_error(std::string("cannot load libnccl: ") + dlerror()); return SXMC_ENCCL; }
+  g_nccl.GetUniqueId = (int (*)(nccl_unique_id*))dlsym(lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(nccl_comm_t*, int, nccl_unique_id, int))dlsym(lib, "ncclCommInitRank");
+  g_nccl.CommDestroy = (int (*)(nccl_comm_t))dlsym(lib, "ncclCommDestroy");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t))dlsym(lib, "ncclAllReduce");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) {
+    set_error("libnccl lacks a required symbol");
+    return SXMC_ENCCL;
+  }
+  g_nccl.lib = lib;
+  return SXMC_OK;
+}
+static int nccl_fail(int rc, const char* what) {
+  set_error(std::string("NCCL error in ") + what + ": " +
+            (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?"));
+  return SXMC_ENCCL;
+}
+constexpr int NCCL_UINT32 = 3;   // ncclUint32
+constexpr int NCCL_SUM = 0;      // ncclSum
+}  // namespace sxmc
+
+struct sxmc_comm {
+  sxmc::nccl_comm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+};
+
+struct sxmc_chain {
+  int nsources = 0, nsignals = 0, nparameters = 0, nobs = 0, nsystematics = 0;
+  bool systematics_fixed = true;
+  std::vector<double> means, sigmas, nexpected;
+  std::vector<int> fixed;
+  std::vector<unsigned> n_mc;
+  std::vector<short> source_id;
+  std::vector<sxmc_hist*> pdfs;
+  int total_nbins = 0;
+  uint64_t seed = 0, stream_id = 0;
+  cudaStream_t stream = nullptr;
+  ChainState* st_dev = nullptr;
+  ChainState* st_host = nullptr;      // pinned
+  unsigned* hist_buf[2] = {nullptr, nullptr};   // [ns*total_nbins bins][ns norms]
+  size_t hist_words = 0;
+  Batch batch[2];
+  NllSignal* sigs_dev[2] = {nullptr, nullptr};
+  double* partials = nullptr;
+  unsigned* ticket = nullptr;
+  float* lut_dev = nullptr;
+  size_t nevents = 0;
+  int nll_grid = 1;
+  bool have_data = false;
+  int last_buf = 0;
+  float* rows_dev = nullptr; long long row_cap = 0;
+  double* nll_trace_dev = nullptr; double* prop_trace_dev = nullptr; unsigned trace_steps = 0;
+  bool trace = false;
+  double* tape_n_dev = nullptr; size_t n_tape_n = 0;
+  double* tape_u_dev = nullptr; size_t n_tape_u = 0;
+  sxmc_comm* comm = nullptr;
+  int mode = 0;
+  float loop_ms = 0;
+  long launches = 0;
+  long long nrows = 0, accepted = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+namespace sxmc {
+
+static int chain_build_tables(sxmc_chain* c) {
+  const int ns = c->nsignals;
+  for (int b = 0; b < 2; ++b) {
+    SXMC_TRY(c->batch[b].reserve(ns));
+    unsigned* bins = c->hist_buf[b];
+    unsigned* norms = c->hist_buf[b] + (size_t)ns * c->total_nbins;
+    std::vector<NllSignal> sg(ns);
+    for (int j = 0; j < ns; ++j) {
+      sxmc_hist* h = c->pdfs[j];
+      SXMC_TRY(fill_job(h, c->batch[b].host[j], bins + (size_t)j * c->total_nbins, norms + j,
+                        c->st_dev->proposed + c->nsources, 1));
+      sg[j].bins = bins + (size_t)j * c->total_nbins;
+      sg[j].norm = norms + j;
+      sg[j].read_bins = h->read_bins_dev;
+      sg[j].nexpected = c->nexpected[j];
+      sg[j].bin_volume = h->bin_volume;
+      sg[j].n_mc = c->n_mc[j];
+      sg[j].total_nbins = h->total_nbins;
+      sg[j].source_id = c->source_id[j];
+    }
+    c->batch[b].n_ep = 0;
+    plan_launch(c->batch[b], ns);
+    SXMC_TRY(upload_batch(c->batch[b], ns, c->stream));
+    SXMC_CUDA(cudaMemcpyAsync(c->sigs_dev[b], sg.data(), sizeof(NllSignal) * ns, cudaMemcpyHostToDevice, c->stream));
+    SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  return SXMC_OK;
+}
+
+static int chain_bin(sxmc_chain* c, int b) {
+  SXMC_TRY(launch_bin(c->batch[b].launch, c->stream));
+  c->launches += 1;
+  if (c->comm && c->comm->nranks > 1) {
+    int rc = g_nccl.AllReduce(c->hist_buf[b], c->hist_buf[b], c->hist_words, NCCL_UINT32, NCCL_SUM,
+                              c->comm->comm, c->stream);
+    if (rc) return nccl_fail(rc, "ncclAllReduce");
+    c->launches += 1;
+  }
+  return SXMC_OK;
+}
+
+static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut) {
+  NllLaunch L;
+  L.sigs_dev = c->sigs_dev[b];
+  L.nsignals = c->nsignals;
+  L.nevents = (long long)c->nevents;
+  L.state = c->st_dev;
+  L.partials = c->partials;
+  L.ticket = c->ticket;
+  L.mode = mode;
+  L.lut = lut;
+  L.zero_ptr = zero_other ? c->hist_buf[1 - b] : nullptr;
+  L.zero_words = zero_other ? c->hist_words : 0;
+  L.grid = c->nll_grid;
+  SXMC_TRY(launch_nll(L, c->stream));
+  c->launches += 1;
+  return SXMC_OK;
+}
+
+}  // namespace sxmc
+
+extern "C" {
+
+int sxmc_hists_eval_host(sxmc_hist* const* hs, int n, const double* params, int nparams,
+                         long param_offset, unsigned* norms_out, float* pdf_out) {
+  if (n <= 0) return SXMC_OK;
+  SXMC_TRY(ensure_init());
+  cudaStream_t stream = hs[0]->stream;
+  double* p_dev = nullptr;
+  unsigned* n_dev = nullptr;
+  float* pdf_dev = nullptr;
+  size_t npts = hs[0]->npoints;
+  for (int j = 1; j < n; ++j) npts = std::max(npts, hs[j]->npoints);
+  cudaError_t e = cudaMalloc(&p_dev, sizeof(double) * std::max(1, nparams));
+  if (e == cudaSuccess) e = cudaMalloc(&n_dev, sizeof(unsigned) * n);
+  if (e == cudaSuccess && pdf_out && npts) e = cudaMalloc(&pdf_dev, sizeof(float) * npts * n);
+  int rc = SXMC_OK;
+  if (e == cudaSuccess && nparams > 0)
+    e = cudaMemcpyAsync(p_dev, params, sizeof(double) * nparams, cudaMemcpyHostToDevice, stream);
+  if (e == cudaSuccess) {
+    for (int j = 0; j < n; ++j) {
+      sxmc_hist_set_param_buffer(hs[j], p_dev, param_offset, 1);
+      sxmc_hist_set_norm_buffer(hs[j], n_dev, j);
+      sxmc_hist_set_pdf_buffer(hs[j], pdf_dev, (long)(j * npts), 1);
+    }
+    rc = sxmc_hists_eval_async(hs, n, pdf_dev != nullptr);
+    if (!rc) e = cudaMemcpyAsync(norms_out, n_dev, sizeof(unsigned) * n, cudaMemcpyDeviceToHost, stream);
+    if (!rc && e == cudaSuccess && pdf_dev)
+      e = cudaMemcpyAsync(pdf_out, pdf_dev, sizeof(float) * npts * n, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  }
+  for (int j = 0; j < n; ++j) {   // the temporaries die here: unbind them
+    sxmc_hist_set_param_buffer(hs[j], nullptr, 0, 1);
+    sxmc_hist_set_norm_buffer(hs[j], nullptr, 0);
+    sxmc_hist_set_pdf_buffer(hs[j], nullptr, 0, 1);
+  }
+  cudaFree(p_dev); cudaFree(n_dev); cudaFree(pdf_dev);
+  if (e != cudaSuccess) return cuda_fail(e, "sxmc_hists_eval_host", __FILE__, __LINE__);
+  return rc;
+}
+
+int sxmc_nll_eval(const float* lut_dev, size_t nevents, size_t nsignals, const double* pars_dev,
+                  size_t nparameters, size_t nsources, const double* means_dev,
+                  const double* sigmas_dev, const double* nexpected_dev, const unsigned* n_mc_dev,
+                  const short* source_id_dev, const unsigned* norms_dev, double* nll_out_host,
+                  double* event_sum_out_host) {
+  SXMC_TRY(ensure_init());
+  double* out2 = nullptr;
+  SXMC_CUDA(cudaMalloc(&out2, 2 * sizeof(double)));
+  int rc = launch_nll_lut(lut_dev, nevents, nsignals, pars_dev, nparameters, nsources, means_dev,
+                          sigmas_dev, nexpected_dev, n_mc_dev, source_id_dev, norms_dev, out2, 0);
+  double h[2] = {0, 0};
+  cudaError_t e = cudaMemcpy(h, out2, sizeof h, cudaMemcpyDeviceToHost);
+  cudaFree(out2);
+  if (e != cudaSuccess) return cuda_fail(e, "sxmc_nll_eval", __FILE__, __LINE__);
+  if (nll_out_host) *nll_out_host = h[0];
+  if (event_sum_out_host) *event_sum_out_host = h[1];
+  return rc;
+}
+
+// ---------------------------------------------------------------------------------------
+// MCMC
+// ---------------------------------------------------------------------------------------
+int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out) {
+  if (!cfg || !out) SXMC_INVAL("sxmc_chain_create: NULL argument");
+  *out = nullptr;
+  if (cfg->nparameters <= 0 || cfg->nparameters > SXMC_MAX_PARAMETERS)
+    SXMC_INVAL("sxmc_chain_create: nparameters out of range (SXMC_MAX_PARAMETERS)");
+  if (cfg->nsignals <= 0 || cfg->nsignals > 128) SXMC_INVAL("sxmc_chain_create: nsignals out of range (1..128)");
+  if (cfg->nsources <= 0 || cfg->nsources > cfg->nparameters) SXMC_INVAL("sxmc_chain_create: nsources out of range");
+  SXMC_TRY(ensure_init());
+  sxmc_chain* c = new sxmc_chain;
+  c->nsources = cfg->nsources; c->nsignals = cfg->nsignals; c->nparameters = cfg->nparameters;
+  c->nobs = cfg->nobservables; c->nsystematics = cfg->nsystematics;
+  c->systematics_fixed = cfg->systematics_fixed != 0;
+  c->means.assign(cfg->parameter_means, cfg->parameter_means + cfg->nparameters);
+  c->sigmas.assign(cfg->parameter_sigma, cfg->parameter_sigma + cfg->nparameters);
+  c->fixed.assign(cfg->parameter_fixed, cfg->parameter_fixed + cfg->nparameters);
+  c->pdfs.assign(cfg->pdfs, cfg->pdfs + cfg->nsignals);
+  c->nexpected.assign(cfg->nexpected, cfg->nexpected + cfg->nsignals);
+  c->n_mc.assign(cfg->n_mc, cfg->n_mc + cfg->nsignals);
+  c->source_id.assign(cfg->source_id, cfg->source_id + cfg->nsignals);
+  c->total_nbins = c->pdfs[0]->total_nbins;
+  for (int j = 0; j < c->nsignals; ++j) {
+    if (c->pdfs[j]->total_nbins != c->total_nbins || c->pdfs[j]->nobs != c->nobs) {
+      delete c;
+      SXMC_INVAL("sxmc_chain_create: all signal PDFs must share the observables' binning");
+    }
+    if (c->source_id[j] < 0 || c->source_id[j] >= c->nsources) {
+      delete c;
+      SXMC_INVAL("sxmc_chain_create: source_id out of range");
+    }
+  }
+  c->hist_words = (size_t)c->nsignals * ((size_t)c->total_nbins + 1);
+  cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMalloc(&c->st_dev, sizeof(ChainState));
+  if (e == cudaSuccess) e = cudaMallocHost(&c->st_host, sizeof(ChainState));
+  for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+    e = cudaMalloc(&c->hist_buf[b], sizeof(unsigned) * c->hist_words);
+    if (e == cudaSuccess) e = cudaMalloc(&c->sigs_dev[b], sizeof(NllSignal) * c->nsignals);
+  }
+  if (e == cudaSuccess) e = cudaMalloc(&c->partials, sizeof(double) * 148 * 8);
+  if (e == cudaSuccess) e = cudaMalloc(&c->ticket, sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMemset(c->ticket, 0, sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
+  if (e != cudaSuccess) { sxmc_chain_destroy(c); return cuda_fail(e, "sxmc_chain_create", __FILE__, __LINE__); }
+  *out = c;
+  return SXMC_OK;
+}
+
+int sxmc_chain_destroy(sxmc_chain* c) {
+  if (!c) return SXMC_OK;
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  cudaFree(c->st_dev);
+  if (c->st_host) cudaFreeHost(c->st_host);
+  for (int b = 0; b < 2; ++b) { cudaFree(c->hist_buf[b]); cudaFree(c->sigs_dev[b]); c->batch[b].release(); }
+  cudaFree(c->partials); cudaFree(c->ticket); cudaFree(c->lut_dev); cudaFree(c->rows_dev);
+  cudaFree(c->nll_trace_dev); cudaFree(c->prop_trace_dev); cudaFree(c->tape_n_dev); cudaFree(c->tape_u_dev);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return SXMC_OK;
+}
+
+int sxmc_chain_set_seed(sxmc_chain* c, uint64_t seed, uint64_t stream_id) {
+  c->seed = seed; c->stream_id = stream_id; return SXMC_OK;
+}
+
+int sxmc_chain_set_tapes(sxmc_chain* c, const double* normals, size_t n_normals,
+                         const double* uniforms, size_t n_uniforms) {
+  cudaFree(c->tape_n_dev); cudaFree(c->tape_u_dev);
+  c->tape_n_dev = nullptr; c->tape_u_dev = nullptr; c->n_tape_n = 0; c->n_tape_u = 0;
+  if (normals && uniforms) {
+    SXMC_CUDA(cudaMalloc(&c->tape_n_dev, sizeof(double) * std::max<size_t>(1, n_normals)));
+    SXMC_CUDA(cudaMalloc(&c->tape_u_dev, sizeof(double) * std::max<size_t>(1, n_uniforms)));
+    SXMC_CUDA(cudaMemcpy(c->tape_n_dev, normals, sizeof(double) * n_normals, cudaMemcpyHostToDevice));
+    SXMC_CUDA(cudaMemcpy(c->tape_u_dev, uniforms, sizeof(double) * n_uniforms, cudaMemcpyHostToDevice));
+    c->n_tape_n = n_normals; c->n_tape_u = n_uniforms;
+  }
+  return SXMC_OK;
+}
+
+int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm) { c->comm = comm; return SXMC_OK; }
+int sxmc_chain_set_mode(sxmc_chain* c, int mode) { c->mode = mode; return SXMC_OK; }
+int sxmc_chain_enable_trace(sxmc_chain* c, int on) { c->trace = on != 0; return SXMC_OK; }
+
+int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
+  if (data_nfloats % (size_t)(c->nobs + 1) != 0)
+    SXMC_INVAL("Number of entries in evaluation points array not divisible by number of observables.");
+  c->nevents = data_nfloats / (size_t)(c->nobs + 1);
+  // p->SetEvalPoints(data) for every pdf (src/mcmc.cpp:235)
+  for (int j = 0; j < c->nsignals; ++j) SXMC_TRY(sxmc_hist_set_eval_points(c->pdfs[j], data, data_nfloats));
+  c->nll_grid = nll_grid_for((long long)c->nevents);
+  cudaFree(c->lut_dev);
+  c->lut_dev = nullptr;
+  SXMC_CUDA(cudaMalloc(&c->lut_dev, sizeof(float) * std::max<size_t>(1, c->nevents * c->nsignals)));
+  SXMC_TRY(chain_build_tables(c));
+  c->have_data = true;
+  return SXMC_OK;
+}
+
+}  // extern "C"
+
+namespace sxmc {
+
+// Host-side initial state: the block of src/mcmc.cpp:152-228.
+static void chain_init_state(sxmc_chain* c, ChainState& s, unsigned nsteps, float burnin_fraction,
+                             int debug_mode) {
+  memset(&s, 0, sizeof s);
+  const int np = c->nparameters;
+  int nfloat = 0;
+  for (int i = 0; i < np; ++i) {
+    s.current[i] = c->means[i];
+    s.proposed[i] = c->means[i];
+    s.means[i] = c->means[i];
+    s.sigmas[i] = c->sigmas[i];
+    s.fixed[i] = c->fixed[i];
+    nfloat += c->fixed[i] ? 0 : 1;
+  }
+  const float scale_factor = 2.4 * 2.4 / nfloat;   // Haario, 2001 (src/mcmc.cpp:199)
+  s.scale_factor = scale_factor;
+  for (int i = 0; i < np; ++i) {
+    if (c->fixed[i]) { s.jump_width[i] = -1; continue; }
+    float mean = c->means[i];
+    float sigma = c->sigmas[i];
+    float width = 0.1;
+    if (sigma > 0) {
+      width = sigma;
+    } else if (i < c->nsignals) {     // sic: nsignals, not nsources (src/mcmc.cpp:217)
+      float m = std::max(mean, (float)10);
+      width = sqrt(m) / m;
+    } else {
+      width = sqrt(std::max(mean, (float)1));
+    }
+    s.jump_width[i] = 0.1 * width * scale_factor;
+  }
+  s.nparameters = np;
+  s.nsources = c->nsources;
+  s.nsignals = c->nsignals;
+  s.debug_mode = debug_mode;
+  s.step = 0;
+  s.burnin_steps = nsteps * burnin_fraction;        // src/mcmc.cpp:152
+  s.seed = c->seed;
+  s.stream_id = c->stream_id;
+  s.tape_normals = c->tape_n_dev; s.n_normals = c->n_tape_n;
+  s.tape_uniforms = c->tape_u_dev; s.n_uniforms = c->n_tape_u;
+  s.rows = c->rows_dev;
+  s.row_cap = c->row_cap;
+  s.nll_trace = c->trace ? c->nll_trace_dev : nullptr;
+  s.prop_trace = c->trace ? c->prop_trace_dev : nullptr;
+}
+
+static int chain_push_state(sxmc_chain* c) {
+  SXMC_CUDA(cudaMemcpyAsync(c->st_dev, c->st_host, sizeof(ChainState), cudaMemcpyHostToDevice, c->stream));
+  return SXMC_OK;
+}
+static int chain_pull_state(sxmc_chain* c) {
+  SXMC_CUDA(cudaMemcpyAsync(c->st_host, c->st_dev, sizeof(ChainState), cudaMemcpyDeviceToHost, c->stream));
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  return SXMC_OK;
+}
+
+// one MCMC step enqueued on the chain's stream: [bin -> (allreduce)] -> lookup+nll+decide+propose
+static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b) {
+  if (rebin) SXMC_TRY(chain_bin(c, b));
+  SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));
+  return SXMC_OK;
+}
+
+}  // namespace sxmc
+
+extern "C" {
+
+int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
+                   float burnin_fraction, int debug_mode, unsigned sync_interval, long* nrows_out) {
+  (void)sync_interval;
+  if (!c) SXMC_INVAL("sxmc_chain_run: NULL chain");
+  SXMC_TRY(sxmc_chain_set_data(c, data, data_nfloats));
+  const int np = c->nparameters;
+  // chain buffer: every step fits (the reference drains a sync_interval-sized buffer instead)
+  if (c->row_cap < (long long)nsteps || !c->rows_dev) {
+    cudaFree(c->rows_dev);
+    c->rows_dev = nullptr;
+    c->row_cap = std::max<long long>(1, nsteps);
+    SXMC_CUDA(cudaMalloc(&c->rows_dev, sizeof(float) * (size_t)c->row_cap * (np + 1)));
+  }
+  if (c->trace && c->trace_steps < nsteps) {
+    cudaFree(c->nll_trace_dev); cudaFree(c->prop_trace_dev);
+    c->nll_trace_dev = nullptr; c->prop_trace_dev = nullptr;
+    SXMC_CUDA(cudaMalloc(&c->nll_trace_dev, sizeof(double) * std::max(1u, nsteps)));
+    SXMC_CUDA(cudaMalloc(&c->prop_trace_dev, sizeof(double) * std::max(1u, nsteps) * np));
+    c->trace_steps = nsteps;
+  }
+  chain_init_state(c, *c->st_host, nsteps, burnin_fraction, debug_mode);
+  SXMC_TRY(chain_push_state(c));
+  c->launches = 0;
+
+  // initial evaluation at the means (src/mcmc.cpp:233-252): always bins, whatever is fixed
+  SXMC_CUDA(cudaMemsetAsync(c->hist_buf[0], 0, sizeof(unsigned) * c->hist_words, c->stream));
+  SXMC_CUDA(cudaMemsetAsync(c->hist_buf[1], 0, sizeof(unsigned) * c->hist_words, c->stream));
+  SXMC_TRY(chain_bin(c, 0));
+  SXMC_TRY(chain_nll(c, 0, NLL_MODE_INIT, false, nullptr));
+  c->last_buf = 0;
+
+  const bool rebin = c->nsystematics > 0 && !c->systematics_fixed;   // src/mcmc.cpp:264
+  SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
+  unsigned done = 0;
+  const bool has_comm = c->comm && c->comm->nranks > 1;
+  if (c->mode == 0 && nsteps >= 32) {
+    // CUDA graph of GRAPH_STEPS consecutive steps; step i bins into buffer (i+1)&1 when rebinning
+    const unsigned GRAPH_STEPS = 16;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    const long before = c->launches;
+    SXMC_CUDA(cudaStreamBeginCapture(c->stream, has_comm ? cudaStreamCaptureModeRelaxed
+                                                          : cudaStreamCaptureModeThreadLocal));
+    int rc = SXMC_OK;
+    for (unsigned k = 0; k < GRAPH_STEPS && !rc; ++k) rc = chain_enqueue_step(c, rebin, rebin ? (int)((k + 1) & 1) : 0);
+    cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture", __FILE__, __LINE__);
+    const long per_graph = c->launches - before;
+    c->launches = before;
+    e = cudaGraphInstantiate(&exec, graph, 0);
+    if (e != cudaSuccess) { cudaGraphDestroy(graph); return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__); }
+    const unsigned ngraphs = nsteps / GRAPH_STEPS;
+    for (unsigned g = 0; g < ngraphs; ++g) {
+      e = cudaGraphLaunch(exec, c->stream);
+      if (e != cudaSuccess) break;
+      c->launches += per_graph;
+    }
+    cudaGraphExecDestroy(exec);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphLaunch", __FILE__, __LINE__);
+    done = ngraphs * GRAPH_STEPS;   // GRAPH_STEPS is even: buffer parity is preserved
+  }
+  for (unsigned i = done; i < nsteps; ++i)
+    SXMC_TRY(chain_enqueue_step(c, rebin, rebin ? (int)((i + 1) & 1) : 0));
+  if (rebin && nsteps > 0) c->last_buf = (int)(nsteps & 1);   // step nsteps-1 used buffer nsteps&1
+  SXMC_CUDA(cudaEventRecord(c->ev1, c->stream));
+  SXMC_TRY(chain_pull_state(c));
+  SXMC_CUDA(cudaEventElapsedTime(&c->loop_ms, c->ev0, c->ev1));
+  c->nrows = c->st_host->nrows;
+  c->accepted = c->st_host->accepted;
+  if (nrows_out) *nrows_out = (long)std::min(c->nrows, c->row_cap);
+  return SXMC_OK;
+}
+
+int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows) {
+  long long n = std::min<long long>(std::min(c->nrows, c->row_cap), max_rows);
+  if (n > 0)
+    SXMC_CUDA(cudaMemcpy(rows_out, c->rows_dev, sizeof(float) * (size_t)n * (c->nparameters + 1),
+                         cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out) { *accepted_out = (long)c->accepted; return SXMC_OK; }
+int sxmc_chain_loop_ms(sxmc_chain* c, float* ms_out) { *ms_out = c->loop_ms; return SXMC_OK; }
+int sxmc_chain_launches(sxmc_chain* c, long* launches_out) { *launches_out = c->launches; return SXMC_OK; }
+
+int sxmc_chain_read_trace(sxmc_chain* c, double* nll_trace_out, double* proposed_out, unsigned nsteps) {
+  if (!c->nll_trace_dev || nsteps > c->trace_steps) { set_error("trace was not enabled for that many steps"); return SXMC_ESTATE; }
+  if (nll_trace_out) SXMC_CUDA(cudaMemcpy(nll_trace_out, c->nll_trace_dev, sizeof(double) * nsteps, cudaMemcpyDeviceToHost));
+  if (proposed_out)
+    SXMC_CUDA(cudaMemcpy(proposed_out, c->prop_trace_dev, sizeof(double) * nsteps * c->nparameters, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+
+int sxmc_chain_nll_at(sxmc_chain* c, const double* pars, int rebin, double* nll_out, double* event_sum_out) {
+  if (!c->have_data) { set_error("sxmc_chain_nll_at: no data set"); return SXMC_ESTATE; }
+  if (!c->st_host->nparameters) {   // never run: build a neutral state
+    chain_init_state(c, *c->st_host, 0, 0.f, 0);
+    SXMC_TRY(chain_push_state(c));
+    rebin = 1;
+  }
+  SXMC_CUDA(cudaMemcpyAsync(c->st_dev->proposed, pars, sizeof(double) * c->nparameters, cudaMemcpyHostToDevice, c->stream));
+  const int b = c->last_buf;
+  cudaEvent_t e0 = c->ev0, e1 = c->ev1;
+  if (rebin) {
+    SXMC_CUDA(cudaMemsetAsync(c->hist_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
+    if (g_timing) SXMC_CUDA(cudaEventRecord(e0, c->stream));
+    SXMC_TRY(chain_bin(c, b));
+    if (g_timing) {
+      SXMC_CUDA(cudaEventRecord(e1, c->stream));
+      SXMC_CUDA(cudaEventSynchronize(e1));
+      SXMC_CUDA(cudaEventElapsedTime(&g_last_bin_ms, e0, e1));
+    }
+  }
+  if (g_timing) SXMC_CUDA(cudaEventRecord(e0, c->stream));
+  SXMC_TRY(chain_nll(c, b, NLL_MODE_EVAL_ONLY, false, c->lut_dev));
+  if (g_timing) {
+    SXMC_CUDA(cudaEventRecord(e1, c->stream));
+    SXMC_CUDA(cudaEventSynchronize(e1));
+    SXMC_CUDA(cudaEventElapsedTime(&g_last_nll_ms, e0, e1));
+  }
+  double out[2];
+  SXMC_CUDA(cudaMemcpyAsync(out, &c->st_dev->last_nll, sizeof out, cudaMemcpyDeviceToHost, c->stream));
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  if (nll_out) *nll_out = out[0];
+  if (event_sum_out) *event_sum_out = out[1];
+  return SXMC_OK;
+}
+
+int sxmc_chain_get_norms(sxmc_chain* c, unsigned* norms_out) {
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  SXMC_CUDA(cudaMemcpy(norms_out, c->hist_buf[c->last_buf] + (size_t)c->nsignals * c->total_nbins,
+                       sizeof(unsigned) * c->nsignals, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+int sxmc_chain_get_lut(sxmc_chain* c, float* lut_out) {
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  SXMC_CUDA(cudaMemcpy(lut_out, c->lut_dev, sizeof(float) * c->nevents * c->nsignals, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+int sxmc_chain_get_bins(sxmc_chain* c, unsigned* bins_out) {
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  SXMC_CUDA(cudaMemcpy(bins_out, c->hist_buf[c->last_buf], sizeof(unsigned) * (size_t)c->nsignals * c->total_nbins,
+                       cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// multi-GPU
+// ---------------------------------------------------------------------------------------
+int sxmc_comm_unique_id(void* id128_out) {
+  SXMC_TRY(load_nccl());
+  nccl_unique_id id;
+  int rc = g_nccl.GetUniqueId(&id);
+  if (rc) return nccl_fail(rc, "ncclGetUniqueId");
+  memcpy(id128_out, &id, sizeof id);
+  return SXMC_OK;
+}
+int sxmc_comm_create(const void* id128, int nranks, int rank, sxmc_comm** out) {
+  SXMC_TRY(ensure_init());
+  SXMC_TRY(load_nccl());
+  nccl_unique_id id;
+  memcpy(&id, id128, sizeof id);
+  sxmc_comm* c = new sxmc_comm;
+  c->nranks = nranks; c->rank = rank;
+  int rc = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+  if (rc) { delete c; return nccl_fail(rc, "ncclCommInitRank"); }
+  *out = c;
+  return SXMC_OK;
+}
+int sxmc_comm_destroy(sxmc_comm* comm) {
+  if (!comm) return SXMC_OK;
+  if (comm->comm) g_nccl.CommDestroy(comm->comm);
+  delete comm;
+  return SXMC_OK;
+}
+int sxmc_comm_allreduce_u32(sxmc_comm* comm, unsigned* dev, size_t count) {
+  int rc = g_nccl.AllReduce(dev, dev, count, NCCL_UINT32, NCCL_SUM, comm->comm, 0);
+  if (rc) return nccl_fail(rc, "ncclAllReduce");
+  SXMC_CUDA(cudaStreamSynchronize(0));
+  return SXMC_OK;
+}
+
+}  // extern "C"

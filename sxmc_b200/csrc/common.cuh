@@ -1,0 +1,115 @@
+// common.cuh -- shared device-side structures of libsxmc_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+
+#include "../../include/sxmc_b200.h"
+
+namespace sxmc {
+
+// ---- sample layout -------------------------------------------------------------------
+// Samples of one PDF are stored as one float column per field (SoA).  Within a column,
+// samples are grouped in warp-tiles of WT_SAMPLES = 32 lanes x LANE_RUN samples.  In the
+// (bin-sorted) sample order, lane l of a warp-tile owns the LANE_RUN *consecutive* samples
+// [l*LANE_RUN, (l+1)*LANE_RUN); in memory the tile is LANE_RUN/4 rows of 32 float4, row q
+// holding samples 4q..4q+3 of every lane, so that one LDG.128 per lane reads 512
+// contiguous bytes per warp while each thread walks a sorted run (its bin changes rarely,
+// which is what makes the per-thread run-length aggregation of the histogram updates work).
+constexpr int LANE_RUN = 32;
+constexpr int WT_SAMPLES = 32 * LANE_RUN;       // 1024 samples per warp-tile
+constexpr int WT_ROWS = LANE_RUN / 4;           // float4 rows per warp-tile
+constexpr int BIN_THREADS = 256;
+constexpr int BIN_WARPS = BIN_THREADS / 32;     // warp-tiles per block-tile
+
+constexpr int MAX_SLOTS = 6;                    // columns the fast kernel keeps in registers
+
+struct SystDesc {
+  short type;        // SXMC_SYST_*
+  short obs;         // FIELD index of the observable it moves
+  short extra;       // FIELD index of the truth value (RESOLUTION_SCALE)
+  short npars;
+  short pidx[SXMC_MAX_NPARS];   // global coefficient indices
+  short obs_slot;    // register slot of obs / extra in the fast kernel
+  short extra_slot;
+};
+
+// One PDF's binning work.  Lives in device memory; read with uniform loads.
+struct BinJob {
+  const float* cols[SXMC_MAX_NFIELDS];   // per FIELD column (tiled layout), nwtiles*1024 floats
+  unsigned long long nwtiles;            // warp-tiles (samples padded with +inf observables)
+  unsigned* bins;                        // [total_nbins] global histogram
+  unsigned* norm;                        // in-domain count slot
+  const double* params;                  // parameter buffer + offset
+  long long param_stride;
+  int total_nbins;
+  int nobs;
+  int nfields;
+  int nsyst;
+  int nslots;
+  int slot_field[MAX_SLOTS];             // register slot -> field index (observables first)
+  double lower[SXMC_MAX_NFIELDS];
+  double upper[SXMC_MAX_NFIELDS];
+  double scale[SXMC_MAX_NFIELDS];        // nbins / (upper - lower), src/pdfz.cpp:365-368
+  int stride[SXMC_MAX_NFIELDS];          // row-major strides, src/pdfz.cpp:206-213
+  SystDesc syst[SXMC_MAX_SYST];
+};
+
+// One signal as seen by the lookup + event-likelihood kernel.
+struct NllSignal {
+  const unsigned* bins;       // histogram of this step
+  const unsigned* norm;       // its in-domain count
+  const int* read_bins;       // per event flat bin, -1 outside, -2 other dataset
+  double nexpected;
+  double bin_volume;
+  unsigned n_mc;
+  int total_nbins;
+  short source_id;
+};
+
+// Device-resident chain state (the hemi::Arrays of src/mcmc.cpp:159-232 in one struct).
+struct ChainState {
+  double current[SXMC_MAX_PARAMETERS];
+  double proposed[SXMC_MAX_PARAMETERS];
+  double means[SXMC_MAX_PARAMETERS];
+  double sigmas[SXMC_MAX_PARAMETERS];
+  float jump_width[SXMC_MAX_PARAMETERS];
+  int fixed[SXMC_MAX_PARAMETERS];
+  double stat_sx[SXMC_MAX_PARAMETERS];    // running sums over the rows since the last reset
+  double stat_sxx[SXMC_MAX_PARAMETERS];
+  double stat_n;
+  double current_nll;
+  double proposed_nll;
+  double event_total;                     // persistent event_total_sum (NaN keeps the old one)
+  float scale_factor;
+  int nparameters, nsources, nsignals;
+  int debug_mode;
+  unsigned step;                          // next step index i of the loop
+  unsigned burnin_steps;
+  long long nrows;                        // rows in the ntuple since the last Reset()
+  long long accepted;
+  unsigned long long seed, stream_id;
+  // tapes (test hook)
+  const double* tape_normals; unsigned long long n_normals, i_normal;
+  const double* tape_uniforms; unsigned long long n_uniforms, i_uniform;
+  // outputs
+  float* rows;                            // [row_cap][nparameters+1]
+  long long row_cap;
+  double* nll_trace;                      // optional [nsteps]
+  double* prop_trace;                     // optional [nsteps][nparameters]
+  double last_nll, last_event_sum;        // results of an evaluate-only pass
+};
+
+enum NllMode { NLL_MODE_STEP = 0, NLL_MODE_INIT = 1, NLL_MODE_EVAL_ONLY = 2 };
+
+// error plumbing --------------------------------------------------------------------------
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define SXMC_CUDA(expr)                                                       \
+  do {                                                                        \
+    cudaError_t _e = (expr);                                                  \
+    if (_e != cudaSuccess) return ::sxmc::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+}  // namespace sxmc

@@ -1,0 +1,72 @@
+// kernels.h -- host-callable launchers of the sm_100a kernels (internal to libsxmc_b200).
+#pragma once
+#include "common.cuh"
+
+namespace sxmc {
+
+struct PrepGeo {     // histogram geometry passed by value to the small preparation kernels
+  double lower[SXMC_MAX_NFIELDS], upper[SXMC_MAX_NFIELDS], scale[SXMC_MAX_NFIELDS];
+  int nbins[SXMC_MAX_NFIELDS], stride[SXMC_MAX_NFIELDS];
+  int total_nbins;
+};
+
+struct BinLaunch {
+  const BinJob* jobs_dev;
+  const unsigned long long* prefix_dev;   // [njobs+1] block-tile prefix sums
+  int njobs;
+  unsigned long long total_btiles;
+  bool fast;                 // register-resident kernel (uniform geometry, nobs<=3)
+  bool smem_hist;            // shared-memory privatised histograms
+  int nobs, nslots;
+  int max_total_nbins;
+  int blocks_per_sm;         // <=0: occupancy maximum
+  double lower[3], upper[3], scale[3];
+  int stride[3];
+};
+
+struct EvalPdfJob {
+  const int* read_bins;
+  const unsigned* bins;
+  const unsigned* norm;
+  float* out;                // pdf buffer + offset
+  long long stride;
+  long long npoints;
+  double bin_volume;
+  int total_nbins;
+};
+
+bool bin_fast_supported(int nobs, int nslots);
+int launch_bin(const BinLaunch& L, cudaStream_t stream);
+int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,
+                   const PrepGeo& g, int primary, bool sort, float* cols_dev,
+                   unsigned long long col_pitch, unsigned* perm_dev, cudaStream_t stream);
+int unprepare_to_aos(const float* cols_dev, unsigned long long col_pitch, const unsigned* perm_dev,
+                     unsigned long long n, int nfields, float* aos_dev, cudaStream_t stream);
+int launch_read_bins(const float* points_dev, long long npoints, int nobs, const PrepGeo& g,
+                     unsigned dataset, int* read_bins_dev, cudaStream_t stream);
+int launch_eval_pdf(const EvalPdfJob* jobs_dev, int njobs, long long max_points, cudaStream_t stream);
+
+// ---- nll_kernels.cu ----
+struct NllLaunch {
+  const NllSignal* sigs_dev;
+  int nsignals;
+  long long nevents;
+  ChainState* state;            // device
+  double* partials;             // [grid] device
+  unsigned* ticket;             // device, zero before first use (self-resetting)
+  int mode;                     // NllMode
+  float* lut;                   // optional materialised lut [nsignals][nevents] (signal-major)
+  unsigned* zero_ptr;           // optional buffer to clear for the next step
+  unsigned long long zero_words;
+  int grid;                     // fixed for the life of a chain (deterministic summation order)
+};
+int nll_grid_for(long long nevents);
+int launch_nll(const NllLaunch& L, cudaStream_t stream);
+
+// standalone MCMC::nll over a materialised lut (src/mcmc.cpp:390-415)
+int launch_nll_lut(const float* lut, size_t ne, size_t ns, const double* pars, size_t npars,
+                   size_t nsources, const double* means, const double* sigmas,
+                   const double* nexpected, const unsigned* n_mc, const short* source_id,
+                   const unsigned* norms, double* out2_dev, cudaStream_t stream);
+
+}  // namespace sxmc

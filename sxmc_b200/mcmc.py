@@ -1,0 +1,230 @@
+"""Host-side mirror of the reference's ``MCMC`` and ``LikelihoodSpace`` classes
+(src/mcmc.h:36-138, src/likelihood.h:25-100) over the C ABI, plus the plain-data
+``Source`` / ``Signal`` / ``Systematic`` / ``Observable`` structs MCMC's constructor takes
+(src/source.h:23-57, src/signal.h:29-72, src/systematic.h:26-48, src/observable.h:24-41).
+
+The whole chain runs device-resident inside libsxmc_b200.so."""
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import List
+
+import numpy as np
+
+from . import pdfz
+from ._lib import ChainConfig, c_dp, c_fp, c_ip, c_sp, c_up, c_vp, lib, ptr
+from .pdfz import _check
+
+
+@dataclass
+class Source:
+    name: str = ""
+    index: int = 0
+    mean: float = 0.0
+    sigma: float = 0.0
+    fixed: bool = False
+
+
+@dataclass
+class Systematic:
+    name: str = ""
+    npars: int = 1
+    means: List[float] = field(default_factory=lambda: [0.0])
+    sigmas: List[float] = field(default_factory=lambda: [0.0])
+    fixed: bool = False
+
+
+@dataclass
+class Observable:
+    name: str = ""
+
+
+@dataclass
+class Signal:
+    name: str = ""
+    histogram: pdfz.EvalHist = None
+    nexpected: float = 0.0
+    n_mc: int = 0
+    source: Source = None
+
+
+class LikelihoodSpace:
+    """Holds the chain ntuple: rows of nparameters+1 floats, last = NLL (src/likelihood.h:30).
+    Post-processing (error estimators) is out of scope for the hot path."""
+
+    def __init__(self, samples, names):
+        self.samples = samples
+        self.names = names
+
+    def get_samples(self):
+        return self.samples
+
+    def get_best_fit(self):
+        """Parameters of the minimum-NLL row (src/likelihood.cpp:46-72, without the errors)."""
+        i = int(np.argmin(self.samples[:, -1]))
+        return dict(zip(self.names[:-1], self.samples[i, :-1])), float(self.samples[i, -1])
+
+
+class MCMC:
+    """MCMC(sources, signals, systematics, observables) (src/mcmc.cpp:28-130)."""
+
+    def __init__(self, sources, signals, systematics, observables):
+        self.nsources, self.nsignals = len(sources), len(signals)
+        self.nsystematics, self.nobservables = len(systematics), len(observables)
+        means, sigmas, fixed = [], [], []
+        for s in sources:
+            # Source.mean / sigma are float members (src/source.h:55-56)
+            means.append(float(np.float32(s.mean)))
+            sigmas.append(float(np.float32(s.sigma)))
+            fixed.append(bool(s.fixed))
+        self.systematics_fixed = True
+        self.parameter_names = [s.name for s in sources]
+        for y in systematics:
+            if not y.fixed:
+                self.systematics_fixed = False
+            for j in range(y.npars):
+                means.append(float(y.means[j]))
+                sigmas.append(float(y.sigmas[j]))
+                fixed.append(bool(y.fixed))
+                self.parameter_names.append("%s_%d" % (y.name, j))
+        self.parameter_names.append("likelihood")
+        self.nparameters = len(means)
+        self._means = np.asarray(means, dtype=np.float64)
+        self._sigmas = np.asarray(sigmas, dtype=np.float64)
+        self._fixed = np.asarray(fixed, dtype=np.int32)
+        self._nexp = np.asarray([s.nexpected for s in signals], dtype=np.float64)
+        self._n_mc = np.asarray([s.n_mc for s in signals], dtype=np.uint32)
+        self._sid = np.asarray([s.source.index for s in signals], dtype=np.int16)
+        self._pdfs = [s.histogram for s in signals]
+        self._harr = (c_vp * self.nsignals)(*[h._h for h in self._pdfs])
+        cfg = ChainConfig(self.nsources, self.nsignals, self.nparameters, self.nobservables,
+                          ptr(self._means, c_dp), ptr(self._sigmas, c_dp), ptr(self._fixed, c_ip),
+                          int(self.systematics_fixed), self.nsystematics, self._harr,
+                          ptr(self._nexp, c_dp), ptr(self._n_mc, c_up), ptr(self._sid, c_sp))
+        self._c = c_vp()
+        _check(lib().sxmc_chain_create(C.byref(cfg), C.byref(self._c)))
+        self.nrows = 0
+
+    def close(self):
+        if self._c:
+            lib().sxmc_chain_destroy(self._c)
+            self._c = c_vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- configuration that has no reference counterpart (RNG is gRandom there)
+    def set_seed(self, seed, stream_id=0):
+        _check(lib().sxmc_chain_set_seed(self._c, int(seed), int(stream_id)))
+
+    def set_tapes(self, normals, uniforms):
+        if normals is None:
+            _check(lib().sxmc_chain_set_tapes(self._c, None, 0, None, 0))
+            return
+        n = np.ascontiguousarray(normals, dtype=np.float64)
+        u = np.ascontiguousarray(uniforms, dtype=np.float64)
+        _check(lib().sxmc_chain_set_tapes(self._c, ptr(n, c_dp), n.size, ptr(u, c_dp), u.size))
+
+    def set_mode(self, mode):
+        _check(lib().sxmc_chain_set_mode(self._c, int(mode)))
+
+    def set_comm(self, comm):
+        _check(lib().sxmc_chain_set_comm(self._c, comm))
+
+    def enable_trace(self, on=True):
+        _check(lib().sxmc_chain_enable_trace(self._c, int(on)))
+
+    # -- MCMC::operator() (src/mcmc.cpp:143-387)
+    def __call__(self, data, nsteps, burnin_fraction, debug_mode=False, sync_interval=10000):
+        d = np.ascontiguousarray(data, dtype=np.float32).ravel()
+        dd = d if d.size else np.zeros(1, np.float32)
+        nrows = C.c_long(0)
+        _check(lib().sxmc_chain_run(self._c, ptr(dd, c_fp), d.size, int(nsteps),
+                                    float(burnin_fraction), int(debug_mode), int(sync_interval),
+                                    C.byref(nrows)))
+        self.nrows = nrows.value
+        rows = np.zeros((max(1, self.nrows), self.nparameters + 1), dtype=np.float32)
+        _check(lib().sxmc_chain_read(self._c, ptr(rows, c_fp), rows.shape[0]))
+        return LikelihoodSpace(rows[:self.nrows], self.parameter_names)
+
+    def accepted(self):
+        v = C.c_long(0)
+        _check(lib().sxmc_chain_accepted(self._c, C.byref(v)))
+        return v.value
+
+    def loop_ms(self):
+        v = C.c_float(0)
+        _check(lib().sxmc_chain_loop_ms(self._c, C.byref(v)))
+        return v.value
+
+    def launches(self):
+        v = C.c_long(0)
+        _check(lib().sxmc_chain_launches(self._c, C.byref(v)))
+        return v.value
+
+    def read_trace(self, nsteps):
+        nll = np.zeros(max(1, nsteps), dtype=np.float64)
+        prop = np.zeros((max(1, nsteps), self.nparameters), dtype=np.float64)
+        _check(lib().sxmc_chain_read_trace(self._c, ptr(nll, c_dp), ptr(prop, c_dp), int(nsteps)))
+        return nll[:nsteps], prop[:nsteps]
+
+    # -- MCMC::nll (src/mcmc.cpp:390-415) at a host parameter vector, PDFs re-evaluated
+    def set_data(self, data):
+        d = np.ascontiguousarray(data, dtype=np.float32).ravel()
+        dd = d if d.size else np.zeros(1, np.float32)
+        _check(lib().sxmc_chain_set_data(self._c, ptr(dd, c_fp), d.size))
+        self._nevents = d.size // (self.nobservables + 1)
+
+    def nll(self, pars, rebin=True):
+        p = np.ascontiguousarray(pars, dtype=np.float64)
+        v, ev = C.c_double(0), C.c_double(0)
+        _check(lib().sxmc_chain_nll_at(self._c, ptr(p, c_dp), int(rebin), C.byref(v), C.byref(ev)))
+        return v.value, ev.value
+
+    def norms(self):
+        out = np.zeros(self.nsignals, dtype=np.uint32)
+        _check(lib().sxmc_chain_get_norms(self._c, ptr(out, c_up)))
+        return out
+
+    def lut(self):
+        out = np.zeros((self.nsignals, max(1, self._nevents)), dtype=np.float32)
+        _check(lib().sxmc_chain_get_lut(self._c, ptr(out, c_fp)))
+        return out[:, :self._nevents]
+
+    def bins(self):
+        tn = self._pdfs[0].TotalBins()
+        out = np.zeros((self.nsignals, tn), dtype=np.uint32)
+        _check(lib().sxmc_chain_get_bins(self._c, ptr(out, c_up)))
+        return out
+
+
+def build_fit(fit, sort=True):
+    """FitSpec (sxmc_b200.workloads) -> (hists, MCMC), the way src/signal.cpp:112-169 and
+    src/sxmc.cpp:96 wire the reference objects."""
+    hists = []
+    for sig in fit.signals:
+        h = pdfz.EvalHist(sig.samples, sig.samples.shape[1], fit.nobs, fit.lower, fit.upper,
+                          fit.nbins, sig.dataset)
+        if not sort:
+            h.SetLayout(False)
+        for i in sig.systematics:
+            y = fit.systematics[i]
+            if y.type == pdfz.SHIFT:
+                h.AddSystematic(pdfz.ShiftSystematic(y.obs, y.pidx))
+            elif y.type == pdfz.SCALE:
+                h.AddSystematic(pdfz.ScaleSystematic(y.obs, y.pidx))
+            elif y.type == pdfz.CTSCALE:
+                h.AddSystematic(pdfz.CosThetaScaleSystematic(y.obs, y.pidx))
+            else:
+                h.AddSystematic(pdfz.ResolutionScaleSystematic(y.obs, y.extra, y.pidx))
+        hists.append(h)
+    sources = [Source("s%d" % i, i, fit.source_means[i], fit.source_sigmas[i], fit.source_fixed[i])
+               for i in range(fit.nsources)]
+    systs = [Systematic("y%d" % i, y.npars, list(y.means), list(y.sigmas), y.fixed)
+             for i, y in enumerate(fit.systematics)]
+    signals = [Signal("sig%d" % j, hists[j], sig.nexpected, sig.n_mc, sources[sig.source])
+               for j, sig in enumerate(fit.signals)]
+    mc = MCMC(sources, signals, systs, [Observable("o%d" % i) for i in range(fit.nobs)])
+    return hists, mc

@@ -1,0 +1,377 @@
+"""Parity tests proper: the CUDA path (through the C ABI) against the CPU oracle, the
+reference's gtest golden vectors and the committed reference fixtures.  Integer work
+(bins, norms, read_bins) and the float lut are compared bit-exactly; NLL within 1e-6
+relative (the tolerance BASELINE.json's north_star states)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import port
+from sxmc_b200 import workloads as W
+from tests import golden_vectors as G
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+NLL_RTOL = 1e-6   # north_star: 1e-6 on NLL per step
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _env(oracle_built):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from sxmc_b200 import _lib
+    _lib.check(_lib.lib().sxmc_init(0))
+    yield
+    from sxmc_b200 import pdfz
+    pdfz.set_bin_tuning(8192, 0, False)
+
+
+def _pars(fit, seed):
+    rng = np.random.default_rng(seed)
+    p = fit.parameter_means().copy()
+    p[:fit.nsources] = rng.uniform(0.5, 1.5, fit.nsources)
+    sig = fit.parameter_sigmas()
+    p[fit.nsources:] += rng.normal(0, 1, fit.nparameters - fit.nsources) * 3 * sig[fit.nsources:]
+    return p
+
+
+def _gpu_eval_api(fit, pars):
+    """Through the pdfz::EvalHist mirror, one PDF at a time (EvalAsync/EvalFinished)."""
+    from sxmc_b200 import pdfz
+    ns, ne = fit.nsignals, fit.nevents
+    params = pdfz.Array.from_host(pars, np.float64)
+    norms = pdfz.Array(ns, np.uint32)
+    lut = pdfz.Array(ns * ne, np.float32)
+    bins = []
+    for j, sig in enumerate(fit.signals):
+        h = pdfz.EvalHist(sig.samples, sig.samples.shape[1], fit.nobs, fit.lower, fit.upper,
+                          fit.nbins, sig.dataset)
+        for i in sig.systematics:
+            y = fit.systematics[i]
+            cls = {pdfz.SHIFT: pdfz.ShiftSystematic, pdfz.SCALE: pdfz.ScaleSystematic,
+                   pdfz.CTSCALE: pdfz.CosThetaScaleSystematic}.get(y.type)
+            pars_arr = pdfz.Array.from_host(y.pidx, np.int16)
+            if cls is None:
+                h.AddSystematic(pdfz.ResolutionScaleSystematic(y.obs, y.extra, pars_arr))
+            else:
+                h.AddSystematic(cls(y.obs, pars_arr))
+        h.SetEvalPoints(fit.data)
+        h.SetPDFValueBuffer(lut, j * ne, 1)
+        h.SetNormalizationBuffer(norms, j)
+        h.SetParameterBuffer(params, fit.nsources)
+        h.EvalAsync()
+        h.EvalFinished()
+        bins.append(h.Bins())
+        h.close()
+    return (np.stack(bins), norms.readOnlyHostPtr().copy(),
+            lut.readOnlyHostPtr().reshape(ns, ne).copy())
+
+
+# ---------------------------------------------------------------------------------------
+# the reference's own gtest vectors (test/test_pdfz*.cpp), through the EvalHist mirror
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", G.CASES, ids=[c[0] for c in G.CASES])
+def test_reference_gtest_vectors(case):
+    name, samples, geom, evalp, syst, value, norm, expect = case
+    fit = G.case_fit(samples, geom, evalp, syst, value)
+    pars = np.array([1.0] + ([value] if syst else []))
+    bins, norms, lut = _gpu_eval_api(fit, pars)
+    assert int(norms[0]) == norm
+    assert int(bins.sum()) == norm
+    G.check_pdf_values(lut[0], expect)
+
+
+def test_offset_stride_vector():
+    """test/test_pdfz.cpp:98-126: sentinel values around the written slots survive."""
+    from sxmc_b200 import pdfz
+    o = G.OFFSET_STRIDE
+    h = pdfz.EvalHist(G.SAMPLES_1D, 1, 1, [0.0], [1.0], [2])
+    h.SetEvalPoints(G.EVAL_1D)
+    pdf = pdfz.Array.from_host(np.full(20, -55.0, np.float32), np.float32)
+    norm = pdfz.Array.from_host(o["norm_init"], np.uint32)
+    params = pdfz.Array.from_host([1.0], np.float64)
+    h.SetPDFValueBuffer(pdf, o["pdf_offset"], o["pdf_stride"])
+    h.SetNormalizationBuffer(norm, o["norm_offset"])
+    h.SetParameterBuffer(params)
+    h.EvalAsync()
+    h.EvalFinished()
+    assert list(norm.readOnlyHostPtr()) == o["norm_expect"]
+    got = pdf.readOnlyHostPtr()
+    for i in range(20):
+        if i in o["pdf_expect"]:
+            e = o["pdf_expect"][i]
+            assert np.isnan(got[i]) if e is None else G.float_eq_4ulp(got[i], e)
+        else:
+            assert got[i] == -55.0
+    h.close()
+
+
+def test_eval_without_points_and_get_samples():
+    from sxmc_b200 import pdfz
+    fit = W.config_C(0.0005)
+    sig = fit.signals[3]
+    h = pdfz.EvalHist(sig.samples, sig.samples.shape[1], fit.nobs, fit.lower, fit.upper, fit.nbins)
+    h.AddSystematic(pdfz.ScaleSystematic(0, [0]))
+    norm = pdfz.Array(1, np.uint32)
+    params = pdfz.Array.from_host([0.02], np.float64)
+    h.SetNormalizationBuffer(norm, 0)
+    h.SetParameterBuffer(params, 0)
+    h.EvalAsync(False)       # src/pdfz.cpp:474: no eval points, histogram only
+    h.EvalFinished()
+    want_bins, want_norm = port.bin_signal(W.FitSpec(
+        name="x", lower=fit.lower, upper=fit.upper, nbins=fit.nbins, source_means=[1.0],
+        source_sigmas=[0.0], source_fixed=[False],
+        systematics=[W.SystSpec(type=W.SCALE, obs=0)],
+        signals=[W.SignalSpec(samples=sig.samples, nexpected=1.0, source=0)],
+        data=np.zeros((0, fit.nobs + 1), np.float32)), 0, [0.02])
+    assert np.array_equal(h.Bins(), want_bins) and int(norm.readOnlyHostPtr()[0]) == want_norm
+    # GetSamples returns the caller's rows in the caller's order although the device
+    # layout is bin-sorted and tiled
+    assert h.GetSamples().tobytes() == sig.samples.tobytes()
+    h.close()
+
+
+# ---------------------------------------------------------------------------------------
+# workloads A-D (scaled), CUDA vs oracle, several kernel configurations
+# ---------------------------------------------------------------------------------------
+SMALL = [("A", 0.01), ("B", 0.02), ("C", 0.002), ("D", 0.003)]
+VARIANTS = [("smem", dict(smem_hist_max_bins=56 * 1024)), ("global", dict(smem_hist_max_bins=0)),
+            ("generic", dict(force_generic=True)), ("generic_global", dict(force_generic=True, smem_hist_max_bins=0))]
+
+
+@pytest.mark.parametrize("variant", VARIANTS, ids=[v[0] for v in VARIANTS])
+@pytest.mark.parametrize("name,scale", SMALL, ids=[s[0] for s in SMALL])
+def test_chain_eval_matches_oracle(name, scale, variant):
+    from sxmc_b200 import mcmc, pdfz
+    pdfz.set_bin_tuning(**dict(dict(smem_hist_max_bins=8192, blocks_per_sm=0, force_generic=False),
+                               **variant[1]))
+    fit = W.WORKLOADS[name](scale)
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_data(fit.data)
+    for seed in (1, 2, 3):
+        pars = _pars(fit, seed)
+        nll, ev = chain.nll(pars)
+        bins, norms, lut = port.eval_all(fit, pars)
+        want, want_ev = port.nll(fit, lut, pars, norms)
+        assert np.array_equal(chain.bins(), bins)
+        assert np.array_equal(chain.norms(), norms)
+        assert chain.lut().tobytes() == lut.tobytes()
+        assert abs(ev - want_ev) <= NLL_RTOL * abs(want_ev)
+        assert abs(nll - want) <= NLL_RTOL * abs(want)
+    pdfz.set_bin_tuning(8192, 0, False)
+
+
+def test_unsorted_layout_gives_identical_histograms():
+    from sxmc_b200 import mcmc
+    fit = W.config_C(0.003)
+    pars = _pars(fit, 5)
+    out = []
+    for sort in (True, False):
+        hists, chain = mcmc.build_fit(fit, sort=sort)
+        chain.set_data(fit.data)
+        chain.nll(pars)
+        out.append((chain.bins(), chain.norms()))
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+
+
+def test_api_path_matches_oracle_and_read_bins():
+    from sxmc_b200 import pdfz
+    fit = W.config_D(0.002)
+    pars = _pars(fit, 9)
+    bins, norms, lut = _gpu_eval_api(fit, pars)
+    b0, n0, l0 = port.eval_all(fit, pars)
+    assert np.array_equal(bins, b0) and np.array_equal(norms, n0) and lut.tobytes() == l0.tobytes()
+    sig = fit.signals[0]
+    h = pdfz.EvalHist(sig.samples, sig.samples.shape[1], fit.nobs, fit.lower, fit.upper, fit.nbins, 0)
+    # edge rows: outside the domain, other dataset, exactly on the bounds
+    extra = np.array([[4.99, 1.0, 0.0, 0], [15.0, 1.0, 0.0, 0], [5.0, 0.0, -1.0, 0],
+                      [7.0, 3.0, 0.5, 1], [20.0, 3.0, 0.5, 1]], dtype=np.float32)
+    pts = np.concatenate([fit.data[:1000], extra])
+    h.SetEvalPoints(pts)
+    assert np.array_equal(h.ReadBins(), port.read_bins(fit, 0, pts))
+    h.close()
+
+
+def test_committed_reference_fixtures():
+    """Against outputs of the UNMODIFIED reference (tests/golden/make_ref_fixtures.py)."""
+    from sxmc_b200 import mcmc
+    z = np.load(os.path.join(HERE, "golden", "ref_fixtures.npz"))
+    for name, scale in SMALL:
+        fit = W.WORKLOADS[name](scale)
+        hists, chain = mcmc.build_fit(fit)
+        chain.set_data(fit.data)
+        pars = z[name + "_pars"]
+        nll, ev = chain.nll(pars)
+        assert np.array_equal(chain.bins(), z[name + "_bins"])
+        assert np.array_equal(chain.norms(), z[name + "_norms"])
+        assert chain.lut().tobytes() == z[name + "_lut"].tobytes()
+        assert abs(nll - float(z[name + "_nll"])) <= NLL_RTOL * abs(float(z[name + "_nll"]))
+        assert abs(ev - float(z[name + "_evsum"])) <= NLL_RTOL * abs(float(z[name + "_evsum"]))
+
+
+def test_polynomial_and_ctscale_systematics():
+    """Multi-coefficient series (p = sum p_i x^i, src/pdfz.cpp:310-314) and ctscale."""
+    from sxmc_b200 import mcmc
+    base = W.config_D(0.002)
+    systs = [W.SystSpec(type=W.SHIFT, obs=0, means=[0.01, 0.002], sigmas=[0.01, 0.001]),
+             W.SystSpec(type=W.SCALE, obs=0, means=[0.0, 0.001, 0.0001], sigmas=[0.01, 0.001, 0.0001]),
+             W.SystSpec(type=W.CTSCALE, obs=2, means=[0.01], sigmas=[0.01]),
+             W.SystSpec(type=W.RESOLUTION_SCALE, obs=0, extra=3, means=[0.02], sigmas=[0.01])]
+    fit = W.FitSpec(name="poly", lower=base.lower, upper=base.upper, nbins=base.nbins,
+                    source_means=base.source_means[:4], source_sigmas=base.source_sigmas[:4],
+                    source_fixed=base.source_fixed[:4], systematics=systs,
+                    signals=[W.SignalSpec(samples=s.samples, nexpected=s.nexpected, source=j)
+                             for j, s in enumerate(base.signals[:4])], data=base.data[:5000])
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_data(fit.data)
+    pars = fit.parameter_means().copy()
+    nll, ev = chain.nll(pars)
+    bins, norms, lut = port.eval_all(fit, pars)
+    want, _ = port.nll(fit, lut, pars, norms)
+    assert np.array_equal(chain.bins(), bins) and np.array_equal(chain.norms(), norms)
+    assert abs(nll - want) <= NLL_RTOL * abs(want)
+
+
+def test_empty_and_ragged_inputs():
+    from sxmc_b200 import mcmc
+    base = W.config_B(0.001)
+    sigs = [W.SignalSpec(samples=base.signals[0].samples[:0], nexpected=10.0, source=0, n_mc=5),
+            W.SignalSpec(samples=base.signals[1].samples[:1], nexpected=10.0, source=1),
+            W.SignalSpec(samples=base.signals[2].samples[:1025], nexpected=10.0, source=2)]
+    fit = W.FitSpec(name="ragged", lower=base.lower, upper=base.upper, nbins=base.nbins,
+                    source_means=[1.0] * 3, source_sigmas=[0.0] * 3, source_fixed=[False] * 3,
+                    systematics=base.systematics, signals=sigs, data=base.data[:7])
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_data(fit.data)
+    pars = fit.parameter_means().copy()
+    nll, ev = chain.nll(pars)
+    bins, norms, lut = port.eval_all(fit, pars)
+    want, want_ev = port.nll(fit, lut, pars, norms)
+    assert np.array_equal(chain.bins(), bins) and np.array_equal(chain.norms(), norms)
+    assert np.array_equal(np.isnan(chain.lut()), np.isnan(lut))   # empty PDF -> NaN values
+    assert (nll == want) or abs(nll - want) <= NLL_RTOL * abs(want)
+
+
+# ---------------------------------------------------------------------------------------
+# chains
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", [0, 1], ids=["graph", "stream"])
+def test_tape_driven_chain_matches_oracle_chain(mode):
+    """Same random numbers in => same accept/reject sequence and the same float rows out."""
+    from sxmc_b200 import mcmc
+    fit = W.config_B(0.005)
+    nsteps = 400
+    rng = np.random.default_rng(123)
+    normals = rng.normal(size=(nsteps + 1) * fit.nparameters)
+    uniforms = rng.random(nsteps)
+    want = port.mcmc(fit, nsteps, 0.1, normals, uniforms, trace=True)
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_mode(mode)
+    chain.set_tapes(normals, uniforms)
+    chain.enable_trace()
+    ls = chain(fit.data, nsteps, 0.1)
+    got = ls.get_samples()
+    nll_tr, prop_tr = chain.read_trace(nsteps)
+    assert got.shape == want["chain"].shape
+    assert chain.accepted() == want["accepted"]
+    assert np.array_equal(prop_tr, want["prop_trace"])          # proposals bit-identical
+    assert np.allclose(nll_tr, want["nll_trace"], rtol=NLL_RTOL, atol=0)
+    assert np.array_equal(got[:, :-1], want["chain"][:, :-1])
+    assert np.allclose(got[:, -1], want["chain"][:, -1], rtol=1e-6)
+    # and against the chain the UNMODIFIED reference produced from the same tape
+    z = np.load(os.path.join(HERE, "golden", "ref_fixtures.npz"))
+    assert np.array_equal(z["chainB_normals"], normals)
+    assert np.array_equal(got[:, :-1], z["chainB_chain"][:, :-1])
+
+
+def test_fixed_systematics_and_debug_mode_chain():
+    from sxmc_b200 import mcmc
+    fit = W.config_A(0.004)
+    for y in fit.systematics:
+        y.fixed = True
+    nsteps = 300
+    rng = np.random.default_rng(5)
+    normals = rng.normal(size=(nsteps + 1) * fit.nparameters)
+    uniforms = rng.random(nsteps)
+    for debug in (False, True):
+        want = port.mcmc(fit, nsteps, 0.2, normals, uniforms, debug_mode=debug)
+        hists, chain = mcmc.build_fit(fit)
+        chain.set_tapes(normals, uniforms)
+        got = chain(fit.data, nsteps, 0.2, debug_mode=debug).get_samples()
+        assert got.shape == want["chain"].shape
+        assert np.array_equal(got[:, :-1], want["chain"][:, :-1])
+
+
+def test_philox_chain_posterior_agrees_with_oracle_chain():
+    """RNG streams differ by construction (TRandom vs Philox): compare posteriors.  Quantiles
+    must agree within Monte-Carlo error (here: 5 x the batch-means standard error)."""
+    from sxmc_b200 import mcmc
+    fit = W.config_B(0.01)
+    nsteps = 20000
+    rng = np.random.default_rng(99)
+    want = port.mcmc(fit, nsteps, 0.1, rng.normal(size=(nsteps + 1) * fit.nparameters),
+                     rng.random(nsteps))["chain"]
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_seed(2024, 0)
+    got = chain(fit.data, nsteps, 0.1).get_samples()
+    assert got.shape == want.shape
+    acc = chain.accepted() / nsteps
+    assert 0.05 < acc < 0.9
+
+    def batch_se(x, q, nb=20):
+        parts = np.array_split(x, nb)
+        return np.std([np.quantile(p, q) for p in parts]) / np.sqrt(nb)
+
+    for k in range(fit.nparameters):
+        for q in (0.16, 0.5, 0.84):
+            se = np.hypot(batch_se(got[:, k], q), batch_se(want[:, k], q))
+            assert abs(np.quantile(got[:, k], q) - np.quantile(want[:, k], q)) <= 5 * se + 1e-9, (k, q)
+    # two seeds give different chains; the same seed reproduces bit-identically
+    chain.set_seed(2024, 0)
+    again = chain(fit.data, 2000, 0.1).get_samples()
+    chain.set_seed(2024, 0)
+    again2 = chain(fit.data, 2000, 0.1).get_samples()
+    chain.set_seed(2025, 0)
+    other = chain(fit.data, 2000, 0.1).get_samples()
+    assert again.tobytes() == again2.tobytes() and again.tobytes() != other.tobytes()
+
+
+# ---------------------------------------------------------------------------------------
+# full-size properties (BASELINE.json sizes; the oracle still finishes in seconds for B)
+# ---------------------------------------------------------------------------------------
+def test_full_size_config_B_bit_exact_and_properties():
+    from sxmc_b200 import mcmc
+    fit = W.config_B(1.0)
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_data(fit.data)
+    pars = _pars(fit, 21)
+    nll, ev = chain.nll(pars)
+    bins, norms, lut = port.eval_all(fit, pars)
+    want, _ = port.nll(fit, lut, pars, norms)
+    assert np.array_equal(chain.bins(), bins) and np.array_equal(chain.norms(), norms)
+    assert chain.lut().tobytes() == lut.tobytes()
+    assert abs(nll - want) <= NLL_RTOL * abs(want)
+    # size-independent properties: counts conserve, a huge shift empties the histogram
+    b = chain.bins()
+    assert np.array_equal(b.sum(axis=1), chain.norms())
+    assert np.all(chain.norms() <= [s.n_mc for s in fit.signals])
+    far = pars.copy()
+    far[fit.nsources] = 1e6
+    chain.nll(far)
+    assert chain.bins().sum() == 0 and chain.norms().sum() == 0
+
+
+def test_config_C_tenth_scale_bit_exact():
+    from sxmc_b200 import mcmc
+    fit = W.config_C(0.1)      # 10 x 1M samples, 5000 bins, scale + resolution_scale
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_data(fit.data)
+    pars = _pars(fit, 22)
+    nll, ev = chain.nll(pars)
+    bins, norms, lut = port.eval_all(fit, pars)
+    want, _ = port.nll(fit, lut, pars, norms)
+    assert np.array_equal(chain.bins(), bins) and np.array_equal(chain.norms(), norms)
+    assert abs(nll - want) <= NLL_RTOL * abs(want)
