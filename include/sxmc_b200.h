@@ -164,6 +164,20 @@ int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm);
 int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
                    float burnin_fraction, int debug_mode, unsigned sync_interval,
                    long* nrows_out);
+/* The same call in three parts, so that a caller (bench.py, an ensemble driver) can keep a
+ * chain resident and advance it in segments:  begin = src/mcmc.cpp:143-258 (buffers, initial
+ * widths, SetEvalPoints, initial evaluation and NLL, first proposal; `nsteps` is the total the
+ * segments will add up to -- it fixes the burn-in points);  advance = `nsteps` iterations of
+ * the loop at :261-378;  end = the final drain (:351-377) that makes rows/accepted readable. */
+int sxmc_chain_begin(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
+                     float burnin_fraction, int debug_mode);
+int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps);
+int sxmc_chain_end(sxmc_chain* c, long* nrows_out);
+/* Measurement variant of advance: plain stream launches with a CUDA event around every kernel
+ * and, when flush_bytes > 0, an L2 flush (memset of flush_bytes) before every step, outside
+ * the timed intervals.  Outputs are sums over the nsteps steps, in ms. */
+int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
+                             float* step_ms_sum, float* bin_ms_sum, float* nll_ms_sum);
 /* the ntuple rows: nparameters+1 floats each (src/nll_kernels.cpp:78-84) */
 int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows);
 int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out);

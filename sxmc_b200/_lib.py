@@ -83,6 +83,10 @@ SYMBOLS = {
     "sxmc_chain_set_comm": (C.c_int, [c_vp, c_vp]),
     "sxmc_chain_run": (C.c_int, [c_vp, c_fp, _SIZE, C.c_uint, C.c_float, C.c_int, C.c_uint,
                                  C.POINTER(C.c_long)]),
+    "sxmc_chain_begin": (C.c_int, [c_vp, c_fp, _SIZE, C.c_uint, C.c_float, C.c_int]),
+    "sxmc_chain_advance": (C.c_int, [c_vp, C.c_uint]),
+    "sxmc_chain_end": (C.c_int, [c_vp, C.POINTER(C.c_long)]),
+    "sxmc_chain_advance_timed": (C.c_int, [c_vp, C.c_uint, _SIZE, c_fp, c_fp, c_fp]),
     "sxmc_chain_read": (C.c_int, [c_vp, c_fp, C.c_long]),
     "sxmc_chain_accepted": (C.c_int, [c_vp, C.POINTER(C.c_long)]),
     "sxmc_chain_loop_ms": (C.c_int, [c_vp, c_fp]),

@@ -653,9 +653,18 @@ struct sxmc_chain {
   long launches = 0;
   long long nrows = 0, accepted = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  unsigned steps_done = 0, steps_planned = 0;
+  cudaGraphExec_t graph_exec = nullptr;   // GRAPH_STEPS steps; rebuilt when the tables change
+  long graph_launches = 0;
+  void* flush_buf = nullptr; size_t flush_bytes = 0;
+  std::vector<cudaEvent_t> tev;
 };
 
 namespace sxmc {
+
+static void chain_drop_graph(sxmc_chain* c) {
+  if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+}
 
 static int chain_build_tables(sxmc_chain* c) {
   const int ns = c->nsignals;
@@ -831,6 +840,9 @@ int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out) {
 int sxmc_chain_destroy(sxmc_chain* c) {
   if (!c) return SXMC_OK;
   if (c->stream) cudaStreamSynchronize(c->stream);
+  chain_drop_graph(c);
+  cudaFree(c->flush_buf);
+  for (auto& e : c->tev) cudaEventDestroy(e);
   cudaFree(c->st_dev);
   if (c->st_host) cudaFreeHost(c->st_host);
   for (int b = 0; b < 2; ++b) { cudaFree(c->hist_buf[b]); cudaFree(c->sigs_dev[b]); c->batch[b].release(); }
@@ -861,7 +873,7 @@ int sxmc_chain_set_tapes(sxmc_chain* c, const double* normals, size_t n_normals,
   return SXMC_OK;
 }
 
-int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm) { c->comm = comm; return SXMC_OK; }
+int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm) { chain_drop_graph(c); c->comm = comm; return SXMC_OK; }
 int sxmc_chain_set_mode(sxmc_chain* c, int mode) { c->mode = mode; return SXMC_OK; }
 int sxmc_chain_enable_trace(sxmc_chain* c, int on) { c->trace = on != 0; return SXMC_OK; }
 
@@ -869,6 +881,7 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
   if (data_nfloats % (size_t)(c->nobs + 1) != 0)
     SXMC_INVAL("Number of entries in evaluation points array not divisible by number of observables.");
   c->nevents = data_nfloats / (size_t)(c->nobs + 1);
+  chain_drop_graph(c);   // the captured launches bake nevents and the table pointers
   // p->SetEvalPoints(data) for every pdf (src/mcmc.cpp:235)
   for (int j = 0; j < c->nsignals; ++j) SXMC_TRY(sxmc_hist_set_eval_points(c->pdfs[j], data, data_nfloats));
   c->nll_grid = nll_grid_for((long long)c->nevents);
@@ -952,10 +965,9 @@ static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b) {
 
 extern "C" {
 
-int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
-                   float burnin_fraction, int debug_mode, unsigned sync_interval, long* nrows_out) {
-  (void)sync_interval;
-  if (!c) SXMC_INVAL("sxmc_chain_run: NULL chain");
+int sxmc_chain_begin(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
+                     float burnin_fraction, int debug_mode) {
+  if (!c) SXMC_INVAL("sxmc_chain_begin: NULL chain");
   SXMC_TRY(sxmc_chain_set_data(c, data, data_nfloats));
   const int np = c->nparameters;
   // chain buffer: every step fits (the reference drains a sync_interval-sized buffer instead)
@@ -975,6 +987,9 @@ int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsign
   chain_init_state(c, *c->st_host, nsteps, burnin_fraction, debug_mode);
   SXMC_TRY(chain_push_state(c));
   c->launches = 0;
+  c->loop_ms = 0;
+  c->steps_done = 0;
+  c->steps_planned = nsteps;
 
   // initial evaluation at the means (src/mcmc.cpp:233-252): always bins, whatever is fixed
   SXMC_CUDA(cudaMemsetAsync(c->hist_buf[0], 0, sizeof(unsigned) * c->hist_words, c->stream));
@@ -982,49 +997,135 @@ int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsign
   SXMC_TRY(chain_bin(c, 0));
   SXMC_TRY(chain_nll(c, 0, NLL_MODE_INIT, false, nullptr));
   c->last_buf = 0;
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  return SXMC_OK;
+}
 
+// Advance the chain by nsteps (the body of the loop at src/mcmc.cpp:261-378), device-resident.
+int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
+  if (!c || !c->have_data) { set_error("sxmc_chain_advance: sxmc_chain_begin was not called"); return SXMC_ESTATE; }
+  if ((unsigned long long)c->steps_done + nsteps > c->steps_planned) {
+    set_error("sxmc_chain_advance: more steps than sxmc_chain_begin announced");
+    return SXMC_ESTATE;
+  }
   const bool rebin = c->nsystematics > 0 && !c->systematics_fixed;   // src/mcmc.cpp:264
-  SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
-  unsigned done = 0;
   const bool has_comm = c->comm && c->comm->nranks > 1;
-  if (c->mode == 0 && nsteps >= 32) {
-    // CUDA graph of GRAPH_STEPS consecutive steps; step i bins into buffer (i+1)&1 when rebinning
-    const unsigned GRAPH_STEPS = 16;
+  const unsigned GRAPH_STEPS = 16;   // even: the histogram double-buffer parity is preserved
+  unsigned left = nsteps;
+  auto plain_step = [&]() -> int {
+    const unsigned i = c->steps_done;
+    int rc = chain_enqueue_step(c, rebin, rebin ? (int)((i + 1) & 1) : 0);
+    if (!rc) { c->steps_done += 1; left -= 1; }
+    return rc;
+  };
+  if (c->mode == 0 && left >= 2 * GRAPH_STEPS && !c->graph_exec) {
+    // CUDA graph of GRAPH_STEPS consecutive steps starting at an even step index
     cudaGraph_t graph = nullptr;
-    cudaGraphExec_t exec = nullptr;
     const long before = c->launches;
     SXMC_CUDA(cudaStreamBeginCapture(c->stream, has_comm ? cudaStreamCaptureModeRelaxed
                                                           : cudaStreamCaptureModeThreadLocal));
     int rc = SXMC_OK;
     for (unsigned k = 0; k < GRAPH_STEPS && !rc; ++k) rc = chain_enqueue_step(c, rebin, rebin ? (int)((k + 1) & 1) : 0);
     cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    c->graph_launches = c->launches - before;
+    c->launches = before;
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture", __FILE__, __LINE__);
-    const long per_graph = c->launches - before;
-    c->launches = before;
-    e = cudaGraphInstantiate(&exec, graph, 0);
-    if (e != cudaSuccess) { cudaGraphDestroy(graph); return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__); }
-    const unsigned ngraphs = nsteps / GRAPH_STEPS;
-    for (unsigned g = 0; g < ngraphs; ++g) {
-      e = cudaGraphLaunch(exec, c->stream);
-      if (e != cudaSuccess) break;
-      c->launches += per_graph;
-    }
-    cudaGraphExecDestroy(exec);
+    e = cudaGraphInstantiate(&c->graph_exec, graph, 0);
     cudaGraphDestroy(graph);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphLaunch", __FILE__, __LINE__);
-    done = ngraphs * GRAPH_STEPS;   // GRAPH_STEPS is even: buffer parity is preserved
+    if (e != cudaSuccess) { c->graph_exec = nullptr; return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__); }
   }
-  for (unsigned i = done; i < nsteps; ++i)
-    SXMC_TRY(chain_enqueue_step(c, rebin, rebin ? (int)((i + 1) & 1) : 0));
-  if (rebin && nsteps > 0) c->last_buf = (int)(nsteps & 1);   // step nsteps-1 used buffer nsteps&1
+  SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
+  if (c->mode == 0 && c->graph_exec) {
+    if ((c->steps_done & 1u) && left > 0) SXMC_TRY(plain_step());
+    while (left >= GRAPH_STEPS) {
+      SXMC_CUDA(cudaGraphLaunch(c->graph_exec, c->stream));
+      c->launches += c->graph_launches;
+      c->steps_done += GRAPH_STEPS;
+      left -= GRAPH_STEPS;
+    }
+  }
+  while (left > 0) SXMC_TRY(plain_step());
+  if (rebin && c->steps_done > 0) c->last_buf = (int)(c->steps_done & 1);   // step n-1 used buffer n&1
   SXMC_CUDA(cudaEventRecord(c->ev1, c->stream));
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  SXMC_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+  c->loop_ms += ms;
+  return SXMC_OK;
+}
+
+// Same steps as sxmc_chain_advance, issued as plain stream launches with a CUDA event around
+// every kernel, and (flush_bytes > 0) an L2 flush -- a memset of flush_bytes -- before every
+// step, outside the timed intervals.  Measurement only.
+int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes, float* step_ms_sum,
+                             float* bin_ms_sum, float* nll_ms_sum) {
+  if (!c || !c->have_data) { set_error("sxmc_chain_advance_timed: sxmc_chain_begin was not called"); return SXMC_ESTATE; }
+  if ((unsigned long long)c->steps_done + nsteps > c->steps_planned) {
+    set_error("sxmc_chain_advance_timed: more steps than sxmc_chain_begin announced");
+    return SXMC_ESTATE;
+  }
+  const bool rebin = c->nsystematics > 0 && !c->systematics_fixed;
+  if (flush_bytes > c->flush_bytes) {
+    cudaFree(c->flush_buf);
+    c->flush_buf = nullptr;
+    c->flush_bytes = 0;
+    SXMC_CUDA(cudaMalloc(&c->flush_buf, flush_bytes));
+    c->flush_bytes = flush_bytes;
+  }
+  const unsigned CHUNK = 64;
+  if (c->tev.empty()) {
+    c->tev.resize(3 * CHUNK);
+    for (auto& e : c->tev) SXMC_CUDA(cudaEventCreate(&e));
+  }
+  double t_step = 0, t_bin = 0, t_nll = 0;
+  unsigned left = nsteps;
+  while (left > 0) {
+    const unsigned n = std::min(left, CHUNK);
+    for (unsigned k = 0; k < n; ++k) {
+      const unsigned i = c->steps_done;
+      const int b = rebin ? (int)((i + 1) & 1) : 0;
+      if (flush_bytes) SXMC_CUDA(cudaMemsetAsync(c->flush_buf, (int)(i & 0xff), flush_bytes, c->stream));
+      SXMC_CUDA(cudaEventRecord(c->tev[3 * k], c->stream));
+      if (rebin) SXMC_TRY(chain_bin(c, b));
+      SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 1], c->stream));
+      SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));
+      SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 2], c->stream));
+      c->steps_done += 1;
+    }
+    SXMC_CUDA(cudaStreamSynchronize(c->stream));
+    for (unsigned k = 0; k < n; ++k) {
+      float a = 0, b2 = 0;
+      SXMC_CUDA(cudaEventElapsedTime(&a, c->tev[3 * k], c->tev[3 * k + 1]));
+      SXMC_CUDA(cudaEventElapsedTime(&b2, c->tev[3 * k + 1], c->tev[3 * k + 2]));
+      t_bin += a; t_nll += b2; t_step += a + b2;
+    }
+    left -= n;
+  }
+  if (rebin && c->steps_done > 0) c->last_buf = (int)(c->steps_done & 1);
+  c->loop_ms += (float)t_step;
+  if (step_ms_sum) *step_ms_sum = (float)t_step;
+  if (bin_ms_sum) *bin_ms_sum = (float)t_bin;
+  if (nll_ms_sum) *nll_ms_sum = (float)t_nll;
+  return SXMC_OK;
+}
+
+int sxmc_chain_end(sxmc_chain* c, long* nrows_out) {
+  if (!c) SXMC_INVAL("sxmc_chain_end: NULL chain");
   SXMC_TRY(chain_pull_state(c));
-  SXMC_CUDA(cudaEventElapsedTime(&c->loop_ms, c->ev0, c->ev1));
   c->nrows = c->st_host->nrows;
   c->accepted = c->st_host->accepted;
   if (nrows_out) *nrows_out = (long)std::min(c->nrows, c->row_cap);
   return SXMC_OK;
+}
+
+int sxmc_chain_run(sxmc_chain* c, const float* data, size_t data_nfloats, unsigned nsteps,
+                   float burnin_fraction, int debug_mode, unsigned sync_interval, long* nrows_out) {
+  (void)sync_interval;
+  if (!c) SXMC_INVAL("sxmc_chain_run: NULL chain");
+  SXMC_TRY(sxmc_chain_begin(c, data, data_nfloats, nsteps, burnin_fraction, debug_mode));
+  SXMC_TRY(sxmc_chain_advance(c, nsteps));
+  return sxmc_chain_end(c, nrows_out);
 }
 
 int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows) {

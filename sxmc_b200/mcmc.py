@@ -149,6 +149,32 @@ class MCMC:
         _check(lib().sxmc_chain_read(self._c, ptr(rows, c_fp), rows.shape[0]))
         return LikelihoodSpace(rows[:self.nrows], self.parameter_names)
 
+    # -- the same call in parts (sxmc_chain_begin / advance / end), for resident chains
+    def begin(self, data, nsteps, burnin_fraction, debug_mode=False):
+        d = np.ascontiguousarray(data, dtype=np.float32).ravel()
+        dd = d if d.size else np.zeros(1, np.float32)
+        _check(lib().sxmc_chain_begin(self._c, ptr(dd, c_fp), d.size, int(nsteps),
+                                      float(burnin_fraction), int(debug_mode)))
+        self._nevents = d.size // (self.nobservables + 1)
+
+    def advance(self, nsteps):
+        _check(lib().sxmc_chain_advance(self._c, int(nsteps)))
+
+    def advance_timed(self, nsteps, flush_bytes=0):
+        """Returns (step_ms, bin_ms, nll_ms) summed over nsteps, from per-kernel CUDA events."""
+        a, b, c = C.c_float(0), C.c_float(0), C.c_float(0)
+        _check(lib().sxmc_chain_advance_timed(self._c, int(nsteps), int(flush_bytes),
+                                              C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def end(self):
+        nrows = C.c_long(0)
+        _check(lib().sxmc_chain_end(self._c, C.byref(nrows)))
+        self.nrows = nrows.value
+        rows = np.zeros((max(1, self.nrows), self.nparameters + 1), dtype=np.float32)
+        _check(lib().sxmc_chain_read(self._c, ptr(rows, c_fp), rows.shape[0]))
+        return LikelihoodSpace(rows[:self.nrows], self.parameter_names)
+
     def accepted(self):
         v = C.c_long(0)
         _check(lib().sxmc_chain_accepted(self._c, C.byref(v)))
