@@ -113,31 +113,57 @@ __device__ __forceinline__ float4 ldg_stream(const float4* p) {
 // =========================================================================================
 
 // All systematics of a fast launch have a single coefficient (npars <= 1): p is the same for
-// every sample, resolved once per segment into SystRt::c0 / onep.
-template <int NS>
-__device__ __forceinline__ void apply_syst_slots(double (&f)[NS][4], const SystRt& s) {
+// every sample, resolved once per segment into SystRt::c0 / onep.  The (type, slot, slot)
+// triple of each systematic is warp-uniform; it is dispatched with switch statements whose
+// cases index the slot array with compile-time constants only, so the 4-sample working set
+// stays in registers (a loop with `if (s.obs != o) continue` gets rewritten by the compiler
+// into a dynamically indexed local-memory array).
+constexpr int FAST_MAX_OPS = 4;
+
+template <int NS, int O, int E>
+__device__ __forceinline__ void op_resolution(double (&f)[NS][4], const double c0) {
 #pragma unroll
-  for (int o = 0; o < NS; ++o) {
-    if (s.obs != o) continue;
-    if (s.type == SXMC_SYST_RESOLUTION_SCALE) {
+  for (int k = 0; k < 4; ++k)
+    f[O][k] = __dadd_rn(f[O][k], __dmul_rn(c0, __dadd_rn(f[O][k], -f[E][k])));
+}
+
+template <int NS, int O>
+__device__ __forceinline__ void op_on(double (&f)[NS][4], const int type, const int ext,
+                                      const double c0, const double onep) {
+  if (type == SXMC_SYST_SHIFT) {
 #pragma unroll
-      for (int e = 0; e < NS; ++e) {
-        if (s.extra != e) continue;
+    for (int k = 0; k < 4; ++k) f[O][k] = __dadd_rn(f[O][k], c0);
+  } else if (type == SXMC_SYST_SCALE) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          f[o][k] = __dadd_rn(f[o][k], __dmul_rn(s.c0, __dadd_rn(f[o][k], -f[e][k])));
-      }
-    } else if (s.type == SXMC_SYST_SHIFT) {
+    for (int k = 0; k < 4; ++k) f[O][k] = __dmul_rn(f[O][k], onep);
+  } else if (type == SXMC_SYST_CTSCALE) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) f[o][k] = __dadd_rn(f[o][k], s.c0);
-    } else if (s.type == SXMC_SYST_SCALE) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) f[o][k] = __dmul_rn(f[o][k], s.onep);
-    } else {  // CTSCALE
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        f[o][k] = __dadd_rn(1.0, __dmul_rn(__dadd_rn(f[o][k], -1.0), s.onep));
+    for (int k = 0; k < 4; ++k)
+      f[O][k] = __dadd_rn(1.0, __dmul_rn(__dadd_rn(f[O][k], -1.0), onep));
+  } else {  // RESOLUTION_SCALE
+    switch (ext) {
+      case 0: op_resolution<NS, O, 0>(f, c0); break;
+      case 1: if constexpr (NS > 1) op_resolution<NS, O, 1>(f, c0); break;
+      case 2: if constexpr (NS > 2) op_resolution<NS, O, 2>(f, c0); break;
+      case 3: if constexpr (NS > 3) op_resolution<NS, O, 3>(f, c0); break;
+      case 4: if constexpr (NS > 4) op_resolution<NS, O, 4>(f, c0); break;
+      default: if constexpr (NS > 5) op_resolution<NS, O, 5>(f, c0); break;
     }
+  }
+}
+
+// code = type | obs_slot << 4 | extra_slot << 8
+template <int NS>
+__device__ __forceinline__ void apply_op(double (&f)[NS][4], const int code, const double c0,
+                                         const double onep) {
+  const int type = code & 15, ext = code >> 8;
+  switch ((code >> 4) & 15) {
+    case 0: op_on<NS, 0>(f, type, ext, c0, onep); break;
+    case 1: if constexpr (NS > 1) op_on<NS, 1>(f, type, ext, c0, onep); break;
+    case 2: if constexpr (NS > 2) op_on<NS, 2>(f, type, ext, c0, onep); break;
+    case 3: if constexpr (NS > 3) op_on<NS, 3>(f, type, ext, c0, onep); break;
+    case 4: if constexpr (NS > 4) op_on<NS, 4>(f, type, ext, c0, onep); break;
+    default: if constexpr (NS > 5) op_on<NS, 5>(f, type, ext, c0, onep); break;
   }
 }
 
@@ -156,82 +182,164 @@ __device__ __forceinline__ int flat_bin(const double (&x)[NOBS], const Geo& g) {
   return in ? b : -1;
 }
 
-template <int NOBS, int NS, bool SMEM, int U>
-__global__ void __launch_bounds__(BIN_THREADS)
-bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __restrict__ btile_prefix,
-                int njobs, const Geo geo) {
-  extern __shared__ unsigned s_hist[];
+// ---- mbarrier / bulk-copy (TMA unit, SASS UBLKCP) primitives ---------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  unsigned ok = 0;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ float4 lds128(unsigned addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr));
+  return v;
+}
+
+// One persistent CTA per SM, FAST_WARPS warps.  Work unit = a "chunk": R consecutive rows
+// (R x 512 B per column) of a warp-tile.  The chunk sequence of all jobs is cut evenly over
+// the CTAs; inside a CTA each job segment is cut into one CONTIGUOUS chunk range per warp.
+// Every warp runs its own S-stage pipeline: lane 0 issues one bulk async copy (TMA unit)
+// per column per chunk into the warp's private shared-memory stages, completion is signalled
+// on a per-stage mbarrier, and the warp consumes the stage with conflict-free LDS.128 --
+// the loads in flight live in shared memory, not in registers, and no CTA-wide barrier is
+// needed in steady state.
+template <int NOBS, int NS, bool SMEM>
+__global__ void __launch_bounds__(FAST_THREADS, 1)
+bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __restrict__ chunk_prefix,
+                int njobs, const Geo geo, const int R, const int S, const unsigned stage_off) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ SystRt s_syst[SXMC_MAX_SYST];
+  __shared__ __align__(8) unsigned long long s_bar[FAST_WARPS * FAST_MAX_STAGES];
+  unsigned* s_hist = reinterpret_cast<unsigned*>(smem_raw);
 
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const unsigned long long total = btile_prefix[njobs];
+  const unsigned col_bytes = (unsigned)R * 512u;          // one column of one chunk
+  const unsigned stage_bytes = NS * col_bytes;
+  const unsigned my_stage0 = smem_u32(smem_raw + stage_off) + (unsigned)(warp * S) * stage_bytes;
+  const unsigned my_bar0 = smem_u32(&s_bar[warp * FAST_MAX_STAGES]);
+  if (lane == 0) {
+    for (int s = 0; s < S; ++s) mbar_init(my_bar0 + 8u * s, 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  const unsigned long long total = chunk_prefix[njobs];
   unsigned long long t0 = total * blockIdx.x / gridDim.x;
   const unsigned long long t1 = total * (blockIdx.x + 1ull) / gridDim.x;
   if (t0 >= t1) return;
   int j = 0;
-  while (btile_prefix[j + 1] <= t0) ++j;
+  while (chunk_prefix[j + 1] <= t0) ++j;
+  unsigned it = 0;    // chunks this warp has consumed so far: stage = it % S, parity = (it / S) & 1
 
   while (t0 < t1) {
     const BinJob& job = jobs[j];
-    const unsigned long long jbeg = btile_prefix[j], jend = btile_prefix[j + 1];
+    const unsigned long long jbeg = chunk_prefix[j], jend = chunk_prefix[j + 1];
     const unsigned long long tend = t1 < jend ? t1 : jend;
     const int nsyst = job.nsyst;
     if (threadIdx.x < nsyst) resolve_syst(job, threadIdx.x, s_syst[threadIdx.x], true);
     if (SMEM)
-      for (int b = threadIdx.x; b < geo.total_nbins; b += BIN_THREADS) s_hist[b] = 0;
+      for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) s_hist[b] = 0;
     __syncthreads();
 
+    // the segment's systematics, in registers
+    int op_code[FAST_MAX_OPS];
+    double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
+#pragma unroll
+    for (int k = 0; k < FAST_MAX_OPS; ++k) {
+      op_code[k] = 0; op_c0[k] = 0.0; op_onep[k] = 1.0;
+      if (k < nsyst) {
+        op_code[k] = s_syst[k].type | (s_syst[k].obs << 4) | (s_syst[k].extra << 8);
+        op_c0[k] = s_syst[k].c0;
+        op_onep[k] = s_syst[k].onep;
+      }
+    }
+
     unsigned* hist = SMEM ? s_hist : job.bins;
-    const float4* col[NS];
+    const unsigned char* col[NS];
 #pragma unroll
     for (int c = 0; c < NS; ++c)
-      col[c] = reinterpret_cast<const float4*>(job.cols[job.slot_field[c]]);
-    const unsigned long long nwt = job.nwtiles;
+      col[c] = reinterpret_cast<const unsigned char*>(job.cols[job.slot_field[c]]);
+
+    // this warp's contiguous chunk range [ca, cb) of the job (chunk c starts at byte c * col_bytes)
+    const unsigned long long n = tend - t0;
+    const unsigned long long ca = (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
+    const unsigned long long cb = (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
+
+    auto issue = [&](unsigned long long c, unsigned slot) {   // lane 0 only
+      const unsigned bar = my_bar0 + 8u * slot;
+      const unsigned dst = my_stage0 + slot * stage_bytes;
+      mbar_expect_tx(bar, stage_bytes);
+#pragma unroll
+      for (int k = 0; k < NS; ++k) bulk_g2s(dst + k * col_bytes, col[k] + c * col_bytes, col_bytes, bar);
+    };
+    if (lane == 0)
+      for (unsigned i = 0; i < (unsigned)S && ca + i < cb; ++i) issue(ca + i, (it + i) % (unsigned)S);
 
     RunAcc acc;
     acc.norm = 0;
-    for (unsigned long long bt = t0; bt < tend; ++bt) {
-      const unsigned long long wt = (bt - jbeg) * BIN_WARPS + warp;
-      if (wt >= nwt) continue;
-      acc.cur = -1;
-      acc.cnt = 0;
-      const unsigned long long base = wt * (WT_ROWS * 32ull) + lane;
+    acc.cur = -1;
+    acc.cnt = 0;
 #pragma unroll 1
-      for (int q0 = 0; q0 < WT_ROWS; q0 += U) {
-        float4 v[NS][U];
+    for (unsigned long long c = ca; c < cb; ++c, ++it) {
+      const unsigned slot = it % (unsigned)S;
+      mbar_wait(my_bar0 + 8u * slot, (it / (unsigned)S) & 1u);
+      const unsigned src = my_stage0 + slot * stage_bytes + (unsigned)lane * 16u;
+#pragma unroll 1
+      for (int r = 0; r < R; ++r) {
+        double f[NS][4];
 #pragma unroll
-        for (int u = 0; u < U; ++u)
+        for (int k = 0; k < NS; ++k) {
+          const float4 v = lds128(src + k * col_bytes + r * 512u);
+          f[k][0] = (double)v.x; f[k][1] = (double)v.y; f[k][2] = (double)v.z; f[k][3] = (double)v.w;
+        }
 #pragma unroll
-          for (int c = 0; c < NS; ++c) v[c][u] = ldg_stream(col[c] + base + (q0 + u) * 32);
+        for (int k = 0; k < FAST_MAX_OPS; ++k)
+          if (k < nsyst) apply_op<NS>(f, op_code[k], op_c0[k], op_onep[k]);
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          double f[NS][4];
+        for (int k = 0; k < 4; ++k) {
+          double x[NOBS];
 #pragma unroll
-          for (int c = 0; c < NS; ++c) {
-            f[c][0] = (double)v[c][u].x; f[c][1] = (double)v[c][u].y;
-            f[c][2] = (double)v[c][u].z; f[c][3] = (double)v[c][u].w;
-          }
-          for (int k = 0; k < nsyst; ++k) apply_syst_slots<NS>(f, s_syst[k]);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            double x[NOBS];
-#pragma unroll
-            for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
-            run_push<SMEM>(acc, flat_bin<NOBS>(x, geo), hist, geo.total_nbins);
-          }
+          for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
+          run_push<SMEM>(acc, flat_bin<NOBS>(x, geo), hist, geo.total_nbins);
         }
       }
-      run_flush<SMEM>(acc, hist, geo.total_nbins);
+      __syncwarp();                       // every lane has read the stage before it is refilled
+      if (lane == 0 && c + (unsigned)S < cb) issue(c + (unsigned)S, slot);
     }
+    run_flush<SMEM>(acc, hist, geo.total_nbins);
 
     const unsigned wnorm = __reduce_add_sync(0xffffffffu, acc.norm);
     if (lane == 0 && wnorm) atomicAdd(job.norm, wnorm);
     if (SMEM) {
       __syncthreads();
-      for (int b = threadIdx.x; b < geo.total_nbins; b += BIN_THREADS) {
-        const unsigned c = s_hist[b];
-        if (c) atomicAdd(job.bins + b, c);
+      for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) {
+        const unsigned cnt = s_hist[b];
+        if (cnt) atomicAdd(job.bins + b, cnt);
       }
     }
     __syncthreads();   // s_syst / s_hist are rewritten by the next segment
@@ -316,32 +424,45 @@ bin_generic_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __
 // =========================================================================================
 // launch dispatch
 // =========================================================================================
-typedef void (*FastKernel)(const BinJob*, const unsigned long long*, int, const Geo);
-
-template <int NOBS, int NS, bool SMEM>
-static FastKernel pick_fast_u() {
-  constexpr int U = (NS <= 2) ? 4 : 2;
-  return bin_fast_kernel<NOBS, NS, SMEM, U>;
-}
+typedef void (*FastKernel)(const BinJob*, const unsigned long long*, int, const Geo, int, int, unsigned);
 
 template <bool SMEM>
 static FastKernel pick_fast(int nobs, int ns) {
   switch (nobs * 10 + ns) {
-    case 11: return pick_fast_u<1, 1, SMEM>();
-    case 12: return pick_fast_u<1, 2, SMEM>();
-    case 13: return pick_fast_u<1, 3, SMEM>();
-    case 22: return pick_fast_u<2, 2, SMEM>();
-    case 23: return pick_fast_u<2, 3, SMEM>();
-    case 24: return pick_fast_u<2, 4, SMEM>();
-    case 33: return pick_fast_u<3, 3, SMEM>();
-    case 34: return pick_fast_u<3, 4, SMEM>();
-    case 35: return pick_fast_u<3, 5, SMEM>();
+    case 11: return bin_fast_kernel<1, 1, SMEM>;
+    case 12: return bin_fast_kernel<1, 2, SMEM>;
+    case 13: return bin_fast_kernel<1, 3, SMEM>;
+    case 22: return bin_fast_kernel<2, 2, SMEM>;
+    case 23: return bin_fast_kernel<2, 3, SMEM>;
+    case 24: return bin_fast_kernel<2, 4, SMEM>;
+    case 33: return bin_fast_kernel<3, 3, SMEM>;
+    case 34: return bin_fast_kernel<3, 4, SMEM>;
+    case 35: return bin_fast_kernel<3, 5, SMEM>;
   }
   return nullptr;
 }
 
 bool bin_fast_supported(int nobs, int nslots) {
   return pick_fast<false>(nobs, nslots) != nullptr;
+}
+
+// Shared-memory plan of the fast kernel: [histogram][FAST_WARPS x S stages of NS x R x 512 B].
+// Returns false when not even 2 single-row stages fit beside the histogram.
+bool bin_fast_plan(int nslots, int hist_bins, int* R_out, int* S_out, unsigned* stage_off_out,
+                   size_t* smem_out) {
+  const size_t limit = 227 * 1024 - 2048;      // opt-in maximum minus the static part
+  const size_t hist = ((size_t)hist_bins * sizeof(unsigned) + 127) & ~(size_t)127;
+  if (hist >= limit) return false;
+  for (int R = 2; R >= 1; --R) {
+    const size_t per_stage = (size_t)FAST_WARPS * nslots * R * 512;
+    int S = (int)((limit - hist) / per_stage);
+    if (S > FAST_MAX_STAGES) S = FAST_MAX_STAGES;
+    if (S >= 3 || (R == 1 && S >= 2)) {
+      *R_out = R; *S_out = S; *stage_off_out = (unsigned)hist; *smem_out = hist + per_stage * S;
+      return true;
+    }
+  }
+  return false;
 }
 
 static int g_num_sms = 0;
@@ -356,17 +477,27 @@ static int num_sms() {
 }
 
 int launch_bin(const BinLaunch& L, cudaStream_t stream) {
-  if (L.total_btiles == 0) return SXMC_OK;
-  const size_t smem = L.smem_hist ? sizeof(unsigned) * (size_t)L.max_total_nbins : 0;
-  const void* fn = nullptr;
-  FastKernel fk = nullptr;
+  if (L.total_units == 0) return SXMC_OK;
   if (L.fast) {
-    fk = L.smem_hist ? pick_fast<true>(L.nobs, L.nslots) : pick_fast<false>(L.nobs, L.nslots);
+    FastKernel fk = L.smem_hist ? pick_fast<true>(L.nobs, L.nslots) : pick_fast<false>(L.nobs, L.nslots);
     if (!fk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
-    fn = (const void*)fk;
-  } else {
-    fn = L.smem_hist ? (const void*)bin_generic_kernel<true> : (const void*)bin_generic_kernel<false>;
+    SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
+    // one persistent CTA per SM; at least one chunk per warp
+    unsigned long long grid = (unsigned long long)num_sms();
+    const unsigned long long max_grid = (L.total_units + FAST_WARPS - 1) / FAST_WARPS;
+    if (grid > max_grid) grid = max_grid;
+    Geo g;
+    for (int i = 0; i < 3; ++i) {
+      g.lo[i] = L.lower[i]; g.hi[i] = L.upper[i]; g.sc[i] = L.scale[i]; g.st[i] = L.stride[i];
+    }
+    g.total_nbins = L.max_total_nbins;
+    fk<<<(unsigned)grid, FAST_THREADS, L.smem_bytes, stream>>>(L.jobs_dev, L.prefix_dev, L.njobs, g,
+                                                               L.rows_per_stage, L.nstages, L.stage_off);
+    SXMC_CUDA(cudaGetLastError());
+    return SXMC_OK;
   }
+  const size_t smem = L.smem_hist ? sizeof(unsigned) * (size_t)L.max_total_nbins : 0;
+  const void* fn = L.smem_hist ? (const void*)bin_generic_kernel<true> : (const void*)bin_generic_kernel<false>;
   if (smem > 48 * 1024)
     SXMC_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
@@ -374,15 +505,8 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
   if (occ < 1) occ = 1;
   if (L.blocks_per_sm > 0 && L.blocks_per_sm < occ) occ = L.blocks_per_sm;
   unsigned long long grid = (unsigned long long)num_sms() * occ;
-  if (grid > L.total_btiles) grid = L.total_btiles;
-  if (L.fast) {
-    Geo g;
-    for (int i = 0; i < 3; ++i) {
-      g.lo[i] = L.lower[i]; g.hi[i] = L.upper[i]; g.sc[i] = L.scale[i]; g.st[i] = L.stride[i];
-    }
-    g.total_nbins = L.max_total_nbins;
-    fk<<<(unsigned)grid, BIN_THREADS, smem, stream>>>(L.jobs_dev, L.prefix_dev, L.njobs, g);
-  } else if (L.smem_hist) {
+  if (grid > L.total_units) grid = L.total_units;
+  if (L.smem_hist) {
     bin_generic_kernel<true><<<(unsigned)grid, BIN_THREADS, smem, stream>>>(
         L.jobs_dev, L.prefix_dev, L.njobs, L.max_total_nbins);
   } else {

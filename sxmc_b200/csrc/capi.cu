@@ -238,15 +238,11 @@ static void plan_launch(Batch& b, int n) {
   L.jobs_dev = b.dev;
   L.prefix_dev = b.prefix_dev;
   L.njobs = n;
-  unsigned long long total = 0;
-  b.prefix_host[0] = 0;
   bool uniform = true;
   int max_bins = 0, max_slots = 0;
   bool poly = false;
   for (int j = 0; j < n; ++j) {
     const BinJob& job = b.host[j];
-    total += (job.nwtiles + BIN_WARPS - 1) / BIN_WARPS;
-    b.prefix_host[j + 1] = total;
     max_bins = std::max(max_bins, job.total_nbins);
     max_slots = std::max(max_slots, job.nslots);
     const BinJob& j0 = b.host[0];
@@ -257,14 +253,23 @@ static void plan_launch(Batch& b, int n) {
         uniform = false;
     for (int k = 0; k < job.nsyst; ++k)
       if (job.syst[k].npars > 1) poly = true;   // per-sample polynomials go through the generic kernel
+    if (job.nsyst > 4) poly = true;             // FAST_MAX_OPS register-resident systematics
   }
-  L.total_btiles = total;
   L.max_total_nbins = max_bins;
   L.nobs = n ? b.host[0].nobs : 0;
   L.nslots = max_slots;
+  L.smem_hist = max_bins <= g_smem_hist_max_bins;
+  L.blocks_per_sm = g_blocks_per_sm;
   L.fast = n > 0 && uniform && !poly && !g_force_generic && L.nobs <= 3 &&
            bin_fast_supported(L.nobs, max_slots);
   if (L.fast) {
+    // pipeline stages share the shared memory with the privatised histogram; when the
+    // histogram leaves no room for them it stays in global memory (L2 atomics)
+    if (!(L.smem_hist && bin_fast_plan(max_slots, max_bins, &L.rows_per_stage, &L.nstages,
+                                       &L.stage_off, &L.smem_bytes))) {
+      L.smem_hist = false;
+      bin_fast_plan(max_slots, 0, &L.rows_per_stage, &L.nstages, &L.stage_off, &L.smem_bytes);
+    }
     // every job of a fast launch uses the same slot count (columns it does not need are
     // simply re-reads of observable 0)
     for (int j = 0; j < n; ++j) {
@@ -277,8 +282,16 @@ static void plan_launch(Batch& b, int n) {
       L.scale[o] = b.host[0].scale[o]; L.stride[o] = b.host[0].stride[o];
     }
   }
-  L.smem_hist = max_bins <= g_smem_hist_max_bins;
-  L.blocks_per_sm = g_blocks_per_sm;
+  // work units: chunks of rows_per_stage rows (fast) or block-tiles of BIN_WARPS warp-tiles
+  unsigned long long total = 0;
+  b.prefix_host[0] = 0;
+  for (int j = 0; j < n; ++j) {
+    const BinJob& job = b.host[j];
+    if (L.fast) total += job.nwtiles * (unsigned long long)(WT_ROWS / L.rows_per_stage);
+    else total += (job.nwtiles + BIN_WARPS - 1) / BIN_WARPS;
+    b.prefix_host[j + 1] = total;
+  }
+  L.total_units = total;
 }
 
 static int upload_batch(Batch& b, int n, cudaStream_t stream) {

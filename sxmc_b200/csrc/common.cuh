@@ -22,6 +22,10 @@ constexpr int WT_ROWS = LANE_RUN / 4;           // float4 rows per warp-tile
 constexpr int BIN_THREADS = 256;
 constexpr int BIN_WARPS = BIN_THREADS / 32;     // warp-tiles per block-tile
 
+constexpr int FAST_WARPS = 16;                  // warps of the persistent fast binning CTA
+constexpr int FAST_THREADS = FAST_WARPS * 32;
+constexpr int FAST_MAX_STAGES = 8;              // bulk-copy pipeline stages per warp
+
 constexpr int MAX_SLOTS = 6;                    // columns the fast kernel keeps in registers
 
 struct SystDesc {

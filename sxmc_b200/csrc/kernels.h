@@ -12,14 +12,18 @@ struct PrepGeo {     // histogram geometry passed by value to the small preparat
 
 struct BinLaunch {
   const BinJob* jobs_dev;
-  const unsigned long long* prefix_dev;   // [njobs+1] block-tile prefix sums
+  const unsigned long long* prefix_dev;   // [njobs+1] prefix sums of work units: chunks of
+                                          // rows_per_stage rows (fast) / 8-warp-tile block-tiles (generic)
   int njobs;
-  unsigned long long total_btiles;
+  unsigned long long total_units;
   bool fast;                 // register-resident kernel (uniform geometry, nobs<=3)
   bool smem_hist;            // shared-memory privatised histograms
   int nobs, nslots;
   int max_total_nbins;
-  int blocks_per_sm;         // <=0: occupancy maximum
+  int blocks_per_sm;         // <=0: occupancy maximum (generic kernel)
+  int rows_per_stage, nstages;   // fast kernel pipeline shape
+  unsigned stage_off;            // byte offset of the stages in dynamic shared memory
+  size_t smem_bytes;
   double lower[3], upper[3], scale[3];
   int stride[3];
 };
@@ -36,6 +40,8 @@ struct EvalPdfJob {
 };
 
 bool bin_fast_supported(int nobs, int nslots);
+bool bin_fast_plan(int nslots, int hist_bins, int* R_out, int* S_out, unsigned* stage_off_out,
+                   size_t* smem_out);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);
 int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,
                    const PrepGeo& g, int primary, bool sort, float* cols_dev,
