@@ -109,8 +109,10 @@ int sxmc_hist_set_layout(sxmc_hist* h, int sort);
 int sxmc_hist_prepare(sxmc_hist* h);
 /* tuning knobs of the binning launch (EvalHist::OptimizeBin analogue, src/pdfz.cpp:630-727):
  * smem_hist_max_bins: histograms up to this many bins are privatised in shared memory;
- * blocks_per_sm <= 0 keeps the default. */
-int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_generic);
+ * blocks_per_sm <= 0 keeps the default;  kernel_select: 0 = automatic, bit 0 = force the
+ * generic (interpreting) kernel, bit 1 = force run-time systematic dispatch in the fast
+ * kernel (no compile-time program) -- both used by the parity tests to cover every path. */
+int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
 int sxmc_enable_kernel_timing(int on);

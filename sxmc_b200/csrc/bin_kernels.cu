@@ -167,6 +167,27 @@ __device__ __forceinline__ void apply_op(double (&f)[NS][4], const int code, con
   }
 }
 
+// Compile-time systematic programs.  A program is up to FAST_MAX_OPS op codes of 8 bits,
+// code = type | slot_obs << 2 | slot_extra << 5, packed little-endian in CODES; NOPS < 0 selects
+// the run-time dispatch above.  Kernels are instantiated for the programs of the BASELINE
+// workloads (table in pick_fast); any other fit runs the dispatching instantiation.
+template <int NS, int CODE>
+__device__ __forceinline__ void apply_static(double (&f)[NS][4], const double c0, const double onep) {
+  constexpr int type = CODE & 3, O = (CODE >> 2) & 7, E = (CODE >> 5) & 7;
+  static_assert(O < NS && E < NS, "systematic program addresses a slot the kernel does not load");
+  if constexpr (type == SXMC_SYST_RESOLUTION_SCALE) {
+    op_resolution<NS, O, E>(f, c0);
+  } else {
+    op_on<NS, O>(f, type, 0, c0, onep);   // `type` is a constant here: the chain folds
+  }
+}
+
+// (int)v for 0 <= v < 2^31 without the conversion pipe: v + 2^52 rounded toward -inf leaves
+// floor(v) in the low mantissa word.  Only used on in-domain samples (v >= 0).
+__device__ __forceinline__ int trunc_nonneg(double v) {
+  return __double2loint(__dadd_rd(v, 4503599627370496.0));
+}
+
 // flat bin of one transformed sample, -1 when outside the PDF domain (src/pdfz.cpp:386-398).
 // NaN compares false on both tests => outside (the reference's (int)NaN is undefined).
 template <int NOBS>
@@ -176,10 +197,21 @@ __device__ __forceinline__ int flat_bin(const double (&x)[NOBS], const Geo& g) {
 #pragma unroll
   for (int o = 0; o < NOBS; ++o) {
     in = in && (x[o] >= g.lo[o]) && (x[o] < g.hi[o]);
-    const int i = __double2int_rz(__dmul_rn(__dadd_rn(x[o], -g.lo[o]), g.sc[o]));
+    const int i = trunc_nonneg(__dmul_rn(__dadd_rn(x[o], -g.lo[o]), g.sc[o]));
     b += (NOBS == 1 ? i : i * g.st[o]);
   }
   return in ? b : -1;
+}
+
+// four consecutive samples of a lane's sorted run: usually all in the current bin
+template <bool SMEM>
+__device__ __forceinline__ void run_push4(RunAcc& r, const int (&b)[4], unsigned* hist, int total_nbins) {
+  if (b[0] == r.cur && b[1] == r.cur && b[2] == r.cur && b[3] == r.cur) {
+    r.cnt += 4;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) run_push<SMEM>(r, b[k], hist, total_nbins);
+  }
 }
 
 // ---- mbarrier / bulk-copy (TMA unit, SASS UBLKCP) primitives ---------------------------------
@@ -226,7 +258,7 @@ __device__ __forceinline__ float4 lds128(unsigned addr) {
 // on a per-stage mbarrier, and the warp consumes the stage with conflict-free LDS.128 --
 // the loads in flight live in shared memory, not in registers, and no CTA-wide barrier is
 // needed in steady state.
-template <int NOBS, int NS, bool SMEM>
+template <int NOBS, int NS, bool SMEM, int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(FAST_THREADS, 1)
 bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __restrict__ chunk_prefix,
                 int njobs, const Geo geo, const int R, const int S, const unsigned stage_off) {
@@ -317,16 +349,25 @@ bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __res
           const float4 v = lds128(src + k * col_bytes + r * 512u);
           f[k][0] = (double)v.x; f[k][1] = (double)v.y; f[k][2] = (double)v.z; f[k][3] = (double)v.w;
         }
+        if constexpr (NOPS < 0) {
 #pragma unroll
-        for (int k = 0; k < FAST_MAX_OPS; ++k)
-          if (k < nsyst) apply_op<NS>(f, op_code[k], op_c0[k], op_onep[k]);
+          for (int k = 0; k < FAST_MAX_OPS; ++k)
+            if (k < nsyst) apply_op<NS>(f, op_code[k], op_c0[k], op_onep[k]);
+        } else {
+          if constexpr (NOPS > 0) apply_static<NS, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
+          if constexpr (NOPS > 1) apply_static<NS, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
+          if constexpr (NOPS > 2) apply_static<NS, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
+          if constexpr (NOPS > 3) apply_static<NS, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
+        }
+        int bq[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           double x[NOBS];
 #pragma unroll
           for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
-          run_push<SMEM>(acc, flat_bin<NOBS>(x, geo), hist, geo.total_nbins);
+          bq[k] = flat_bin<NOBS>(x, geo);
         }
+        run_push4<SMEM>(acc, bq, hist, geo.total_nbins);
       }
       __syncwarp();                       // every lane has read the stage before it is refilled
       if (lane == 0 && c + (unsigned)S < cb) issue(c + (unsigned)S, slot);
@@ -426,24 +467,46 @@ bin_generic_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __
 // =========================================================================================
 typedef void (*FastKernel)(const BinJob*, const unsigned long long*, int, const Geo, int, int, unsigned);
 
-template <bool SMEM>
-static FastKernel pick_fast(int nobs, int ns) {
-  switch (nobs * 10 + ns) {
-    case 11: return bin_fast_kernel<1, 1, SMEM>;
-    case 12: return bin_fast_kernel<1, 2, SMEM>;
-    case 13: return bin_fast_kernel<1, 3, SMEM>;
-    case 22: return bin_fast_kernel<2, 2, SMEM>;
-    case 23: return bin_fast_kernel<2, 3, SMEM>;
-    case 24: return bin_fast_kernel<2, 4, SMEM>;
-    case 33: return bin_fast_kernel<3, 3, SMEM>;
-    case 34: return bin_fast_kernel<3, 4, SMEM>;
-    case 35: return bin_fast_kernel<3, 5, SMEM>;
-  }
+#define OPC(type, obs, ext) ((unsigned)((type) | ((obs) << 2) | ((ext) << 5)))
+struct FastEntry {
+  int nobs, ns, nops;
+  unsigned codes;
+  FastKernel k[2];   // [global-memory histogram, shared-memory histogram]
+};
+#define FE(NOBS, NS, NOPS, CODES)                                                   \
+  { NOBS, NS, NOPS, (CODES),                                                        \
+    { bin_fast_kernel<NOBS, NS, false, NOPS, (CODES)>, bin_fast_kernel<NOBS, NS, true, NOPS, (CODES)> } }
+static const FastEntry g_fast_table[] = {
+    // run-time dispatch of the systematics (any program of <= FAST_MAX_OPS single-coefficient ops)
+    FE(1, 1, -1, 0u), FE(1, 2, -1, 0u), FE(1, 3, -1, 0u), FE(2, 2, -1, 0u), FE(2, 3, -1, 0u),
+    FE(2, 4, -1, 0u), FE(3, 3, -1, 0u), FE(3, 4, -1, 0u), FE(3, 5, -1, 0u),
+    // no systematics
+    FE(1, 1, 0, 0u), FE(2, 2, 0, 0u), FE(3, 3, 0, 0u),
+    // workload B / bench_pdfz: shift(energy)
+    FE(1, 1, 1, OPC(SXMC_SYST_SHIFT, 0, 0)),
+    FE(1, 1, 1, OPC(SXMC_SYST_SCALE, 0, 0)),
+    // workload A: scale(energy), resolution_scale(energy; mc_energy)
+    FE(1, 2, 2, OPC(SXMC_SYST_SCALE, 0, 0) | OPC(SXMC_SYST_RESOLUTION_SCALE, 0, 1) << 8),
+    // workload C: the same on 2-D energy x radius
+    FE(2, 3, 2, OPC(SXMC_SYST_SCALE, 0, 0) | OPC(SXMC_SYST_RESOLUTION_SCALE, 0, 2) << 8),
+    // workload D: scale(energy), resolution_scale(energy; mc_energy), shift(radius) on 3-D
+    FE(3, 4, 3, OPC(SXMC_SYST_SCALE, 0, 0) | OPC(SXMC_SYST_RESOLUTION_SCALE, 0, 3) << 8 |
+                    OPC(SXMC_SYST_SHIFT, 1, 0) << 16),
+};
+
+// nops < 0: the dispatching instantiation
+static FastKernel pick_fast(int nobs, int ns, int nops, unsigned codes, bool smem) {
+  for (const FastEntry& e : g_fast_table)
+    if (e.nobs == nobs && e.ns == ns && e.nops == nops && (nops <= 0 || e.codes == codes))
+      return e.k[smem ? 1 : 0];
   return nullptr;
 }
 
 bool bin_fast_supported(int nobs, int nslots) {
-  return pick_fast<false>(nobs, nslots) != nullptr;
+  return pick_fast(nobs, nslots, -1, 0u, false) != nullptr;
+}
+bool bin_fast_has_program(int nobs, int nslots, int nops, unsigned codes) {
+  return nops >= 0 && pick_fast(nobs, nslots, nops, codes, false) != nullptr;
 }
 
 // Shared-memory plan of the fast kernel: [histogram][FAST_WARPS x S stages of NS x R x 512 B].
@@ -479,7 +542,7 @@ static int num_sms() {
 int launch_bin(const BinLaunch& L, cudaStream_t stream) {
   if (L.total_units == 0) return SXMC_OK;
   if (L.fast) {
-    FastKernel fk = L.smem_hist ? pick_fast<true>(L.nobs, L.nslots) : pick_fast<false>(L.nobs, L.nslots);
+    FastKernel fk = pick_fast(L.nobs, L.nslots, L.prog_nops, L.prog_codes, L.smem_hist);
     if (!fk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
     SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
     // one persistent CTA per SM; at least one chunk per warp

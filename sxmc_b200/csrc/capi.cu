@@ -28,6 +28,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
 static int g_smem_hist_max_bins = 8192;
 static int g_blocks_per_sm = 0;
 static int g_force_generic = 0;
+static int g_force_dynamic = 0;   // fast kernel with run-time systematic dispatch only
 static int g_timing = 0;
 static float g_last_bin_ms = -1.f, g_last_nll_ms = -1.f;
 static bool g_init_done = false;
@@ -281,6 +282,24 @@ static void plan_launch(Batch& b, int n) {
       L.lower[o] = b.host[0].lower[o]; L.upper[o] = b.host[0].upper[o];
       L.scale[o] = b.host[0].scale[o]; L.stride[o] = b.host[0].stride[o];
     }
+    // the systematic program, if every job runs the same one and a kernel was built for it
+    L.prog_nops = -1;
+    L.prog_codes = 0;
+    if (!g_force_dynamic) {
+      int nops = b.host[0].nsyst;
+      unsigned codes = 0;
+      bool same = true;
+      for (int j = 0; j < n && same; ++j) {
+        const BinJob& job = b.host[j];
+        if (job.nsyst != nops) { same = false; break; }
+        unsigned cj = 0;
+        for (int k = 0; k < job.nsyst; ++k)
+          cj |= (unsigned)(job.syst[k].type | (job.syst[k].obs_slot << 2) | (job.syst[k].extra_slot << 5)) << (8 * k);
+        if (j == 0) codes = cj;
+        else if (cj != codes) same = false;
+      }
+      if (same && bin_fast_has_program(L.nobs, max_slots, nops, codes)) { L.prog_nops = nops; L.prog_codes = codes; }
+    }
   }
   // work units: chunks of rows_per_stage rows (fast) or block-tiles of BIN_WARPS warp-tiles
   unsigned long long total = 0;
@@ -356,7 +375,8 @@ int sxmc_host_free(void* host) { if (host) SXMC_CUDA(cudaFreeHost(host)); return
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_generic) {
   if (smem_hist_max_bins >= 0) g_smem_hist_max_bins = std::min(smem_hist_max_bins, 56 * 1024);
   g_blocks_per_sm = blocks_per_sm;
-  g_force_generic = force_generic;
+  g_force_generic = force_generic & 1;
+  g_force_dynamic = (force_generic >> 1) & 1;
   return SXMC_OK;
 }
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }

@@ -21,6 +21,8 @@ struct BinLaunch {
   int nobs, nslots;
   int max_total_nbins;
   int blocks_per_sm;         // <=0: occupancy maximum (generic kernel)
+  int prog_nops;                 // >= 0: compile-time systematic program, < 0: run-time dispatch
+  unsigned prog_codes;
   int rows_per_stage, nstages;   // fast kernel pipeline shape
   unsigned stage_off;            // byte offset of the stages in dynamic shared memory
   size_t smem_bytes;
@@ -40,6 +42,7 @@ struct EvalPdfJob {
 };
 
 bool bin_fast_supported(int nobs, int nslots);
+bool bin_fast_has_program(int nobs, int nslots, int nops, unsigned codes);
 bool bin_fast_plan(int nslots, int hist_bins, int* R_out, int* S_out, unsigned* stage_off_out,
                    size_t* smem_out);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);

@@ -139,6 +139,7 @@ def test_eval_without_points_and_get_samples():
 # ---------------------------------------------------------------------------------------
 SMALL = [("A", 0.01), ("B", 0.02), ("C", 0.002), ("D", 0.003)]
 VARIANTS = [("smem", dict(smem_hist_max_bins=56 * 1024)), ("global", dict(smem_hist_max_bins=0)),
+            ("dynamic", dict(force_dynamic=True)), ("dynamic_global", dict(force_dynamic=True, smem_hist_max_bins=0)),
             ("generic", dict(force_generic=True)), ("generic_global", dict(force_generic=True, smem_hist_max_bins=0))]
 
 
@@ -146,7 +147,7 @@ VARIANTS = [("smem", dict(smem_hist_max_bins=56 * 1024)), ("global", dict(smem_h
 @pytest.mark.parametrize("name,scale", SMALL, ids=[s[0] for s in SMALL])
 def test_chain_eval_matches_oracle(name, scale, variant):
     from sxmc_b200 import mcmc, pdfz
-    pdfz.set_bin_tuning(**dict(dict(smem_hist_max_bins=8192, blocks_per_sm=0, force_generic=False),
+    pdfz.set_bin_tuning(**dict(dict(smem_hist_max_bins=8192, blocks_per_sm=0, force_generic=False, force_dynamic=False),
                                **variant[1]))
     fit = W.WORKLOADS[name](scale)
     hists, chain = mcmc.build_fit(fit)
