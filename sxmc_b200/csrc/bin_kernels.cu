@@ -19,11 +19,7 @@ namespace sxmc {
 
 // Per-launch geometry (identical for every job of a fast-path launch), passed by value so it
 // sits in the constant bank and costs no registers.
-struct Geo {
-  double lo[3], hi[3], sc[3];
-  int st[3];
-  int total_nbins;
-};
+typedef FastGeo Geo;
 
 struct SystRt {       // one systematic, resolved for the current parameter vector
   int type, obs, extra, npars;
@@ -118,7 +114,6 @@ __device__ __forceinline__ float4 ldg_stream(const float4* p) {
 // cases index the slot array with compile-time constants only, so the 4-sample working set
 // stays in registers (a loop with `if (s.obs != o) continue` gets rewritten by the compiler
 // into a dynamically indexed local-memory array).
-constexpr int FAST_MAX_OPS = 4;
 
 template <int NS, int O, int E>
 __device__ __forceinline__ void op_resolution(double (&f)[NS][4], const double c0) {
@@ -260,8 +255,12 @@ __device__ __forceinline__ float4 lds128(unsigned addr) {
 // needed in steady state.
 template <int NOBS, int NS, bool SMEM, int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(FAST_THREADS, 1)
-bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __restrict__ chunk_prefix,
-                int njobs, const Geo geo, const int R, const int S, const unsigned stage_off) {
+bin_fast_kernel(const __grid_constant__ FastParams P) {
+  const Geo& geo = P.geo;
+  const int R = P.R, S = P.S;
+  const unsigned stage_off = P.stage_off;
+  const int njobs = P.njobs;
+  const unsigned long long* chunk_prefix = P.prefix;   // constant bank: no global round trip
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ SystRt s_syst[SXMC_MAX_SYST];
   __shared__ __align__(8) unsigned long long s_bar[FAST_WARPS * FAST_MAX_STAGES];
@@ -289,33 +288,14 @@ bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __res
   unsigned it = 0;    // chunks this warp has consumed so far: stage = it % S, parity = (it / S) & 1
 
   while (t0 < t1) {
-    const BinJob& job = jobs[j];
+    const FastJob& job = P.job[j];
     const unsigned long long jbeg = chunk_prefix[j], jend = chunk_prefix[j + 1];
     const unsigned long long tend = t1 < jend ? t1 : jend;
     const int nsyst = job.nsyst;
-    if (threadIdx.x < nsyst) resolve_syst(job, threadIdx.x, s_syst[threadIdx.x], true);
-    if (SMEM)
-      for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) s_hist[b] = 0;
-    __syncthreads();
 
-    // the segment's systematics, in registers
-    int op_code[FAST_MAX_OPS];
-    double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
-#pragma unroll
-    for (int k = 0; k < FAST_MAX_OPS; ++k) {
-      op_code[k] = 0; op_c0[k] = 0.0; op_onep[k] = 1.0;
-      if (k < nsyst) {
-        op_code[k] = s_syst[k].type | (s_syst[k].obs << 4) | (s_syst[k].extra << 8);
-        op_c0[k] = s_syst[k].c0;
-        op_onep[k] = s_syst[k].onep;
-      }
-    }
-
-    unsigned* hist = SMEM ? s_hist : job.bins;
     const unsigned char* col[NS];
 #pragma unroll
-    for (int c = 0; c < NS; ++c)
-      col[c] = reinterpret_cast<const unsigned char*>(job.cols[job.slot_field[c]]);
+    for (int c = 0; c < NS; ++c) col[c] = reinterpret_cast<const unsigned char*>(job.col[c]);
 
     // this warp's contiguous chunk range [ca, cb) of the job (chunk c starts at byte c * col_bytes)
     const unsigned long long n = tend - t0;
@@ -329,8 +309,36 @@ bin_fast_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __res
 #pragma unroll
       for (int k = 0; k < NS; ++k) bulk_g2s(dst + k * col_bytes, col[k] + c * col_bytes, col_bytes, bar);
     };
+    // first thing in the segment: get the copies going (everything they need is in the
+    // constant bank); the parameter loads and the histogram clear overlap with them
     if (lane == 0)
       for (unsigned i = 0; i < (unsigned)S && ca + i < cb; ++i) issue(ca + i, (it + i) % (unsigned)S);
+
+    if (threadIdx.x < nsyst) {   // p = 0 + par * pow(x, 0)  (src/pdfz.cpp:310-314, npars <= 1)
+      SystRt& sr = s_syst[threadIdx.x];
+      const double par = job.npars[threadIdx.x]
+                             ? job.params[(long long)job.pidx[threadIdx.x] * job.param_stride] : 0.0;
+      sr.c0 = __dadd_rn(0.0, __dmul_rn(par, 1.0));
+      sr.onep = __dadd_rn(1.0, sr.c0);
+    }
+    if (SMEM)
+      for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) s_hist[b] = 0;
+    __syncthreads();
+
+    // the segment's systematics, in registers
+    int op_code[FAST_MAX_OPS];
+    double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
+#pragma unroll
+    for (int k = 0; k < FAST_MAX_OPS; ++k) {
+      op_code[k] = 0; op_c0[k] = 0.0; op_onep[k] = 1.0;
+      if (k < nsyst) {
+        op_code[k] = job.code[k];
+        op_c0[k] = s_syst[k].c0;
+        op_onep[k] = s_syst[k].onep;
+      }
+    }
+
+    unsigned* hist = SMEM ? s_hist : job.bins;
 
     RunAcc acc;
     acc.norm = 0;
@@ -465,7 +473,7 @@ bin_generic_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __
 // =========================================================================================
 // launch dispatch
 // =========================================================================================
-typedef void (*FastKernel)(const BinJob*, const unsigned long long*, int, const Geo, int, int, unsigned);
+typedef void (*FastKernel)(const FastParams);
 
 #define OPC(type, obs, ext) ((unsigned)((type) | ((obs) << 2) | ((ext) << 5)))
 struct FastEntry {
@@ -545,18 +553,41 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
     FastKernel fk = pick_fast(L.nobs, L.nslots, L.prog_nops, L.prog_codes, L.smem_hist);
     if (!fk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
     SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
-    // one persistent CTA per SM; at least one chunk per warp
-    unsigned long long grid = (unsigned long long)num_sms();
-    const unsigned long long max_grid = (L.total_units + FAST_WARPS - 1) / FAST_WARPS;
-    if (grid > max_grid) grid = max_grid;
-    Geo g;
-    for (int i = 0; i < 3; ++i) {
-      g.lo[i] = L.lower[i]; g.hi[i] = L.upper[i]; g.sc[i] = L.scale[i]; g.st[i] = L.stride[i];
+    // jobs travel in the kernel parameters (constant bank), FAST_MAX_JOBS per launch
+    for (int g0 = 0; g0 < L.njobs; g0 += FAST_MAX_JOBS) {
+      const int ng = L.njobs - g0 < FAST_MAX_JOBS ? L.njobs - g0 : FAST_MAX_JOBS;
+      FastParams P;
+      memset(&P, 0, sizeof P);
+      for (int i = 0; i < 3; ++i) {
+        P.geo.lo[i] = L.lower[i]; P.geo.hi[i] = L.upper[i]; P.geo.sc[i] = L.scale[i]; P.geo.st[i] = L.stride[i];
+      }
+      P.geo.total_nbins = L.max_total_nbins;
+      P.R = L.rows_per_stage; P.S = L.nstages; P.stage_off = L.stage_off; P.njobs = ng;
+      unsigned long long total = 0;
+      P.prefix[0] = 0;
+      for (int j = 0; j < ng; ++j) {
+        const BinJob& src = L.jobs_host[g0 + j];
+        FastJob& d = P.job[j];
+        for (int c = 0; c < MAX_SLOTS; ++c) d.col[c] = src.cols[src.slot_field[c < src.nslots ? c : 0]];
+        d.bins = src.bins; d.norm = src.norm; d.params = src.params;
+        d.param_stride = (int)src.param_stride;
+        d.nsyst = src.nsyst;
+        for (int k = 0; k < src.nsyst && k < FAST_MAX_OPS; ++k) {
+          d.code[k] = (unsigned short)(src.syst[k].type | (src.syst[k].obs_slot << 4) | (src.syst[k].extra_slot << 8));
+          d.pidx[k] = src.syst[k].pidx[0];
+          d.npars[k] = (unsigned char)(src.syst[k].npars > 0);
+        }
+        total += src.nwtiles * (unsigned long long)(WT_ROWS / L.rows_per_stage);
+        P.prefix[j + 1] = total;
+      }
+      if (total == 0) continue;
+      // one persistent CTA per SM; at least one chunk per warp
+      unsigned long long grid = (unsigned long long)num_sms();
+      const unsigned long long max_grid = (total + FAST_WARPS - 1) / FAST_WARPS;
+      if (grid > max_grid) grid = max_grid;
+      fk<<<(unsigned)grid, FAST_THREADS, L.smem_bytes, stream>>>(P);
+      SXMC_CUDA(cudaGetLastError());
     }
-    g.total_nbins = L.max_total_nbins;
-    fk<<<(unsigned)grid, FAST_THREADS, L.smem_bytes, stream>>>(L.jobs_dev, L.prefix_dev, L.njobs, g,
-                                                               L.rows_per_stage, L.nstages, L.stage_off);
-    SXMC_CUDA(cudaGetLastError());
     return SXMC_OK;
   }
   const size_t smem = L.smem_hist ? sizeof(unsigned) * (size_t)L.max_total_nbins : 0;

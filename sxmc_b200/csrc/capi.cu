@@ -236,6 +236,7 @@ static int fill_job(sxmc_hist* h, BinJob& job, unsigned* bins, unsigned* norm, c
 static void plan_launch(Batch& b, int n) {
   BinLaunch& L = b.launch;
   memset(&L, 0, sizeof L);
+  L.jobs_host = b.host;
   L.jobs_dev = b.dev;
   L.prefix_dev = b.prefix_dev;
   L.njobs = n;
@@ -743,7 +744,10 @@ static int chain_bin(sxmc_chain* c, int b) {
 static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut) {
   NllLaunch L;
   L.sigs_dev = c->sigs_dev[b];
+  L.norms_dev = c->hist_buf[b] + (size_t)c->nsignals * c->total_nbins;
   L.nsignals = c->nsignals;
+  L.nparameters = c->nparameters;
+  L.nsources = c->nsources;
   L.nevents = (long long)c->nevents;
   L.state = c->st_dev;
   L.partials = c->partials;

@@ -59,6 +59,34 @@ struct BinJob {
   SystDesc syst[SXMC_MAX_SYST];
 };
 
+// Per-launch description of the fast binning kernel, passed BY VALUE (kernel parameters live in
+// the constant bank: a CTA can issue its first bulk copy without a single global load).
+constexpr int FAST_MAX_JOBS = 32;
+constexpr int FAST_MAX_OPS = 4;
+struct FastGeo {
+  double lo[3], hi[3], sc[3];
+  int st[3];
+  int total_nbins;
+};
+struct FastJob {
+  const float* col[MAX_SLOTS];   // register slot -> column (tiled layout)
+  unsigned* bins;
+  unsigned* norm;
+  const double* params;
+  int param_stride;
+  int nsyst;
+  unsigned short code[FAST_MAX_OPS];   // type | obs_slot << 4 | extra_slot << 8
+  short pidx[FAST_MAX_OPS];            // coefficient index of each systematic
+  unsigned char npars[FAST_MAX_OPS];   // 0: the systematic has no coefficient (p = 0)
+};
+struct FastParams {
+  unsigned long long prefix[FAST_MAX_JOBS + 1];   // chunk prefix sums
+  FastJob job[FAST_MAX_JOBS];
+  FastGeo geo;
+  int njobs, R, S;
+  unsigned stage_off;
+};
+
 // One signal as seen by the lookup + event-likelihood kernel.
 struct NllSignal {
   const unsigned* bins;       // histogram of this step

@@ -11,6 +11,7 @@ struct PrepGeo {     // histogram geometry passed by value to the small preparat
 };
 
 struct BinLaunch {
+  const BinJob* jobs_host;   // the same table on the host (the fast kernel takes it by value)
   const BinJob* jobs_dev;
   const unsigned long long* prefix_dev;   // [njobs+1] prefix sums of work units: chunks of
                                           // rows_per_stage rows (fast) / 8-warp-tile block-tiles (generic)
@@ -58,7 +59,8 @@ int launch_eval_pdf(const EvalPdfJob* jobs_dev, int njobs, long long max_points,
 // ---- nll_kernels.cu ----
 struct NllLaunch {
   const NllSignal* sigs_dev;
-  int nsignals;
+  const unsigned* norms_dev;    // [nsignals] in-domain counts of this step (== sigs[j].norm)
+  int nsignals, nparameters, nsources;
   long long nevents;
   ChainState* state;            // device
   double* partials;             // [grid] device
