@@ -202,9 +202,14 @@ int sxmc_chain_nll_at(sxmc_chain* c, const double* pars, int rebin, double* nll_
 int sxmc_chain_get_norms(sxmc_chain* c, unsigned* norms_out);
 int sxmc_chain_get_lut(sxmc_chain* c, float* lut_out);
 int sxmc_chain_get_bins(sxmc_chain* c, unsigned* bins_out);   /* [nsignals][total_nbins] */
-/* chain execution mode: 0 = CUDA graph of the per-step kernel sequence (default),
- * 1 = plain stream launches (debugging / profiling). */
+/* chain execution mode: 0 = automatic (default): the persistent cooperative chain kernel
+ * when a step streams < 64 MB (the fit is latency-bound), else a CUDA graph of the per-step
+ * kernel sequence; 1 = plain stream launches (debugging / profiling); 2 = persistent kernel
+ * or fail; 3 = CUDA graph.  Sample-sharded chains (sxmc_chain_set_comm) never run persistent. */
 int sxmc_chain_set_mode(sxmc_chain* c, int mode);
+/* profiling hook of the persistent kernel: CTA 0 stamps %globaltimer at 8 phase boundaries of
+ * the first 64 steps of each launch; out64x8 (may be NULL) receives the last launch's stamps. */
+int sxmc_chain_phase_stamps(sxmc_chain* c, int enable, unsigned long long* out64x8);
 
 /* ---- multi-GPU (no reference counterpart) ------------------------------- */
 int sxmc_comm_unique_id(void* id128_out);                 /* ncclGetUniqueId, 128 bytes */

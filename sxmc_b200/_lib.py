@@ -99,6 +99,7 @@ SYMBOLS = {
     "sxmc_chain_get_lut": (C.c_int, [c_vp, c_fp]),
     "sxmc_chain_get_bins": (C.c_int, [c_vp, c_up]),
     "sxmc_chain_set_mode": (C.c_int, [c_vp, C.c_int]),
+    "sxmc_chain_phase_stamps": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_uint64)]),
     "sxmc_comm_unique_id": (C.c_int, [c_vp]),
     "sxmc_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "sxmc_comm_destroy": (C.c_int, [c_vp]),

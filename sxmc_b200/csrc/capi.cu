@@ -28,7 +28,8 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
 static int g_smem_hist_max_bins = 8192;
 static int g_blocks_per_sm = 0;
 static int g_force_generic = 0;
-static int g_force_dynamic = 0;   // fast kernel with run-time systematic dispatch only
+static int g_force_dynamic = 0;
+static long long g_persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent   // fast kernel with run-time systematic dispatch only
 static int g_timing = 0;
 static float g_last_bin_ms = -1.f, g_last_nll_ms = -1.f;
 static bool g_init_done = false;
@@ -267,10 +268,11 @@ static void plan_launch(Batch& b, int n) {
   if (L.fast) {
     // pipeline stages share the shared memory with the privatised histogram; when the
     // histogram leaves no room for them it stays in global memory (L2 atomics)
-    if (!(L.smem_hist && bin_fast_plan(max_slots, max_bins, &L.rows_per_stage, &L.nstages,
-                                       &L.stage_off, &L.smem_bytes))) {
+    if (!(L.smem_hist && bin_fast_plan(max_slots, max_bins, BIN_STATIC_RESERVE, &L.rows_per_stage,
+                                       &L.nstages, &L.stage_off, &L.smem_bytes))) {
       L.smem_hist = false;
-      bin_fast_plan(max_slots, 0, &L.rows_per_stage, &L.nstages, &L.stage_off, &L.smem_bytes);
+      bin_fast_plan(max_slots, 0, BIN_STATIC_RESERVE, &L.rows_per_stage, &L.nstages, &L.stage_off,
+                    &L.smem_bytes);
     }
     // every job of a fast launch uses the same slot count (columns it does not need are
     // simply re-reads of observable 0)
@@ -691,6 +693,12 @@ struct sxmc_chain {
   cudaGraphExec_t graph_exec = nullptr;   // GRAPH_STEPS steps; rebuilt when the tables change
   long graph_launches = 0;
   void* flush_buf = nullptr; size_t flush_bytes = 0;
+  double* bcast_dev = nullptr;      // persistent kernel: proposed-vector mailbox [2][MAX_PARAMETERS]
+  unsigned* sync_dev = nullptr;     // persistent kernel: barrier counters, go, abort
+  unsigned* sync_host = nullptr;    // pinned readback of the above
+  long long step_bytes = 0;         // algorithmic bytes one binning pass streams
+  bool used_persistent = false;
+  unsigned long long* stamps_dev = nullptr;   // persistent kernel phase stamps (profiling hook)
   std::vector<cudaEvent_t> tev;
 };
 
@@ -702,6 +710,7 @@ static void chain_drop_graph(sxmc_chain* c) {
 
 static int chain_build_tables(sxmc_chain* c) {
   const int ns = c->nsignals;
+  c->step_bytes = 0;
   for (int b = 0; b < 2; ++b) {
     SXMC_TRY(c->batch[b].reserve(ns));
     unsigned* bins = c->hist_buf[b];
@@ -722,6 +731,10 @@ static int chain_build_tables(sxmc_chain* c) {
     }
     c->batch[b].n_ep = 0;
     plan_launch(c->batch[b], ns);
+    if (b == 0)
+      for (int j = 0; j < ns; ++j)
+        c->step_bytes += (long long)c->batch[0].host[j].nwtiles * WT_SAMPLES * 4ll *
+                         std::max(1, c->batch[0].host[j].nslots);
     SXMC_TRY(upload_batch(c->batch[b], ns, c->stream));
     SXMC_CUDA(cudaMemcpyAsync(c->sigs_dev[b], sg.data(), sizeof(NllSignal) * ns, cudaMemcpyHostToDevice, c->stream));
     SXMC_CUDA(cudaStreamSynchronize(c->stream));
@@ -866,6 +879,9 @@ int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out) {
   }
   if (e == cudaSuccess) e = cudaMalloc(&c->partials, sizeof(double) * 148 * 8);
   if (e == cudaSuccess) e = cudaMalloc(&c->ticket, sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMalloc(&c->bcast_dev, sizeof(double) * 2 * SXMC_MAX_PARAMETERS);
+  if (e == cudaSuccess) e = cudaMalloc(&c->sync_dev, sizeof(unsigned) * 4);
+  if (e == cudaSuccess) e = cudaMallocHost(&c->sync_host, sizeof(unsigned) * 4);
   if (e == cudaSuccess) e = cudaMemset(c->ticket, 0, sizeof(unsigned));
   if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
@@ -879,6 +895,8 @@ int sxmc_chain_destroy(sxmc_chain* c) {
   if (c->stream) cudaStreamSynchronize(c->stream);
   chain_drop_graph(c);
   cudaFree(c->flush_buf);
+  cudaFree(c->bcast_dev); cudaFree(c->sync_dev); cudaFree(c->stamps_dev);
+  if (c->sync_host) cudaFreeHost(c->sync_host);
   for (auto& e : c->tev) cudaEventDestroy(e);
   cudaFree(c->st_dev);
   if (c->st_host) cudaFreeHost(c->st_host);
@@ -912,6 +930,16 @@ int sxmc_chain_set_tapes(sxmc_chain* c, const double* normals, size_t n_normals,
 
 int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm) { chain_drop_graph(c); c->comm = comm; return SXMC_OK; }
 int sxmc_chain_set_mode(sxmc_chain* c, int mode) { c->mode = mode; return SXMC_OK; }
+int sxmc_chain_phase_stamps(sxmc_chain* c, int enable, unsigned long long* out64x8) {
+  if (enable && !c->stamps_dev) {
+    SXMC_CUDA(cudaMalloc(&c->stamps_dev, sizeof(unsigned long long) * 64 * 8));
+    SXMC_CUDA(cudaMemset(c->stamps_dev, 0, sizeof(unsigned long long) * 64 * 8));
+  }
+  if (out64x8 && c->stamps_dev)
+    SXMC_CUDA(cudaMemcpy(out64x8, c->stamps_dev, sizeof(unsigned long long) * 64 * 8, cudaMemcpyDeviceToHost));
+  if (!enable && c->stamps_dev) { cudaFree(c->stamps_dev); c->stamps_dev = nullptr; }
+  return SXMC_OK;
+}
 int sxmc_chain_enable_trace(sxmc_chain* c, int on) { c->trace = on != 0; return SXMC_OK; }
 
 int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
@@ -1049,13 +1077,57 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
   const bool has_comm = c->comm && c->comm->nranks > 1;
   const unsigned GRAPH_STEPS = 16;   // even: the histogram double-buffer parity is preserved
   unsigned left = nsteps;
+  // Small fits: the whole segment in one cooperative launch (chain_kernels.cu).  Chosen when a
+  // step is too short for per-kernel launches to be hidden (the samples fit in L2).
+  c->used_persistent = false;
+  const BinLaunch& BL = c->batch[0].launch;
+  const bool persistent_ok = BL.fast && BL.njobs <= FAST_MAX_JOBS && !has_comm && c->nsignals <= 128 &&
+                             c->pdfs.size() && nsteps > 0;
+  const bool want_persistent = c->mode == 2 || (c->mode == 0 && c->step_bytes <= g_persistent_max_bytes);
+  if (persistent_ok && want_persistent) {
+    PersistParams Q;
+    memset(&Q, 0, sizeof Q);
+    Q.st = c->st_dev;
+    Q.sigs = c->sigs_dev[0];
+    Q.hist_buf[0] = c->hist_buf[0];
+    Q.hist_buf[1] = c->hist_buf[1];
+    Q.hist_words = c->hist_words;
+    Q.partials = c->partials;
+    Q.bcast = c->bcast_dev;
+    Q.sync = c->sync_dev;
+    Q.nevents = (long long)c->nevents;
+    Q.ns = c->nsignals; Q.np = c->nparameters; Q.nsources = c->nsources;
+    Q.nsteps = nsteps;
+    Q.step0 = c->steps_done;
+    Q.rebin = rebin ? 1 : 0;
+    Q.stamps = c->stamps_dev;
+    SXMC_CUDA(cudaMemsetAsync(c->sync_dev, 0, sizeof(unsigned) * 4, c->stream));
+    SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
+    int rc = launch_chain_persistent(BL, Q, c->stream);
+    if (rc == SXMC_OK) {
+      SXMC_CUDA(cudaEventRecord(c->ev1, c->stream));
+      SXMC_CUDA(cudaMemcpyAsync(c->sync_host, c->sync_dev, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost, c->stream));
+      SXMC_CUDA(cudaStreamSynchronize(c->stream));
+      if (c->sync_host[3]) { set_error("persistent chain kernel timed out at a grid barrier"); return SXMC_ESTATE; }
+      float ms = 0;
+      SXMC_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+      c->loop_ms += ms;
+      c->launches += 1;
+      c->steps_done += nsteps;
+      if (rebin && c->steps_done > 0) c->last_buf = (int)(c->steps_done & 1);
+      c->used_persistent = true;
+      return SXMC_OK;
+    }
+    if (c->mode == 2) return rc;     // explicitly requested: report why it cannot run
+    cudaGetLastError();              // automatic: fall through to the graph path
+  }
   auto plain_step = [&]() -> int {
     const unsigned i = c->steps_done;
     int rc = chain_enqueue_step(c, rebin, rebin ? (int)((i + 1) & 1) : 0);
     if (!rc) { c->steps_done += 1; left -= 1; }
     return rc;
   };
-  if (c->mode == 0 && left >= 2 * GRAPH_STEPS && !c->graph_exec) {
+  if ((c->mode == 0 || c->mode == 3) && left >= 2 * GRAPH_STEPS && !c->graph_exec) {
     // CUDA graph of GRAPH_STEPS consecutive steps starting at an even step index
     cudaGraph_t graph = nullptr;
     const long before = c->launches;
@@ -1073,7 +1145,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
     if (e != cudaSuccess) { c->graph_exec = nullptr; return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__); }
   }
   SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
-  if (c->mode == 0 && c->graph_exec) {
+  if ((c->mode == 0 || c->mode == 3) && c->graph_exec) {
     if ((c->steps_done & 1u) && left > 0) SXMC_TRY(plain_step());
     while (left >= GRAPH_STEPS) {
       SXMC_CUDA(cudaGraphLaunch(c->graph_exec, c->stream));

@@ -87,6 +87,25 @@ struct FastParams {
   unsigned stage_off;
 };
 
+// Arguments of the persistent chain kernel (chain_kernels.cu), by value.
+struct ChainState;
+struct NllSignal;
+struct PersistParams {
+  ChainState* st;
+  const NllSignal* sigs;        // static per-signal fields (read_bins, nexpected, bin_volume, n_mc, source_id)
+  unsigned* hist_buf[2];        // [nsignals][total_nbins] + norms[nsignals], double-buffered
+  unsigned long long hist_words;
+  double* partials;             // [grid] per-CTA event sums
+  double* bcast;                // [2][SXMC_MAX_PARAMETERS] proposed vector by step parity
+  unsigned* sync;               // [0] bin barrier, [1] lookup arrivals, [2] go, [3] abort
+  long long nevents;
+  int ns, np, nsources;
+  unsigned nsteps;              // steps in this launch
+  unsigned step0;               // chain index of the first one (histogram buffer parity)
+  int rebin;
+  unsigned long long* stamps;   // optional [64][8] phase timestamps of CTA 0 (ns), profiling only
+};
+
 // One signal as seen by the lookup + event-likelihood kernel.
 struct NllSignal {
   const unsigned* bins;       // histogram of this step

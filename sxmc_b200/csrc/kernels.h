@@ -44,8 +44,13 @@ struct EvalPdfJob {
 
 bool bin_fast_supported(int nobs, int nslots);
 bool bin_fast_has_program(int nobs, int nslots, int nops, unsigned codes);
-bool bin_fast_plan(int nslots, int hist_bins, int* R_out, int* S_out, unsigned* stage_off_out,
-                   size_t* smem_out);
+bool bin_fast_plan(int nslots, int hist_bins, size_t static_reserve, int* R_out, int* S_out,
+                   unsigned* stage_off_out, size_t* smem_out);
+constexpr size_t BIN_STATIC_RESERVE = 2048;   // static shared memory of bin_fast_kernel
+// FastParams of jobs [g0, g0+ng) of a planned launch; *total_out = their chunk count
+void build_fast_params(const BinLaunch& L, int g0, int ng, FastParams& P, unsigned long long* total_out);
+// chain_kernels.cu
+int launch_chain_persistent(const BinLaunch& L, const PersistParams& Q, cudaStream_t stream);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);
 int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,
                    const PrepGeo& g, int primary, bool sort, float* cols_dev,

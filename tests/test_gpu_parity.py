@@ -259,7 +259,7 @@ def test_empty_and_ragged_inputs():
 # ---------------------------------------------------------------------------------------
 # chains
 # ---------------------------------------------------------------------------------------
-@pytest.mark.parametrize("mode", [0, 1], ids=["graph", "stream"])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3], ids=["auto", "stream", "persistent", "graph"])
 def test_tape_driven_chain_matches_oracle_chain(mode):
     """Same random numbers in => same accept/reject sequence and the same float rows out."""
     from sxmc_b200 import mcmc
