@@ -208,7 +208,8 @@ int sxmc_chain_get_bins(sxmc_chain* c, unsigned* bins_out);   /* [nsignals][tota
  * or fail; 3 = CUDA graph.  Sample-sharded chains (sxmc_chain_set_comm) never run persistent. */
 int sxmc_chain_set_mode(sxmc_chain* c, int mode);
 /* profiling hook of the persistent kernel: CTA 0 stamps %globaltimer at 8 phase boundaries of
- * the first 64 steps of each launch; out64x8 (may be NULL) receives the last launch's stamps. */
+ * the first 64 steps of each launch ([64][8] ns), followed at index 512 by [ncta][4] stamps of
+ * every CTA in step 20; out64x8 (may be NULL, else 2048 entries) receives the last launch's. */
 int sxmc_chain_phase_stamps(sxmc_chain* c, int enable, unsigned long long* out64x8);
 
 /* ---- multi-GPU (no reference counterpart) ------------------------------- */

@@ -271,13 +271,45 @@ __device__ __forceinline__ void fast_ctx_init(FastCtx& cx, const FastParams& P, 
   __syncthreads();
 }
 
+// This CTA's chunk range [t0, t1) in the concatenated chunk sequence and the job t0 falls in.
+__device__ __forceinline__ void fast_partition(const FastParams& P, unsigned long long& t0,
+                                               unsigned long long& t1, int& j) {
+  const unsigned long long* chunk_prefix = P.prefix;
+  j = 0;
+  if (P.aligned) {
+    const unsigned b = blockIdx.x;
+    while (j < P.njobs && P.cta_first[j + 1] <= b) ++j;
+    if (j >= P.njobs) { t0 = t1 = 0; return; }
+    const unsigned long long nj = chunk_prefix[j + 1] - chunk_prefix[j];
+    const unsigned cj = P.cta_first[j + 1] - P.cta_first[j], k = b - P.cta_first[j];
+    t0 = chunk_prefix[j] + nj * k / cj;
+    t1 = chunk_prefix[j] + nj * (k + 1ull) / cj;
+    return;
+  }
+  const unsigned long long total = chunk_prefix[P.njobs];
+  t0 = total * blockIdx.x / gridDim.x;
+  t1 = total * (blockIdx.x + 1ull) / gridDim.x;
+  if (t0 >= t1) return;
+  while (chunk_prefix[j + 1] <= t0) ++j;
+}
+
 // One pass over this CTA's share of all jobs.  hist_base != nullptr redirects the outputs to a
 // concatenated buffer [njobs][total_nbins] + norms[njobs]; params_override != nullptr replaces
 // every job's parameter buffer (may point to shared memory).
 template <int NOBS, int NS, bool SMEM, int NOPS, unsigned CODES>
 __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, unsigned* s_hist,
-                                              SystRt* s_syst, unsigned* hist_base,
-                                              const double* params_override) {
+                                              SystRt* s_syst, unsigned* s_norm, unsigned* hist_base,
+                                              const double* params_override,
+                                              unsigned long long* dbg = nullptr) {
+#define BIN_DBG(slot)                                                                  \
+  do {                                                                                 \
+    if (dbg && threadIdx.x == 0) {                                                     \
+      unsigned long long t_;                                                           \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                           \
+      dbg[slot] = t_;                                                                  \
+    }                                                                                  \
+  } while (0)
+  BIN_DBG(0);
   const Geo& geo = P.geo;
   const int R = P.R, S = P.S;
   const int njobs = P.njobs;
@@ -290,12 +322,10 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
   const bool reuse = cx.resident && cx.loaded;            // the stages already hold this warp's chunks
   unsigned it = cx.resident ? 0u : cx.it;
 
-  const unsigned long long total = chunk_prefix[njobs];
-  unsigned long long t0 = total * blockIdx.x / gridDim.x;
-  const unsigned long long t1 = total * (blockIdx.x + 1ull) / gridDim.x;
-  if (t0 >= t1) return;
+  unsigned long long t0, t1;
   int j = 0;
-  while (chunk_prefix[j + 1] <= t0) ++j;
+  fast_partition(P, t0, t1, j);
+  if (t0 >= t1) return;
 
   while (t0 < t1) {
     const FastJob& job = P.job[j];
@@ -335,6 +365,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     if (SMEM)
       for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) s_hist[b] = 0;
     __syncthreads();
+    BIN_DBG(1);
 
     // the segment's systematics, in registers
     int op_code[FAST_MAX_OPS];
@@ -394,17 +425,26 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
       if (lane == 0 && !reuse && c + (unsigned)S < cb) issue(c + (unsigned)S, slot);
     }
     run_flush<SMEM>(acc, hist, geo.total_nbins);
+    BIN_DBG(2);
 
+    // in-domain count: one global atomic per CTA and segment (all CTAs of a signal hit the
+    // same address; per-warp atomics serialise in L2 and dominate small fits)
     const unsigned wnorm = __reduce_add_sync(0xffffffffu, acc.norm);
-    if (lane == 0 && wnorm) atomicAdd(job_norm, wnorm);
+    if (lane == 0 && wnorm) atomicAdd(s_norm, wnorm);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned cn = *s_norm;
+      if (cn) atomicAdd(job_norm, cn);
+      *s_norm = 0u;
+    }
     if (SMEM) {
-      __syncthreads();
       for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) {
         const unsigned cnt = s_hist[b];
         if (cnt) atomicAdd(job_bins + b, cnt);
       }
     }
-    __syncthreads();   // s_syst / s_hist are rewritten by the next segment
+    __syncthreads();   // s_syst / s_hist / s_norm are rewritten by the next segment
+    BIN_DBG(3);
     t0 = tend;
     ++j;
   }
@@ -418,10 +458,12 @@ bin_fast_kernel(const __grid_constant__ FastParams P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ SystRt s_syst[SXMC_MAX_SYST];
   __shared__ __align__(8) unsigned long long s_bar[FAST_WARPS * FAST_MAX_STAGES];
+  __shared__ unsigned s_norm;
+  if (threadIdx.x == 0) s_norm = 0u;
   FastCtx cx;
   fast_ctx_init<NS>(cx, P, smem_raw, s_bar);
   fast_bin_pass<NOBS, NS, SMEM, NOPS, CODES>(P, cx, reinterpret_cast<unsigned*>(smem_raw), s_syst,
-                                             nullptr, nullptr);
+                                             &s_norm, nullptr, nullptr);
 }
 
 // the programs kernels are instantiated for (bin_kernels.cu and chain_kernels.cu)

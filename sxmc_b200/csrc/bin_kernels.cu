@@ -12,6 +12,7 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <algorithm>
 #include <cstring>
 
 namespace sxmc {
@@ -150,7 +151,8 @@ static int num_sms() {
   return g_num_sms;
 }
 
-void build_fast_params(const BinLaunch& L, int g0, int ng, FastParams& P, unsigned long long* total_out) {
+void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams& P,
+                       unsigned long long* total_out) {
   memset(&P, 0, sizeof P);
   for (int i = 0; i < 3; ++i) {
     P.geo.lo[i] = L.lower[i]; P.geo.hi[i] = L.upper[i]; P.geo.sc[i] = L.scale[i]; P.geo.st[i] = L.stride[i];
@@ -175,6 +177,38 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, FastParams& P, unsign
     P.prefix[j + 1] = total;
   }
   *total_out = total;
+  // Small fits: give every job whole CTAs (no CTA spans two jobs).  Big fits keep the even
+  // split, whose balance is perfect and whose second segment costs nothing in proportion.
+  P.aligned = 0;
+  int nonempty = 0;
+  for (int j = 0; j < ng; ++j) nonempty += P.prefix[j + 1] > P.prefix[j];
+  if (total > 0 && nonempty <= grid && total / ((unsigned long long)grid * FAST_WARPS) < 32) {
+    int cta[FAST_MAX_JOBS];
+    int used = 0;
+    for (int j = 0; j < ng; ++j) {
+      const unsigned long long nj = P.prefix[j + 1] - P.prefix[j];
+      cta[j] = nj ? (int)std::max<unsigned long long>(1, nj * grid / total) : 0;
+      used += cta[j];
+    }
+    while (used != grid) {      // hand out / take back CTAs where it changes the load least
+      int best = -1;
+      double score = 0;
+      for (int j = 0; j < ng; ++j) {
+        const unsigned long long nj = P.prefix[j + 1] - P.prefix[j];
+        if (!nj || (used > grid && cta[j] <= 1)) continue;
+        const double load = used < grid ? (double)nj / cta[j] : -(double)nj / (cta[j] - 1);
+        if (best < 0 || load > score) { best = j; score = load; }
+      }
+      if (best < 0) break;
+      cta[best] += used < grid ? 1 : -1;
+      used += used < grid ? 1 : -1;
+    }
+    if (used == grid) {
+      P.cta_first[0] = 0;
+      for (int j = 0; j < ng; ++j) P.cta_first[j + 1] = (unsigned short)(P.cta_first[j] + cta[j]);
+      P.aligned = 1;
+    }
+  }
 }
 
 int launch_bin(const BinLaunch& L, cudaStream_t stream) {
@@ -188,12 +222,13 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
       const int ng = L.njobs - g0 < FAST_MAX_JOBS ? L.njobs - g0 : FAST_MAX_JOBS;
       FastParams P;
       unsigned long long total = 0;
-      build_fast_params(L, g0, ng, P, &total);
+      build_fast_params(L, g0, ng, 0, P, &total);
       if (total == 0) continue;
       // one persistent CTA per SM; at least one chunk per warp
       unsigned long long grid = (unsigned long long)num_sms();
       const unsigned long long max_grid = (total + FAST_WARPS - 1) / FAST_WARPS;
       if (grid > max_grid) grid = max_grid;
+      build_fast_params(L, g0, ng, (int)grid, P, &total);
       fk<<<(unsigned)grid, FAST_THREADS, L.smem_bytes, stream>>>(P);
       SXMC_CUDA(cudaGetLastError());
     }

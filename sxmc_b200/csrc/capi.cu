@@ -932,11 +932,11 @@ int sxmc_chain_set_comm(sxmc_chain* c, sxmc_comm* comm) { chain_drop_graph(c); c
 int sxmc_chain_set_mode(sxmc_chain* c, int mode) { c->mode = mode; return SXMC_OK; }
 int sxmc_chain_phase_stamps(sxmc_chain* c, int enable, unsigned long long* out64x8) {
   if (enable && !c->stamps_dev) {
-    SXMC_CUDA(cudaMalloc(&c->stamps_dev, sizeof(unsigned long long) * 64 * 8));
-    SXMC_CUDA(cudaMemset(c->stamps_dev, 0, sizeof(unsigned long long) * 64 * 8));
+    SXMC_CUDA(cudaMalloc(&c->stamps_dev, sizeof(unsigned long long) * 2048));
+    SXMC_CUDA(cudaMemset(c->stamps_dev, 0, sizeof(unsigned long long) * 2048));
   }
   if (out64x8 && c->stamps_dev)
-    SXMC_CUDA(cudaMemcpy(out64x8, c->stamps_dev, sizeof(unsigned long long) * 64 * 8, cudaMemcpyDeviceToHost));
+    SXMC_CUDA(cudaMemcpy(out64x8, c->stamps_dev, sizeof(unsigned long long) * 2048, cudaMemcpyDeviceToHost));
   if (!enable && c->stamps_dev) { cudaFree(c->stamps_dev); c->stamps_dev = nullptr; }
   return SXMC_OK;
 }

@@ -49,6 +49,13 @@ constexpr unsigned PK_STAMP_STEPS = 64;
     if (Q.stamps && blockIdx.x == 0 && threadIdx.x == 0 && s < PK_STAMP_STEPS)               \
       Q.stamps[s * 8 + (slot)] = globaltimer_ns();                                           \
   } while (0)
+// per-CTA stamps of step PK_CTA_STEP: stamps[512 + blockIdx * 4 + slot]
+constexpr unsigned PK_CTA_STEP = 20;
+#define PK_CTA_STAMP(slot)                                                                    \
+  do {                                                                                        \
+    if (Q.stamps && threadIdx.x == 0 && s == PK_CTA_STEP && blockIdx.x < 256)                 \
+      Q.stamps[512 + blockIdx.x * 4 + (slot)] = globaltimer_ns();                             \
+  } while (0)
 __device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -98,6 +105,10 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
   __shared__ double s_term[PK_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
   __shared__ FinState F;
   __shared__ int s_ok;
+  __shared__ double s_z[SXMC_MAX_PARAMETERS];   // this step's normals / uniform, drawn ahead of the tail
+  __shared__ double s_u;
+  __shared__ unsigned s_norm;
+  if (threadIdx.x == 0) s_norm = 0u;
   unsigned* s_hist = reinterpret_cast<unsigned*>(smem_raw);
 
   const int tid = threadIdx.x;
@@ -113,11 +124,9 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
   FastCtx cx;
   fast_ctx_init<NS>(cx, P, smem_raw, s_bar);
   {  // does every chunk of this warp fit in its stages?  (same partition as fast_bin_pass)
-    const unsigned long long total = P.prefix[P.njobs];
-    unsigned long long t0 = total * blockIdx.x / G;
-    const unsigned long long t1 = total * (blockIdx.x + 1ull) / G;
-    unsigned long long mine = 0;
+    unsigned long long t0, t1, mine = 0;
     int j = 0;
+    fast_partition(P, t0, t1, j);
     while (t0 < t1) {
       while (P.prefix[j + 1] <= t0) ++j;
       const unsigned long long jend = P.prefix[j + 1];
@@ -142,6 +151,7 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
 
   const long long gtid = blockIdx.x * (long long)FAST_THREADS + tid;
   const long long gstride = (long long)G * FAST_THREADS;
+  const long long etid = (long long)tid * G + blockIdx.x;   // events spread over all CTAs
 
   for (unsigned s = 0; s < Q.nsteps; ++s) {
     const unsigned istep = Q.step0 + s;
@@ -150,18 +160,34 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
 
     // ---- bin ------------------------------------------------------------------------------
     PK_STAMP(0);
+    PK_CTA_STAMP(0);
     if (Q.rebin) {
-      fast_bin_pass<NOBS, NS, SMEM, NOPS, CODES>(P, cx, s_hist, s_syst, hb, F.proposed + nsources);
+      fast_bin_pass<NOBS, NS, SMEM, NOPS, CODES>(
+          P, cx, s_hist, s_syst, &s_norm, hb, F.proposed + nsources,
+          (Q.stamps && s == PK_CTA_STEP && blockIdx.x < 148) ? Q.stamps + 1200 + blockIdx.x * 4 : nullptr);
       PK_STAMP(1);
+      PK_CTA_STAMP(1);
       cta_arrive(bar1);
       if (!cta_wait_ge(bar1, (s + 1u) * G, abort_flag, &s_ok)) break;
       PK_STAMP(2);
+      PK_CTA_STAMP(2);
       // the buffer the NEXT step bins into: last read in the previous step's lookup phase
       unsigned* const other = Q.hist_buf[1 - b];
       for (unsigned long long w = gtid; w < Q.hist_words; w += gstride) other[w] = 0u;
     }
 
     // ---- lookup + event likelihood ------------------------------------------------------------
+    // CTA 0's last warp draws the step's random numbers now (Philox is stateless: counter =
+    // step index), off the serial tail
+    const bool pre_rng = blockIdx.x == 0 && !F.tape_normals && !F.tape_uniforms;
+    if (pre_rng && warp == FAST_WARPS - 1) {
+      for (int k = lane; k < np; k += 32)
+        s_z[k] = F.jump_width[k] > 0 ? fin_normal(F, F.step, (unsigned)k, 1u) : 0.0;
+      if (lane == 0) {
+        const uint4 r = fin_random(F, F.step, 0u, 2u);
+        s_u = u01(r.x, r.y);
+      }
+    }
     if (tid < ns) {
       const unsigned norm = __ldcg(hb + (size_t)ns * tnb + tid);
       const float eff = (float)(1.0 * norm / s_nmc[tid]);                    // nll_kernels.cpp:105
@@ -172,7 +198,7 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
     }
     __syncthreads();
     double sum = 0;
-    for (long long i = gtid; i < Q.nevents; i += gstride) {
+    for (long long i = etid; i < Q.nevents; i += gstride) {
       double acc = 0;
       for (int j = 0; j < ns; ++j) {
         const int rb = s_rb[j][i];
@@ -188,6 +214,7 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
     const double bsum = block_sum<FAST_THREADS>(sum, s_warp);
     if (tid == 0) __stcg(Q.partials + blockIdx.x, bsum);
     PK_STAMP(3);
+    PK_CTA_STAMP(3);
     cta_arrive(bar2);
 
     // ---- finish (CTA 0) / wait for the next proposal (others) ---------------------------------
@@ -210,7 +237,9 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
       }
       __syncthreads();
       PK_STAMP(5);
-      if (tid < 32) finish_step(F, Q.st, np, ns, nsources, s_warp[0], NLL_MODE_STEP, s_term, tid);
+      if (tid < 32)
+        finish_step(F, Q.st, np, ns, nsources, s_warp[0], NLL_MODE_STEP, s_term, tid,
+                    pre_rng ? s_z : nullptr, pre_rng ? &s_u : nullptr);
       __syncthreads();
       PK_STAMP(6);
       for (int k = tid; k < np; k += FAST_THREADS) __stcg(next + k, F.proposed[k]);
@@ -244,6 +273,13 @@ static const PersistEntry g_persist_table[] = { SXMC_FAST_TABLE(FE) };
 
 constexpr size_t PK_STATIC_RESERVE = 32 * 1024;   // static shared memory of the kernel above
 
+static int sms_for_plan() {
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms > 0 ? sms : 148;
+}
+
 int launch_chain_persistent(const BinLaunch& L0, const PersistParams& Q, cudaStream_t stream) {
   if (!L0.fast || L0.njobs > FAST_MAX_JOBS || Q.ns > PK_MAX_SIGNALS) {
     set_error("persistent chain kernel: fit shape not supported");
@@ -268,7 +304,7 @@ int launch_chain_persistent(const BinLaunch& L0, const PersistParams& Q, cudaStr
   if (!fk) { set_error("persistent chain kernel: no instantiation for this shape"); return SXMC_ESTATE; }
   FastParams P;
   unsigned long long total = 0;
-  build_fast_params(L, 0, L.njobs, P, &total);
+  build_fast_params(L, 0, L.njobs, sms_for_plan(), P, &total);
   SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
   int occ = 0;
   SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fk, FAST_THREADS, L.smem_bytes));

@@ -85,6 +85,10 @@ struct FastParams {
   FastGeo geo;
   int njobs, R, S;
   unsigned stage_off;
+  // job-aligned partition (small fits): CTAs [cta_first[j], cta_first[j+1]) work on job j only,
+  // so no CTA pays the per-segment overhead twice; aligned == 0: even split of all chunks
+  unsigned short cta_first[FAST_MAX_JOBS + 1];
+  int aligned;
 };
 
 // Arguments of the persistent chain kernel (chain_kernels.cu), by value.

@@ -48,7 +48,9 @@ bool bin_fast_plan(int nslots, int hist_bins, size_t static_reserve, int* R_out,
                    unsigned* stage_off_out, size_t* smem_out);
 constexpr size_t BIN_STATIC_RESERVE = 2048;   // static shared memory of bin_fast_kernel
 // FastParams of jobs [g0, g0+ng) of a planned launch; *total_out = their chunk count
-void build_fast_params(const BinLaunch& L, int g0, int ng, FastParams& P, unsigned long long* total_out);
+// `grid` = the CTA count the kernel will be launched with (decides the job-aligned partition)
+void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams& P,
+                       unsigned long long* total_out);
 // chain_kernels.cu
 int launch_chain_persistent(const BinLaunch& L, const PersistParams& Q, cudaStream_t stream);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);

@@ -115,8 +115,15 @@ __device__ __forceinline__ uint4 fin_random(const FinState& F, unsigned step, un
 
 // pick_new_vector_device (src/nll_kernels.cpp:31-53), executed by one warp; the new point goes
 // to shared memory and to the global state (the next launch's binning kernel reads it there).
+__device__ __forceinline__ double fin_normal(const FinState& F, unsigned step, unsigned k, unsigned purpose) {
+  const uint4 r = fin_random(F, step, k, purpose);
+  const double u1 = u01(r.x, r.y), u2 = u01(r.z, r.w);
+  return sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
+}
+
+// pre_z (optional): the step's normals, computed ahead of time by an idle warp
 static __device__ void propose(FinState& F, ChainState* st, int np, unsigned step_for_rng, unsigned purpose,
-                        int lane) {
+                        int lane, const double* pre_z = nullptr) {
   unsigned long long tape_base = F.i_normal;
   for (int k0 = 0; k0 < np; k0 += 32) {
     const int k = k0 + lane;
@@ -130,9 +137,7 @@ static __device__ void propose(FinState& F, ChainState* st, int np, unsigned ste
           const unsigned long long ti = tape_base + __popc(m & ((1u << lane) - 1));
           z = ti < F.n_normals ? F.tape_normals[ti] : 0.0;
         } else {
-          const uint4 r = fin_random(F, step_for_rng, (unsigned)k, purpose);
-          const double u1 = u01(r.x, r.y), u2 = u01(r.z, r.w);
-          z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
+          z = pre_z ? pre_z[k] : fin_normal(F, step_for_rng, (unsigned)k, purpose);
         }
         v = __dadd_rn(v, __dmul_rn((double)F.jump_width[k], z));
       }
@@ -149,7 +154,8 @@ static __device__ void propose(FinState& F, ChainState* st, int np, unsigned ste
 // copy F; results are written back to the global state with independent stores.
 // s_term: nsignals normalisation terms + nparameters constraint terms, filled beforehand.
 static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, int nsources, double ev_new,
-                            int mode, const double* s_term, int lane) {
+                            int mode, const double* s_term, int lane,
+                            const double* pre_z = nullptr, const double* pre_u = nullptr) {
   // --- burn-in re-tune of the jump widths (src/mcmc.cpp:274-311), before this step's decision
   const unsigned step = F.step;
   bool reset_stats = false;
@@ -216,8 +222,12 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
       F.i_uniform += 1;
       st->i_uniform = F.i_uniform;
     } else {
-      const uint4 r = fin_random(F, step, 0u, 2u);
-      u = u01(r.x, r.y);
+      if (pre_u) {
+        u = *pre_u;
+      } else {
+        const uint4 r = fin_random(F, step, 0u, 2u);
+        u = u01(r.x, r.y);
+      }
     }
     const double nc = F.current_nll;
     accept = (F.debug_mode || (nll < nc || u <= exp(nc - nll))) ? 1 : 0;
@@ -252,7 +262,7 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
     st->step = F.step;
   }
   __syncwarp();
-  propose(F, st, np, step, 1u, lane);
+  propose(F, st, np, step, 1u, lane, pre_z);
 }
 
 }  // namespace sxmc
