@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsxmc_b200.so")
+# SXMC_B200_LIB: tuning experiments load an alternative build of the same library
+LIB_PATH = os.environ.get("SXMC_B200_LIB") or os.path.join(HERE, "libsxmc_b200.so")
 
 c_dp = C.POINTER(C.c_double)
 c_fp = C.POINTER(C.c_float)

@@ -22,7 +22,10 @@ constexpr int WT_ROWS = LANE_RUN / 4;           // float4 rows per warp-tile
 constexpr int BIN_THREADS = 256;
 constexpr int BIN_WARPS = BIN_THREADS / 32;     // warp-tiles per block-tile
 
-constexpr int FAST_WARPS = 16;                  // warps of the persistent fast binning CTA
+#ifndef SXMC_FAST_WARPS
+#define SXMC_FAST_WARPS 16
+#endif
+constexpr int FAST_WARPS = SXMC_FAST_WARPS;     // warps of the persistent fast binning CTA
 constexpr int FAST_THREADS = FAST_WARPS * 32;
 constexpr int FAST_MAX_STAGES = 8;              // bulk-copy pipeline stages per warp
 
