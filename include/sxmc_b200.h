@@ -212,6 +212,41 @@ int sxmc_chain_set_mode(sxmc_chain* c, int mode);
  * every CTA in step 20; out64x8 (may be NULL, else 2048 entries) receives the last launch's. */
 int sxmc_chain_phase_stamps(sxmc_chain* c, int enable, unsigned long long* out64x8);
 
+/* ---- ensemble loop pieces (src/sxmc.cpp:62-134), SURVEY 8(f)-1,2 ------------------------ */
+typedef struct sxmc_generator sxmc_generator;
+/* make_fake_dataset (src/generator.cpp:10-48) in two parts.  create = what is the same for
+ * every experiment: Signal::get_efficiency (src/signal.cpp:172-197) and the histogram
+ * EvalHist::RandomSample samples from (src/pdfz.cpp:817-832, CreateHistogram :496-592), both at
+ * `syst_vals` (the systematics' means), evaluated for all signals in one batched launch.
+ * `uppers`/`lowers` (nlimits = 0 or >= nobservables) are the observables' limits of the
+ * rejection test (:851-855).  The handles are borrowed; their bound buffers are not touched. */
+int sxmc_generator_create(sxmc_hist* const* hs, int n, const double* nexpected, const unsigned* n_mc,
+                          const double* syst_vals, int nsyst_vals, const float* uppers,
+                          const float* lowers, int nlimits, sxmc_generator** out);
+int sxmc_generator_destroy(sxmc_generator* g);
+/* eff[j] = norm_j / n_mc_j (src/signal.cpp:196) */
+int sxmc_generator_efficiency(sxmc_generator* g, double* eff_out);
+/* sample = the per-experiment part (src/pdfz.cpp:834-919): per signal observed =
+ * Poisson(nexpected*eff) or nint, then inversion of the bin CDF + uniform inside the bin
+ * (ROOT TH1::GetRandom / TH2::GetRandom2 / TH3::GetRandom3 restated on Philox4x32-10; key =
+ * (seed, stream_id = experiment index)).  events_out receives rows of nobservables+1 floats,
+ * signal after signal (NULL: count only); *nfloats_out = floats generated. */
+int sxmc_generator_sample(sxmc_generator* g, int poisson, uint64_t seed, uint64_t stream_id,
+                          float* events_out, size_t max_floats, unsigned* observed_out,
+                          size_t* nfloats_out);
+/* sxmc::errors::Contour (src/error_estimators/contour.cpp:18-69) on LikelihoodSpace::get_contour
+ * (src/likelihood.cpp:88-101) as device reductions over rows [nrows][nparameters+1] (DEVICE
+ * pointer; last column = NLL): delta = 0.5*ChisquareQuantile(cl,1); per parameter the extents
+ * of the rows with NLL-min < delta, and the point estimate (mid-range of the rows within 0.13
+ * of the minimum, widened x5 until one qualifies).  The float->text->double round trip of the
+ * reference's selection strings ("likelihood+" << -lmin << "<" << delta) is reproduced. */
+int sxmc_rows_contour(const float* rows_dev, long nrows, int nparameters, float delta,
+                      float* lower_out, float* upper_out, float* point_out, float* lmin_out,
+                      long* ncontour_out);
+/* the same on a chain's resident rows after sxmc_chain_run / sxmc_chain_end */
+int sxmc_chain_contour(sxmc_chain* c, float delta, float* lower_out, float* upper_out,
+                       float* point_out, float* lmin_out, long* ncontour_out);
+
 /* ---- multi-GPU (no reference counterpart) ------------------------------- */
 int sxmc_comm_unique_id(void* id128_out);                 /* ncclGetUniqueId, 128 bytes */
 int sxmc_comm_create(const void* id128, int nranks, int rank, sxmc_comm** out);

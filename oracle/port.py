@@ -172,3 +172,39 @@ def mcmc(fit, nsteps, burnin_fraction, normals, uniforms, debug_mode=False, trac
     return dict(chain=chain[:rows].copy(), accepted=int(acc.value),
                 nll_trace=nll_tr[:nsteps] if trace else None,
                 prop_trace=prop_tr[:nsteps] if trace else None)
+
+
+# ---------------------------------------------------------------------------------------
+# Contour error estimator -- numpy restatement.  PARITY UNPINNED: the reference's code for it
+# runs on ROOT's TNtuple/TTreeFormula (un-vendored) and its tests hold no vector for it.
+# ---------------------------------------------------------------------------------------
+def _through_ostream(v):
+    """A float written with `ostream <<` (6 significant digits) and parsed back by TTreeFormula."""
+    return float("%g" % float(np.float32(v)))
+
+
+def contour(rows, delta):
+    """rows: float32 [n, np+1], last column = NLL.  Follows LikelihoodSpace::get_contour
+    (src/likelihood.cpp:88-101) and Contour::get_interval (src/error_estimators/contour.cpp:30-66).
+    Returns (lower[np], upper[np], point[np], lmin, ncontour)."""
+    rows = np.asarray(rows, dtype=np.float32)
+    nll = rows[:, -1].astype(np.float64)
+    lmin = np.float32(rows[:, -1].min())                       # GetMinimum("likelihood")
+    off = _through_ostream(-lmin)
+    sel = nll + off < _through_ostream(delta)                  # "likelihood+<-lmin><<delta>"
+    pts = rows[sel]
+    assert len(pts) > 0
+    lmin2 = np.float32(pts[:, -1].min())
+    off2 = _through_ostream(-lmin2)
+    dnll = np.float32(0.13)
+    while True:
+        el = pts[pts[:, -1].astype(np.float64) + off2 < _through_ostream(dnll)]
+        dnll = np.float32(dnll * np.float32(5))
+        if len(el) >= 1:
+            break
+    npar = rows.shape[1] - 1
+    lower = pts[:, :npar].min(axis=0)
+    upper = pts[:, :npar].max(axis=0)
+    point = ((el[:, :npar].min(axis=0).astype(np.float64) + el[:, :npar].max(axis=0).astype(np.float64)) / 2
+             ).astype(np.float32)
+    return lower, upper, point, float(lmin), int(len(pts))

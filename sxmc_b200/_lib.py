@@ -101,6 +101,15 @@ SYMBOLS = {
     "sxmc_chain_get_bins": (C.c_int, [c_vp, c_up]),
     "sxmc_chain_set_mode": (C.c_int, [c_vp, C.c_int]),
     "sxmc_chain_phase_stamps": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_uint64)]),
+    "sxmc_generator_create": (C.c_int, [C.POINTER(c_vp), C.c_int, c_dp, c_up, c_dp, C.c_int, c_fp, c_fp,
+                                        C.c_int, C.POINTER(c_vp)]),
+    "sxmc_generator_destroy": (C.c_int, [c_vp]),
+    "sxmc_generator_efficiency": (C.c_int, [c_vp, c_dp]),
+    "sxmc_generator_sample": (C.c_int, [c_vp, C.c_int, C.c_uint64, C.c_uint64, c_fp, _SIZE, c_up,
+                                        C.POINTER(_SIZE)]),
+    "sxmc_rows_contour": (C.c_int, [c_vp, C.c_long, C.c_int, C.c_float, c_fp, c_fp, c_fp, c_fp,
+                                    C.POINTER(C.c_long)]),
+    "sxmc_chain_contour": (C.c_int, [c_vp, C.c_float, c_fp, c_fp, c_fp, c_fp, C.POINTER(C.c_long)]),
     "sxmc_comm_unique_id": (C.c_int, [c_vp]),
     "sxmc_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "sxmc_comm_destroy": (C.c_int, [c_vp]),

@@ -1346,3 +1346,241 @@ int sxmc_comm_allreduce_u32(sxmc_comm* comm, unsigned* dev, size_t count) {
 }
 
 }  // extern "C"
+
+// =========================================================================================
+// Ensemble pieces: fake-data generator and the Contour estimator (ensemble_kernels.cu)
+// =========================================================================================
+struct sxmc_generator {
+  int n = 0, nobs = 0, total_nbins = 0;
+  std::vector<sxmc_hist*> hs;
+  unsigned* bins_dev = nullptr;     // [n][total_nbins] histograms at the systematics' means
+  unsigned* cum_dev = nullptr;      // [n][total_nbins] inclusive prefix sums
+  unsigned* norms_dev = nullptr;    // [n]
+  double* params_dev = nullptr;
+  GenSignal* sigs_dev = nullptr;
+  unsigned long long* counts_dev = nullptr;    // [n+1]
+  unsigned long long* offsets_dev = nullptr;   // [n+1]
+  unsigned long long* counts_host = nullptr;   // pinned [n+1]
+  float* events_dev = nullptr; unsigned long long cap_events = 0;
+  GenGeo geo;
+  std::vector<unsigned> norms, n_mc;
+  std::vector<double> nexpected;
+  Batch batch;
+  cudaStream_t stream = nullptr;
+  unsigned long long last_total = 0;
+};
+
+extern "C" {
+
+int sxmc_generator_destroy(sxmc_generator* g) {
+  if (!g) return SXMC_OK;
+  if (g->stream) cudaStreamSynchronize(g->stream);
+  cudaFree(g->bins_dev); cudaFree(g->cum_dev); cudaFree(g->norms_dev); cudaFree(g->params_dev);
+  cudaFree(g->sigs_dev); cudaFree(g->counts_dev); cudaFree(g->offsets_dev); cudaFree(g->events_dev);
+  if (g->counts_host) cudaFreeHost(g->counts_host);
+  g->batch.release();
+  if (g->stream) cudaStreamDestroy(g->stream);
+  delete g;
+  return SXMC_OK;
+}
+
+int sxmc_generator_create(sxmc_hist* const* hs, int n, const double* nexpected, const unsigned* n_mc,
+                          const double* syst_vals, int nsyst_vals, const float* uppers,
+                          const float* lowers, int nlimits, sxmc_generator** out) {
+  if (!hs || !out || n <= 0 || n > 256) SXMC_INVAL("sxmc_generator_create: 1..256 signal PDFs required");
+  *out = nullptr;
+  SXMC_TRY(ensure_init());
+  const sxmc_hist* h0 = hs[0];
+  if (h0->nobs > 3) SXMC_INVAL("Cannot EvalHist::CreateHistogram for dimensions greater than 3!");   // src/pdfz.cpp:497-499
+  for (int j = 0; j < n; ++j) {
+    const sxmc_hist* h = hs[j];
+    bool same = h->nobs == h0->nobs && h->total_nbins == h0->total_nbins;
+    for (int o = 0; same && o < h->nobs; ++o)
+      same = h->lower[o] == h0->lower[o] && h->upper[o] == h0->upper[o] && h->nbins[o] == h0->nbins[o];
+    if (!same) SXMC_INVAL("sxmc_generator_create: all signal PDFs must share the observables' binning");
+  }
+  if (nlimits != 0 && nlimits < h0->nobs) SXMC_INVAL("sxmc_generator_create: limits must cover every observable");
+  sxmc_generator* g = new sxmc_generator;
+  g->n = n; g->nobs = h0->nobs; g->total_nbins = h0->total_nbins;
+  g->hs.assign(hs, hs + n);
+  g->nexpected.assign(nexpected, nexpected + n);
+  g->n_mc.assign(n_mc, n_mc + n);
+  g->norms.resize(n);
+  memset(&g->geo, 0, sizeof g->geo);
+  g->geo.nobs = h0->nobs; g->geo.total_nbins = h0->total_nbins; g->geo.nlimits = nlimits ? h0->nobs : 0;
+  for (int o = 0; o < h0->nobs; ++o) {
+    g->geo.lower[o] = h0->lower[o];
+    g->geo.width[o] = (h0->upper[o] - h0->lower[o]) / h0->nbins[o];
+    g->geo.stride[o] = h0->stride[o];
+    if (nlimits) { g->geo.lim_lo[o] = lowers[o]; g->geo.lim_hi[o] = uppers[o]; }
+  }
+  const size_t nb = (size_t)n * (size_t)std::max(1, g->total_nbins);
+  cudaError_t e = cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMalloc(&g->bins_dev, sizeof(unsigned) * nb);
+  if (e == cudaSuccess) e = cudaMalloc(&g->cum_dev, sizeof(unsigned) * nb);
+  if (e == cudaSuccess) e = cudaMalloc(&g->norms_dev, sizeof(unsigned) * n);
+  if (e == cudaSuccess) e = cudaMalloc(&g->params_dev, sizeof(double) * std::max(1, nsyst_vals));
+  if (e == cudaSuccess) e = cudaMalloc(&g->sigs_dev, sizeof(GenSignal) * n);
+  if (e == cudaSuccess) e = cudaMalloc(&g->counts_dev, sizeof(unsigned long long) * (n + 1));
+  if (e == cudaSuccess) e = cudaMalloc(&g->offsets_dev, sizeof(unsigned long long) * (n + 1));
+  if (e == cudaSuccess) e = cudaMallocHost(&g->counts_host, sizeof(unsigned long long) * (n + 1));
+  if (e == cudaSuccess) e = cudaMemsetAsync(g->bins_dev, 0, sizeof(unsigned) * nb, g->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(g->norms_dev, 0, sizeof(unsigned) * n, g->stream);
+  if (e == cudaSuccess && nsyst_vals > 0)
+    e = cudaMemcpyAsync(g->params_dev, syst_vals, sizeof(double) * nsyst_vals, cudaMemcpyHostToDevice, g->stream);
+  if (e != cudaSuccess) { sxmc_generator_destroy(g); return cuda_fail(e, "sxmc_generator_create", __FILE__, __LINE__); }
+  // one batched evaluation of every PDF at the systematics' means: the EvalAsync(false) of
+  // get_efficiency (src/signal.cpp:192-194) and of CreateHistogram (src/pdfz.cpp:503-504)
+  int rc = g->batch.reserve(n);
+  for (int j = 0; j < n && !rc; ++j) {
+    for (const SystDesc& d : hs[j]->systs)
+      for (int k = 0; k < d.npars; ++k)
+        if (d.pidx[k] >= nsyst_vals) { set_error("sxmc_generator_create: systematic coefficient index beyond syst_vals"); rc = SXMC_EINVAL; }
+    if (!rc) rc = fill_job(hs[j], g->batch.host[j], g->bins_dev + (size_t)j * g->total_nbins, g->norms_dev + j,
+                           g->params_dev, 1);
+  }
+  if (!rc) {
+    g->batch.n_ep = 0;
+    plan_launch(g->batch, n);
+    rc = upload_batch(g->batch, n, g->stream);
+  }
+  if (!rc) rc = launch_bin(g->batch.launch, g->stream);
+  for (int j = 0; j < n && !rc; ++j)
+    rc = launch_cum(g->bins_dev + (size_t)j * g->total_nbins, g->total_nbins, g->cum_dev + (size_t)j * g->total_nbins,
+                    g->stream);
+  if (!rc) {
+    std::vector<GenSignal> sg(n);
+    for (int j = 0; j < n; ++j) {
+      sg[j].cum = g->cum_dev + (size_t)j * g->total_nbins;
+      sg[j].norm = g->norms_dev + j;
+      sg[j].nexpected = nexpected[j];
+      sg[j].n_mc = n_mc[j];
+      sg[j].dataset = hs[j]->dataset;
+    }
+    e = cudaMemcpyAsync(g->sigs_dev, sg.data(), sizeof(GenSignal) * n, cudaMemcpyHostToDevice, g->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(g->norms.data(), g->norms_dev, sizeof(unsigned) * n, cudaMemcpyDeviceToHost, g->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g->stream);
+    if (e != cudaSuccess) rc = cuda_fail(e, "sxmc_generator_create", __FILE__, __LINE__);
+  }
+  if (rc) { sxmc_generator_destroy(g); return rc; }
+  *out = g;
+  return SXMC_OK;
+}
+
+int sxmc_generator_efficiency(sxmc_generator* g, double* eff_out) {
+  if (!g || !eff_out) SXMC_INVAL("sxmc_generator_efficiency: NULL argument");
+  for (int j = 0; j < g->n; ++j) eff_out[j] = 1.0 * g->norms[j] / (double)g->n_mc[j];   // src/signal.cpp:196
+  return SXMC_OK;
+}
+
+// Draw one dataset into the generator's device buffer.  *nevents_out = rows generated.
+static int generator_draw(sxmc_generator* g, int poisson, uint64_t seed, uint64_t stream_id,
+                          unsigned long long* nevents_out) {
+  // capacity: mean + 10 sigma + slack of the total expectation; regrown (and redrawn) if short
+  double mean_total = 0;
+  for (int j = 0; j < g->n; ++j) mean_total += g->nexpected[j] * (1.0 * g->norms[j] / (double)g->n_mc[j]);
+  unsigned long long want = (unsigned long long)(mean_total + 10.0 * std::sqrt(std::max(mean_total, 1.0)) + 64.0);
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    if (g->cap_events < want) {
+      cudaFree(g->events_dev);
+      g->events_dev = nullptr;
+      g->cap_events = 0;
+      SXMC_CUDA(cudaMalloc(&g->events_dev, sizeof(float) * want * (size_t)(g->nobs + 1)));
+      g->cap_events = want;
+    }
+    SXMC_TRY(launch_generate(g->sigs_dev, g->n, g->geo, poisson, seed, stream_id, g->counts_dev, g->offsets_dev,
+                             g->events_dev, g->cap_events, g->stream));
+    SXMC_CUDA(cudaMemcpyAsync(g->counts_host, g->counts_dev, sizeof(unsigned long long) * (g->n + 1),
+                              cudaMemcpyDeviceToHost, g->stream));
+    SXMC_CUDA(cudaStreamSynchronize(g->stream));
+    if (g->counts_host[g->n] <= g->cap_events) break;
+    want = g->counts_host[g->n];      // counter-based RNG: the redraw yields the same counts
+  }
+  g->last_total = g->counts_host[g->n];
+  *nevents_out = g->last_total;
+  return SXMC_OK;
+}
+
+int sxmc_generator_sample(sxmc_generator* g, int poisson, uint64_t seed, uint64_t stream_id,
+                          float* events_out, size_t max_floats, unsigned* observed_out,
+                          size_t* nfloats_out) {
+  if (!g || !nfloats_out) SXMC_INVAL("sxmc_generator_sample: NULL argument");
+  unsigned long long ne = 0;
+  SXMC_TRY(generator_draw(g, poisson, seed, stream_id, &ne));
+  const size_t nf = (size_t)ne * (size_t)(g->nobs + 1);
+  *nfloats_out = nf;
+  if (observed_out) for (int j = 0; j < g->n; ++j) observed_out[j] = (unsigned)g->counts_host[j];
+  if (events_out) {
+    if (nf > max_floats) { set_error("sxmc_generator_sample: events_out too small (see *nfloats_out)"); return SXMC_EINVAL; }
+    if (nf) SXMC_CUDA(cudaMemcpy(events_out, g->events_dev, sizeof(float) * nf, cudaMemcpyDeviceToHost));
+  }
+  return SXMC_OK;
+}
+
+// ---- Contour estimator ------------------------------------------------------------------------
+int sxmc_rows_contour(const float* rows_dev, long nrows, int nparameters, float delta,
+                      float* lower_out, float* upper_out, float* point_out, float* lmin_out,
+                      long* ncontour_out) {
+  if (!rows_dev || nrows <= 0 || nparameters <= 0) SXMC_INVAL("sxmc_rows_contour: no rows");
+  SXMC_TRY(ensure_init());
+  const int np = nparameters;
+  const int NL = CONTOUR_MAX_LEVELS;
+  const size_t words = 1 + 2 * NL + 2 * (size_t)NL * np;   // lmin | counts (u64 = 2 words) | mins | maxs
+  unsigned* buf = nullptr;
+  SXMC_CUDA(cudaMalloc(&buf, sizeof(unsigned) * (words + 1)));
+  std::vector<unsigned> init(words + 1, 0u);
+  // layout (words): [0] lmin, [1] pad, [2 .. 2+2NL) counts, then mins, then maxs
+  const size_t off_counts = 2, off_min = 2 + 2 * (size_t)NL, off_max = off_min + (size_t)NL * np;
+  init[0] = 0x7f800000u;
+  for (size_t i = 0; i < (size_t)NL * np; ++i) { init[off_min + i] = 0x7f800000u; init[off_max + i] = 0xff800000u; }
+  cudaError_t e = cudaMemcpy(buf, init.data(), sizeof(unsigned) * (words + 1), cudaMemcpyHostToDevice);
+  int rc = SXMC_OK;
+  float lmin = 0;
+  if (e == cudaSuccess) rc = launch_rows_min_nll(rows_dev, nrows, np, (float*)buf, 0);
+  if (e == cudaSuccess && !rc) e = cudaMemcpy(&lmin, buf, sizeof(float), cudaMemcpyDeviceToHost);
+  // "likelihood+" << -lmin << "<" << delta : both floats pass through an ostream (6 significant
+  // digits) and are parsed back as doubles by TTreeFormula (src/likelihood.cpp:91-92)
+  auto through_ostream = [](float v) { char t[64]; snprintf(t, sizeof t, "%g", (double)v); return strtod(t, nullptr); };
+  const double off = through_ostream(-lmin);
+  ContourLevels lv;
+  lv.n = NL;
+  lv.thr[0] = through_ostream(delta);                         // the contour itself
+  float dnll = 0.13f;                                         // src/error_estimators/contour.cpp:43-54
+  for (int l = 1; l < NL; ++l) { lv.thr[l] = std::min(through_ostream(dnll), lv.thr[0]); dnll *= 5; }
+  // (the point-estimate selection runs on the contour points, so its threshold never exceeds delta's)
+  if (e == cudaSuccess && !rc)
+    rc = launch_rows_extents(rows_dev, nrows, np, off, lv, (unsigned long long*)(buf + off_counts),
+                             (float*)(buf + off_min), (float*)(buf + off_max), 0);
+  std::vector<unsigned> res(words + 1);
+  if (e == cudaSuccess && !rc) e = cudaMemcpy(res.data(), buf, sizeof(unsigned) * (words + 1), cudaMemcpyDeviceToHost);
+  cudaFree(buf);
+  if (e != cudaSuccess) return cuda_fail(e, "sxmc_rows_contour", __FILE__, __LINE__);
+  if (rc) return rc;
+  const unsigned long long* counts = (const unsigned long long*)(res.data() + off_counts);
+  const float* mins = (const float*)(res.data() + off_min);
+  const float* maxs = (const float*)(res.data() + off_max);
+  if (counts[0] == 0) { set_error("sxmc_rows_contour: no contour points"); return SXMC_ESTATE; }   // assert at likelihood.cpp:97
+  int lp = -1;
+  for (int l = 1; l < NL; ++l) if (counts[l] >= 1) { lp = l; break; }
+  if (lp < 0) lp = 0;
+  for (int k = 0; k < np; ++k) {
+    if (lower_out) lower_out[k] = mins[k];
+    if (upper_out) upper_out[k] = maxs[k];
+    // (GetMinimum + GetMaximum) / 2 on doubles, stored to a float member
+    if (point_out) point_out[k] = (float)(((double)mins[(size_t)lp * np + k] + (double)maxs[(size_t)lp * np + k]) / 2);
+  }
+  if (lmin_out) *lmin_out = lmin;
+  if (ncontour_out) *ncontour_out = (long)counts[0];
+  return SXMC_OK;
+}
+
+int sxmc_chain_contour(sxmc_chain* c, float delta, float* lower_out, float* upper_out, float* point_out,
+                       float* lmin_out, long* ncontour_out) {
+  if (!c) SXMC_INVAL("sxmc_chain_contour: NULL chain");
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  const long n = (long)std::min(c->nrows, c->row_cap);
+  return sxmc_rows_contour(c->rows_dev, n, c->nparameters, delta, lower_out, upper_out, point_out, lmin_out,
+                           ncontour_out);
+}
+
+}  // extern "C"

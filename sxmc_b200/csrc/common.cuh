@@ -158,6 +158,26 @@ struct ChainState {
   double last_nll, last_event_sum;        // results of an evaluate-only pass
 };
 
+// ---- fake-data generator (ensemble_kernels.cu) ---------------------------------------------
+struct GenSignal {
+  const unsigned* cum;     // inclusive prefix sums of the histogram at the systematics' means
+  const unsigned* norm;    // its in-domain count (get_efficiency)
+  double nexpected;
+  unsigned n_mc;
+  unsigned dataset;
+};
+struct GenGeo {
+  double lower[3], width[3];   // bin low edge = lower + k * width
+  int stride[3];
+  float lim_lo[3], lim_hi[3];  // observable limits of the rejection test (float vectors in the reference)
+  int nobs, nlimits, total_nbins;
+};
+constexpr int CONTOUR_MAX_LEVELS = 12;
+struct ContourLevels {
+  double thr[CONTOUR_MAX_LEVELS];
+  int n;
+};
+
 enum NllMode { NLL_MODE_STEP = 0, NLL_MODE_INIT = 1, NLL_MODE_EVAL_ONLY = 2 };
 
 // error plumbing --------------------------------------------------------------------------

@@ -87,4 +87,14 @@ int launch_nll_lut(const float* lut, size_t ne, size_t ns, const double* pars, s
                    const double* nexpected, const unsigned* n_mc, const short* source_id,
                    const unsigned* norms, double* out2_dev, cudaStream_t stream);
 
+// ---- ensemble_kernels.cu ----
+int launch_cum(const unsigned* bins_dev, int nb, unsigned* cum_dev, cudaStream_t stream);
+int launch_generate(const GenSignal* sigs_dev, int n, const GenGeo& geo, int poisson,
+                    unsigned long long seed, unsigned long long stream_id, unsigned long long* counts_dev,
+                    unsigned long long* offsets_dev, float* events_dev, unsigned long long cap_events,
+                    cudaStream_t stream);
+int launch_rows_min_nll(const float* rows_dev, long long nrows, int np, float* out_dev, cudaStream_t stream);
+int launch_rows_extents(const float* rows_dev, long long nrows, int np, double off, const ContourLevels& lv,
+                        unsigned long long* counts_dev, float* mins_dev, float* maxs_dev, cudaStream_t stream);
+
 }  // namespace sxmc

@@ -1,0 +1,191 @@
+"""Host-side mirror of the reference's ensemble loop (`ensemble()`, src/sxmc.cpp:41-137) and of
+the two pieces either side of the chain inside it:
+
+* ``make_fake_dataset`` (src/generator.cpp:10-48) -- device-side in libsxmc_b200
+  (``sxmc_generator_*``): efficiencies and sampling histograms once per ensemble, one Poisson
+  draw + CDF inversion launch per experiment;
+* the ``Contour`` error estimator (src/error_estimators/contour.cpp:18-69) that turns a chain
+  into the upper limit the ensemble collects (src/sxmc.cpp:110-126) -- device reductions over the
+  resident chain rows (``sxmc_chain_contour``).
+
+Experiments are independent: with ``world`` ranks, experiment ``i`` runs on rank ``i mod world``
+with Philox stream id ``i`` (the reference's single gRandom stream is replaced by one
+counter-based stream per experiment, so the result does not depend on the number of GPUs)."""
+import ctypes as C
+import time
+from dataclasses import dataclass
+from statistics import NormalDist
+
+import numpy as np
+
+from . import sharding
+from ._lib import c_dp, c_fp, c_up, c_vp, check, lib, ptr
+
+
+@dataclass
+class Interval:
+    """src/interval.h:11-28"""
+    one_sided: bool = False
+    point_estimate: float = -1.0
+    lower: float = -1.0
+    upper: float = -1.0
+    cl: float = -1.0
+    coverage: float = -1.0
+
+
+def chisquare_quantile_1dof(cl):
+    """TMath::ChisquareQuantile(cl, 1) = (normal quantile of (1+cl)/2)^2."""
+    z = NormalDist().inv_cdf(0.5 * (1.0 + float(cl)))
+    return z * z
+
+
+def contour_delta(cl):
+    """`float delta = 0.5 * TMath::ChisquareQuantile(_cl, 1)` (contour.cpp:20)."""
+    return float(np.float32(0.5 * chisquare_quantile_1dof(np.float32(cl))))
+
+
+class FakeDataGenerator:
+    """The per-ensemble half of make_fake_dataset: built once from the signals (their
+    EvalHist handles, nexpected, n_mc), the systematics' means and the observables' limits."""
+
+    def __init__(self, signals, systematics, observables):
+        self.nsignals = len(signals)
+        self._harr = (c_vp * self.nsignals)(*[s.histogram._h for s in signals])
+        nexp = np.asarray([s.nexpected for s in signals], dtype=np.float64)
+        n_mc = np.asarray([s.n_mc for s in signals], dtype=np.uint32)
+        vals = np.asarray([m for y in systematics for m in y.means[:y.npars]] or [0.0], dtype=np.float64)
+        nvals = sum(y.npars for y in systematics)
+        up = np.asarray([o.upper for o in observables], dtype=np.float32)
+        lo = np.asarray([o.lower for o in observables], dtype=np.float32)
+        self.nobs = signals[0].histogram.nobservables
+        self._g = c_vp()
+        check(lib().sxmc_generator_create(self._harr, self.nsignals, ptr(nexp, c_dp), ptr(n_mc, c_up),
+                                          ptr(vals, c_dp), int(nvals), ptr(up, c_fp), ptr(lo, c_fp),
+                                          len(observables), C.byref(self._g)))
+        self._expected = nexp
+        self._cap = 0
+        self._buf = None
+
+    def efficiency(self):
+        out = np.zeros(self.nsignals, dtype=np.float64)
+        check(lib().sxmc_generator_efficiency(self._g, ptr(out, c_dp)))
+        return out
+
+    def __call__(self, poisson=True, seed=0, experiment=0):
+        """-> (events float32 [n, nobs+1], observed uint32 [nsignals])"""
+        observed = np.zeros(self.nsignals, dtype=np.uint32)
+        nf = C.c_size_t(0)
+        if self._buf is None:
+            mean = float(np.sum(self._expected * self.efficiency()))
+            self._buf = np.zeros(int(mean + 12 * np.sqrt(max(mean, 1.0)) + 256) * (self.nobs + 1), np.float32)
+        while True:
+            rc = lib().sxmc_generator_sample(self._g, int(bool(poisson)), int(seed), int(experiment),
+                                             ptr(self._buf, c_fp), self._buf.size, ptr(observed, c_up),
+                                             C.byref(nf))
+            if rc != 0 and nf.value > self._buf.size:
+                self._buf = np.zeros(nf.value, np.float32)     # rare: a > 12 sigma draw
+                continue
+            check(rc)
+            break
+        return self._buf[:nf.value].reshape(-1, self.nobs + 1).copy(), observed
+
+    def close(self):
+        if self._g:
+            lib().sxmc_generator_destroy(self._g)
+            self._g = c_vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def make_fake_dataset(signals, systematics, observables, poisson=True, seed=0, experiment=0):
+    """std::vector<float> make_fake_dataset(signals, systematics, observables, poisson)
+    (src/generator.cpp:10-48): flat float vector of rows (observables..., dataset id)."""
+    g = FakeDataGenerator(signals, systematics, observables)
+    try:
+        events, _ = g(poisson, seed, experiment)
+    finally:
+        g.close()
+    return events.ravel()
+
+
+def contour_intervals(chain, cl):
+    """{parameter name: Interval} from the chain's resident rows + the minimum NLL
+    (LikelihoodSpace::extract_best_fit with ERROR_CONTOUR, src/likelihood.cpp:104-137)."""
+    np_ = chain.nparameters
+    lo = np.zeros(np_, np.float32)
+    up = np.zeros(np_, np.float32)
+    pt = np.zeros(np_, np.float32)
+    lmin = C.c_float(0)
+    nc = C.c_long(0)
+    check(lib().sxmc_chain_contour(chain._c, contour_delta(cl), ptr(lo, c_fp), ptr(up, c_fp), ptr(pt, c_fp),
+                                   C.byref(lmin), C.byref(nc)))
+    out = {}
+    for k, name in enumerate(chain.parameter_names[:-1]):
+        out[name] = Interval(False, float(pt[k]), float(lo[k]), float(up[k]), float(np.float32(cl)), -999.0)
+    return out, float(lmin.value)
+
+
+def rows_contour(rows, cl):
+    """The same estimator on host rows [n, nparameters+1] (uploaded to the device)."""
+    rows = np.ascontiguousarray(rows, dtype=np.float32)
+    n, w = rows.shape
+    dev = c_vp()
+    check(lib().sxmc_buf_alloc(rows.nbytes, C.byref(dev)))
+    try:
+        check(lib().sxmc_buf_upload(dev, rows.ctypes.data_as(c_vp), rows.nbytes))
+        lo = np.zeros(w - 1, np.float32)
+        up = np.zeros(w - 1, np.float32)
+        pt = np.zeros(w - 1, np.float32)
+        lmin = C.c_float(0)
+        nc = C.c_long(0)
+        check(lib().sxmc_rows_contour(dev, n, w - 1, contour_delta(cl), ptr(lo, c_fp), ptr(up, c_fp),
+                                      ptr(pt, c_fp), C.byref(lmin), C.byref(nc)))
+    finally:
+        lib().sxmc_buf_free(dev)
+    return lo, up, pt, float(lmin.value), int(nc.value)
+
+
+def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps=None,
+             burnin_fraction=None, rank=0, world=1, observables=None, keep_chains=False, built=None):
+    """The loop of src/sxmc.cpp:62-134 over this rank's experiments.  Returns a dict with the
+    experiment indices run here, their upper limits (`limits.push_back(bfi.upper)`, :126),
+    per-experiment observed counts and wall times.  Use ``sharding.gather_limits`` +
+    ``sharding.median`` for the ensemble-wide result (:218-226)."""
+    from . import mcmc
+    nsteps = fit.nsteps if nsteps is None else int(nsteps)
+    burnin = fit.burnin_fraction if burnin_fraction is None else float(burnin_fraction)
+    hists, chain = built if built is not None else mcmc.build_fit(fit)
+    if observables is None:
+        observables = [mcmc.Observable("o%d" % i, float(fit.lower[i]), float(fit.upper[i]))
+                       for i in range(fit.nobs)]
+    signals = [mcmc.Signal("sig%d" % j, hists[j], s.nexpected, s.n_mc, None) for j, s in enumerate(fit.signals)]
+    systs = [mcmc.Systematic("y%d" % i, y.npars, list(y.means), list(y.sigmas), y.fixed)
+             for i, y in enumerate(fit.systematics)]
+    gen = FakeDataGenerator(signals, systs, observables)
+    mine = sharding.experiments_for_rank(nexperiments, rank, world)
+    out = {"experiments": mine, "limits": [], "observed": [], "seconds": [], "loop_ms": [], "chains": []}
+    for i in mine:
+        t0 = time.perf_counter()
+        events, observed = gen(True, seed, i)                   # make_fake_dataset(..., true)
+        chain.set_seed(seed, i)
+        ls = chain.run_resident(events, nsteps, burnin)         # MCMC::operator(), rows stay on the device
+        best_fit, _ = contour_intervals(chain, confidence)      # ls->get_best_fit()
+        if signal_name in best_fit:
+            out["limits"].append(best_fit[signal_name].upper)
+        else:
+            out["limits"].append(float("nan"))
+        out["observed"].append(observed)
+        out["seconds"].append(time.perf_counter() - t0)
+        out["loop_ms"].append(chain.loop_ms())
+        if keep_chains:
+            out["chains"].append(chain.rows())
+    gen.close()
+    if built is None:
+        chain.close()
+        for h in hists:
+            h.close()
+    return out

@@ -35,7 +35,10 @@ class Systematic:
 
 @dataclass
 class Observable:
+    """src/observable.h:24-41 (the fields the hot path and the generator use)"""
     name: str = ""
+    lower: float = 0.0
+    upper: float = 0.0
 
 
 @dataclass
@@ -148,6 +151,23 @@ class MCMC:
         rows = np.zeros((max(1, self.nrows), self.nparameters + 1), dtype=np.float32)
         _check(lib().sxmc_chain_read(self._c, ptr(rows, c_fp), rows.shape[0]))
         return LikelihoodSpace(rows[:self.nrows], self.parameter_names)
+
+    def run_resident(self, data, nsteps, burnin_fraction, debug_mode=False):
+        """MCMC::operator() without the device->host copy of the rows: they stay resident for
+        `sxmc_chain_contour` (ensemble loop); `rows()` fetches them on demand."""
+        d = np.ascontiguousarray(data, dtype=np.float32).ravel()
+        dd = d if d.size else np.zeros(1, np.float32)
+        nrows = C.c_long(0)
+        _check(lib().sxmc_chain_run(self._c, ptr(dd, c_fp), d.size, int(nsteps),
+                                    float(burnin_fraction), int(debug_mode), 10000, C.byref(nrows)))
+        self.nrows = nrows.value
+        self._nevents = d.size // (self.nobservables + 1)
+        return self.nrows
+
+    def rows(self):
+        rows = np.zeros((max(1, self.nrows), self.nparameters + 1), dtype=np.float32)
+        _check(lib().sxmc_chain_read(self._c, ptr(rows, c_fp), rows.shape[0]))
+        return rows[:self.nrows]
 
     # -- the same call in parts (sxmc_chain_begin / advance / end), for resident chains
     def begin(self, data, nsteps, burnin_fraction, debug_mode=False):

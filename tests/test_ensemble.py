@@ -1,0 +1,151 @@
+"""Ensemble pieces (SURVEY 8(f)-1,2): the device fake-data generator and the Contour
+estimator.  Generator output depends on the RNG (ROOT's in the reference, Philox here), so it
+is checked through what the algorithm guarantees: exact counts without Poisson, Poisson moments
+with it, events distributed as the sampled histogram, limits respected, reproducibility per
+(seed, experiment).  The estimator is compared exactly with the numpy restatement."""
+import numpy as np
+import pytest
+
+from oracle import port
+from sxmc_b200 import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _env(oracle_built):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from sxmc_b200 import _lib
+    _lib.check(_lib.lib().sxmc_init(0))
+
+
+def _generator(fit):
+    from sxmc_b200 import ensemble, mcmc
+    hists, chain = mcmc.build_fit(fit)
+    signals = [mcmc.Signal("sig%d" % j, hists[j], s.nexpected, s.n_mc, None) for j, s in enumerate(fit.signals)]
+    systs = [mcmc.Systematic("y%d" % i, y.npars, list(y.means), list(y.sigmas), y.fixed)
+             for i, y in enumerate(fit.systematics)]
+    obs = [mcmc.Observable("o%d" % i, fit.lower[i], fit.upper[i]) for i in range(fit.nobs)]
+    return ensemble.FakeDataGenerator(signals, systs, obs), hists, chain
+
+
+@pytest.mark.parametrize("name,scale", [("B", 0.05), ("C", 0.002), ("D", 0.003)])
+def test_generator_counts_efficiency_and_distribution(name, scale):
+    fit = W.WORKLOADS[name](scale)
+    gen, hists, chain = _generator(fit)
+    bins, norms, _ = port.eval_all(fit, fit.parameter_means())
+    eff = norms / np.asarray([s.n_mc for s in fit.signals], dtype=np.float64)
+    assert np.array_equal(gen.efficiency(), eff)                       # get_efficiency, exact
+    nexp = np.asarray([s.nexpected for s in fit.signals]) * eff
+
+    # poisson = false: observed = nint(float(nexpected * eff))
+    ev, obs = gen(False, 7, 0)
+    want = np.rint(nexp.astype(np.float32)).astype(np.uint32)
+    assert np.array_equal(obs, want)
+    assert ev.shape == (int(want.sum()), fit.nobs + 1)
+    assert np.all(ev[:, -1] == 0)                                      # dataset id column
+    for o in range(fit.nobs):                                          # limits respected
+        assert np.all(ev[:, o] >= np.float32(fit.lower[o])) and np.all(ev[:, o] <= np.float32(fit.upper[o]))
+
+    # reproducible per (seed, experiment); different experiments differ
+    ev2, obs2 = gen(False, 7, 0)
+    assert np.array_equal(ev, ev2)
+    ev3, _ = gen(False, 7, 1)
+    assert not np.array_equal(ev, ev3)
+
+    # events of signal 0 follow its histogram: chi2 over coarse groups of bins
+    n0 = int(obs[0])
+    e0 = ev[:n0, :fit.nobs].astype(np.float64)
+    idx = np.zeros(n0, dtype=np.int64)
+    stride = 1
+    for o in reversed(range(fit.nobs)):
+        k = np.floor((e0[:, o] - fit.lower[o]) / (fit.upper[o] - fit.lower[o]) * fit.nbins[o]).astype(np.int64)
+        idx += np.clip(k, 0, fit.nbins[o] - 1) * stride
+        stride *= fit.nbins[o]
+    got = np.bincount(idx, minlength=fit.total_nbins).astype(np.float64)
+    p = bins[0] / bins[0].sum()
+    assert np.all(got[p == 0] == 0)                                    # never an empty bin
+    order = np.argsort(-p)
+    groups = np.array_split(order, 20)
+    chi2 = sum((got[g].sum() - n0 * p[g].sum()) ** 2 / max(n0 * p[g].sum(), 1e-9) for g in groups
+               if n0 * p[g].sum() > 5)
+    assert chi2 < 60, chi2                                             # ~19 dof; P(>60) ~ 4e-6
+
+    # poisson = true: mean and variance of the counts over many experiments
+    draws = np.stack([gen(True, 11, i)[1] for i in range(400)]).astype(np.float64)
+    m, v = draws.mean(axis=0), draws.var(axis=0)
+    assert np.all(np.abs(m - nexp) < 5 * np.sqrt(nexp / 400) + 0.05), (m, nexp)
+    assert np.all(np.abs(v / nexp - 1) < 0.35), (v, nexp)
+    gen.close()
+    chain.close()
+    for h in hists:
+        h.close()
+
+
+def test_poisson_small_means_and_zero():
+    fit = W.config_B(0.01)
+    for s, ne in zip(fit.signals, (0.0, 0.7, 4.2)):
+        s.nexpected = ne
+    gen, hists, chain = _generator(fit)
+    eff = gen.efficiency()
+    draws = np.stack([gen(True, 3, i)[1] for i in range(3000)]).astype(np.float64)
+    assert np.all(draws[:, 0] == 0)
+    for j in (1, 2):
+        mu = fit.signals[j].nexpected * eff[j]
+        assert abs(draws[:, j].mean() - mu) < 5 * np.sqrt(mu / 3000)
+        assert abs(draws[:, j].var() / mu - 1) < 0.15
+    gen.close()
+    chain.close()
+    for h in hists:
+        h.close()
+
+
+def test_contour_matches_restatement_on_a_real_chain_and_on_edge_cases():
+    from sxmc_b200 import ensemble, mcmc
+    fit = W.config_B(0.02)
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_seed(5, 0)
+    ls = chain(fit.data, 3000, 0.1)
+    rows = ls.get_samples()
+    for cl in (0.9, 0.68, 0.99):
+        delta = ensemble.contour_delta(cl)
+        want = port.contour(rows, delta)
+        iv, lmin = ensemble.contour_intervals(chain, cl)
+        names = chain.parameter_names[:-1]
+        assert np.array_equal(np.float32([iv[n].lower for n in names]), want[0])
+        assert np.array_equal(np.float32([iv[n].upper for n in names]), want[1])
+        assert np.array_equal(np.float32([iv[n].point_estimate for n in names]), want[2])
+        assert np.float32(lmin) == np.float32(want[3])
+        got = ensemble.rows_contour(rows, cl)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        assert np.array_equal(got[2], want[2]) and got[4] == want[4]
+    # synthetic rows: negative and zero parameters, huge |NLL| (6-digit rounding of -lmin
+    # leaves NO row within 0.13 of the printed minimum: the threshold must widen x5)
+    rng = np.random.default_rng(3)
+    r = rng.normal(size=(5000, 4)).astype(np.float32)
+    r[:, 1] = 0.0
+    r[:, 3] = (-123456.8 + 3.0 * rng.random(5000)).astype(np.float32)   # printed offset: 123457
+    got = ensemble.rows_contour(r, 0.9)
+    want = port.contour(r, ensemble.contour_delta(0.9))
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    assert np.array_equal(got[2], want[2]) and got[4] == want[4]
+    chain.close()
+    for h in hists:
+        h.close()
+
+
+def test_ensemble_limits_are_reproducible_and_cover_the_truth():
+    """A small ensemble: upper limits on source 0 (true rate 1.0 x nexpected) at 90 % CL."""
+    from sxmc_b200 import ensemble
+    fit = W.config_B(0.02)
+    a = ensemble.ensemble(fit, 12, "s0", 0.9, seed=42, nsteps=4000, burnin_fraction=0.1)
+    b = ensemble.ensemble(fit, 12, "s0", 0.9, seed=42, nsteps=4000, burnin_fraction=0.1, rank=1, world=2)
+    assert a["experiments"] == list(range(12)) and b["experiments"] == list(range(1, 12, 2))
+    lim = np.asarray(a["limits"])
+    assert np.all(np.isfinite(lim))
+    # a rank of a 2-rank run reproduces exactly the experiments it owns
+    assert np.array_equal(lim[1::2], np.asarray(b["limits"]))
+    assert np.mean(lim > 1.0) >= 0.7          # upper edge of a 90 % contour: mostly above truth
+    assert np.all(lim < 2.0)
