@@ -247,6 +247,36 @@ int sxmc_rows_contour(const float* rows_dev, long nrows, int nparameters, float 
 int sxmc_chain_contour(sxmc_chain* c, float delta, float* lower_out, float* upper_out,
                        float* point_out, float* lmin_out, long* ncontour_out);
 
+/* ---- chain batch: the fits of an ensemble (src/sxmc.cpp:62-134: nexperiments x MCMC::operator()
+ *      over the same signals) advanced in lockstep by ONE cooperative launch.  Up to 148 chains
+ *      (one per SM) share the Monte-Carlo samples, which stay resident in shared memory; each
+ *      chain has its own data events, random stream and state.  Small fits only (the samples of
+ *      a CTA must fit in shared memory: workloads A, B, E); others fail with SXMC_ESTATE and
+ *      run one chain at a time through sxmc_chain_run.  `cfg` as for sxmc_chain_create. ------- */
+typedef struct sxmc_batch sxmc_batch;
+int sxmc_batch_create(const sxmc_chain_config* cfg, int max_chains, sxmc_batch** out);
+int sxmc_batch_destroy(sxmc_batch* b);
+int sxmc_batch_set_seed(sxmc_batch* b, int slot, uint64_t seed, uint64_t stream_id);
+int sxmc_batch_set_tapes(sxmc_batch* b, int slot, const double* normals, size_t n_normals,
+                         const double* uniforms, size_t n_uniforms);              /* test hook */
+/* the chain's data events: host rows of nobservables+1 floats (SetEvalPoints, src/mcmc.cpp:235) */
+int sxmc_batch_set_data(sxmc_batch* b, int slot, const float* data, size_t data_nfloats);
+/* ... or a fake dataset drawn on the device and consumed there (no host round trip) */
+int sxmc_batch_generate_data(sxmc_batch* b, int slot, sxmc_generator* g, int poisson, uint64_t seed,
+                             uint64_t stream_id, unsigned* observed_out);
+int sxmc_batch_enable_trace(sxmc_batch* b, int on);
+/* MCMC::operator() (src/mcmc.cpp:143-387) for slots [0, nchains): initial evaluation, nsteps
+ * steps with the two burn-in re-tunes, rows kept on the device. */
+int sxmc_batch_run(sxmc_batch* b, int nchains, unsigned nsteps, float burnin_fraction, int debug_mode);
+int sxmc_batch_nrows(sxmc_batch* b, int slot, long* nrows_out, long* accepted_out);
+int sxmc_batch_read(sxmc_batch* b, int slot, float* rows_out, long max_rows);
+int sxmc_batch_read_trace(sxmc_batch* b, int slot, double* nll_trace_out, double* proposed_out,
+                          unsigned nsteps);
+int sxmc_batch_contour(sxmc_batch* b, int slot, float delta, float* lower_out, float* upper_out,
+                       float* point_out, float* lmin_out, long* ncontour_out);
+/* device time of the last sxmc_batch_run launch (all chains, all steps) */
+int sxmc_batch_loop_ms(sxmc_batch* b, float* ms_out);
+
 /* ---- multi-GPU (no reference counterpart) ------------------------------- */
 int sxmc_comm_unique_id(void* id128_out);                 /* ncclGetUniqueId, 128 bytes */
 int sxmc_comm_create(const void* id128, int nranks, int rank, sxmc_comm** out);

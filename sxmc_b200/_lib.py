@@ -110,6 +110,19 @@ SYMBOLS = {
     "sxmc_rows_contour": (C.c_int, [c_vp, C.c_long, C.c_int, C.c_float, c_fp, c_fp, c_fp, c_fp,
                                     C.POINTER(C.c_long)]),
     "sxmc_chain_contour": (C.c_int, [c_vp, C.c_float, c_fp, c_fp, c_fp, c_fp, C.POINTER(C.c_long)]),
+    "sxmc_batch_create": (C.c_int, [C.POINTER(ChainConfig), C.c_int, C.POINTER(c_vp)]),
+    "sxmc_batch_destroy": (C.c_int, [c_vp]),
+    "sxmc_batch_set_seed": (C.c_int, [c_vp, C.c_int, C.c_uint64, C.c_uint64]),
+    "sxmc_batch_set_tapes": (C.c_int, [c_vp, C.c_int, c_dp, _SIZE, c_dp, _SIZE]),
+    "sxmc_batch_set_data": (C.c_int, [c_vp, C.c_int, c_fp, _SIZE]),
+    "sxmc_batch_generate_data": (C.c_int, [c_vp, C.c_int, c_vp, C.c_int, C.c_uint64, C.c_uint64, c_up]),
+    "sxmc_batch_enable_trace": (C.c_int, [c_vp, C.c_int]),
+    "sxmc_batch_run": (C.c_int, [c_vp, C.c_int, C.c_uint, C.c_float, C.c_int]),
+    "sxmc_batch_nrows": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
+    "sxmc_batch_read": (C.c_int, [c_vp, C.c_int, c_fp, C.c_long]),
+    "sxmc_batch_read_trace": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_uint]),
+    "sxmc_batch_contour": (C.c_int, [c_vp, C.c_int, C.c_float, c_fp, c_fp, c_fp, c_fp, C.POINTER(C.c_long)]),
+    "sxmc_batch_loop_ms": (C.c_int, [c_vp, c_fp]),
     "sxmc_comm_unique_id": (C.c_int, [c_vp]),
     "sxmc_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "sxmc_comm_destroy": (C.c_int, [c_vp]),

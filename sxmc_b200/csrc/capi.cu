@@ -963,29 +963,29 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
 namespace sxmc {
 
 // Host-side initial state: the block of src/mcmc.cpp:152-228.
-static void chain_init_state(sxmc_chain* c, ChainState& s, unsigned nsteps, float burnin_fraction,
-                             int debug_mode) {
+static void init_state_common(ChainState& s, int np, int nsources, int nsignals, const double* means,
+                              const double* sigmas, const int* fixed, unsigned nsteps, float burnin_fraction,
+                              int debug_mode) {
   memset(&s, 0, sizeof s);
-  const int np = c->nparameters;
   int nfloat = 0;
   for (int i = 0; i < np; ++i) {
-    s.current[i] = c->means[i];
-    s.proposed[i] = c->means[i];
-    s.means[i] = c->means[i];
-    s.sigmas[i] = c->sigmas[i];
-    s.fixed[i] = c->fixed[i];
-    nfloat += c->fixed[i] ? 0 : 1;
+    s.current[i] = means[i];
+    s.proposed[i] = means[i];
+    s.means[i] = means[i];
+    s.sigmas[i] = sigmas[i];
+    s.fixed[i] = fixed[i];
+    nfloat += fixed[i] ? 0 : 1;
   }
   const float scale_factor = 2.4 * 2.4 / nfloat;   // Haario, 2001 (src/mcmc.cpp:199)
   s.scale_factor = scale_factor;
   for (int i = 0; i < np; ++i) {
-    if (c->fixed[i]) { s.jump_width[i] = -1; continue; }
-    float mean = c->means[i];
-    float sigma = c->sigmas[i];
+    if (fixed[i]) { s.jump_width[i] = -1; continue; }
+    float mean = means[i];
+    float sigma = sigmas[i];
     float width = 0.1;
     if (sigma > 0) {
       width = sigma;
-    } else if (i < c->nsignals) {     // sic: nsignals, not nsources (src/mcmc.cpp:217)
+    } else if (i < nsignals) {     // sic: nsignals, not nsources (src/mcmc.cpp:217)
       float m = std::max(mean, (float)10);
       width = sqrt(m) / m;
     } else {
@@ -994,11 +994,17 @@ static void chain_init_state(sxmc_chain* c, ChainState& s, unsigned nsteps, floa
     s.jump_width[i] = 0.1 * width * scale_factor;
   }
   s.nparameters = np;
-  s.nsources = c->nsources;
-  s.nsignals = c->nsignals;
+  s.nsources = nsources;
+  s.nsignals = nsignals;
   s.debug_mode = debug_mode;
   s.step = 0;
   s.burnin_steps = nsteps * burnin_fraction;        // src/mcmc.cpp:152
+}
+
+static void chain_init_state(sxmc_chain* c, ChainState& s, unsigned nsteps, float burnin_fraction,
+                             int debug_mode) {
+  init_state_common(s, c->nparameters, c->nsources, c->nsignals, c->means.data(), c->sigmas.data(),
+                    c->fixed.data(), nsteps, burnin_fraction, debug_mode);
   s.seed = c->seed;
   s.stream_id = c->stream_id;
   s.tape_normals = c->tape_n_dev; s.n_normals = c->n_tape_n;
@@ -1582,5 +1588,307 @@ int sxmc_chain_contour(sxmc_chain* c, float delta, float* lower_out, float* uppe
   return sxmc_rows_contour(c->rows_dev, n, c->nparameters, delta, lower_out, upper_out, point_out, lmin_out,
                            ncontour_out);
 }
+
+}  // extern "C"
+
+// =========================================================================================
+// Chain batch: many chains over the same PDFs in one cooperative launch (batch_kernels.cu)
+// =========================================================================================
+struct BatchSlot {
+  uint64_t seed = 0, stream_id = 0;
+  int* read_bins = nullptr; size_t rb_cap = 0;       // [nrb][rb_cap]
+  size_t nevents = 0;
+  float* rows = nullptr; long long row_cap = 0;
+  double* tape_n = nullptr; size_t n_tape_n = 0;
+  double* tape_u = nullptr; size_t n_tape_u = 0;
+  double* nll_trace = nullptr; double* prop_trace = nullptr; unsigned trace_steps = 0;
+  long long nrows = 0, accepted = 0;
+};
+
+struct sxmc_batch {
+  int nsources = 0, nsignals = 0, nparameters = 0, nobs = 0, nsystematics = 0;
+  bool systematics_fixed = true;
+  std::vector<double> means, sigmas, nexpected;
+  std::vector<int> fixed;
+  std::vector<unsigned> n_mc;
+  std::vector<short> source_id;
+  std::vector<sxmc_hist*> pdfs;
+  int total_nbins = 0, max_chains = 0;
+  bool shared_rb = true;            // every signal reads the same dataset: one read_bins array per slot
+  size_t hist_words = 0;
+  cudaStream_t stream = nullptr;
+  ChainState* st_dev = nullptr;
+  ChainState* st_host = nullptr;    // pinned [max_chains]
+  unsigned* hist_dev = nullptr;
+  NllSignal* sigs_dev = nullptr;
+  long long* nevents_dev = nullptr;
+  unsigned* sync_dev = nullptr;
+  unsigned* sync_host = nullptr;
+  float* points_dev = nullptr; size_t points_cap = 0;
+  std::vector<BatchSlot> slots;
+  Batch jobs;
+  bool trace = false;
+  float loop_ms = 0;
+  int last_n = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+extern "C" {
+
+int sxmc_batch_destroy(sxmc_batch* b) {
+  if (!b) return SXMC_OK;
+  if (b->stream) cudaStreamSynchronize(b->stream);
+  for (BatchSlot& s : b->slots) {
+    cudaFree(s.read_bins); cudaFree(s.rows); cudaFree(s.tape_n); cudaFree(s.tape_u);
+    cudaFree(s.nll_trace); cudaFree(s.prop_trace);
+  }
+  cudaFree(b->st_dev); cudaFree(b->hist_dev); cudaFree(b->sigs_dev); cudaFree(b->nevents_dev);
+  cudaFree(b->sync_dev); cudaFree(b->points_dev);
+  if (b->st_host) cudaFreeHost(b->st_host);
+  if (b->sync_host) cudaFreeHost(b->sync_host);
+  b->jobs.release();
+  if (b->ev0) cudaEventDestroy(b->ev0);
+  if (b->ev1) cudaEventDestroy(b->ev1);
+  if (b->stream) cudaStreamDestroy(b->stream);
+  delete b;
+  return SXMC_OK;
+}
+
+int sxmc_batch_create(const sxmc_chain_config* cfg, int max_chains, sxmc_batch** out) {
+  if (!cfg || !out) SXMC_INVAL("sxmc_batch_create: NULL argument");
+  *out = nullptr;
+  if (max_chains < 1 || max_chains > BATCH_MAX_CHAINS) SXMC_INVAL("sxmc_batch_create: 1..148 chains per batch");
+  if (cfg->nparameters <= 0 || cfg->nparameters > SXMC_MAX_PARAMETERS)
+    SXMC_INVAL("sxmc_batch_create: nparameters out of range (SXMC_MAX_PARAMETERS)");
+  if (cfg->nsignals <= 0 || cfg->nsignals > 128) SXMC_INVAL("sxmc_batch_create: nsignals out of range (1..128)");
+  if (cfg->nsources <= 0 || cfg->nsources > cfg->nparameters) SXMC_INVAL("sxmc_batch_create: nsources out of range");
+  SXMC_TRY(ensure_init());
+  sxmc_batch* b = new sxmc_batch;
+  b->nsources = cfg->nsources; b->nsignals = cfg->nsignals; b->nparameters = cfg->nparameters;
+  b->nobs = cfg->nobservables; b->nsystematics = cfg->nsystematics;
+  b->systematics_fixed = cfg->systematics_fixed != 0;
+  b->means.assign(cfg->parameter_means, cfg->parameter_means + cfg->nparameters);
+  b->sigmas.assign(cfg->parameter_sigma, cfg->parameter_sigma + cfg->nparameters);
+  b->fixed.assign(cfg->parameter_fixed, cfg->parameter_fixed + cfg->nparameters);
+  b->pdfs.assign(cfg->pdfs, cfg->pdfs + cfg->nsignals);
+  b->nexpected.assign(cfg->nexpected, cfg->nexpected + cfg->nsignals);
+  b->n_mc.assign(cfg->n_mc, cfg->n_mc + cfg->nsignals);
+  b->source_id.assign(cfg->source_id, cfg->source_id + cfg->nsignals);
+  b->total_nbins = b->pdfs[0]->total_nbins;
+  b->max_chains = max_chains;
+  for (int j = 0; j < b->nsignals; ++j) {
+    if (b->pdfs[j]->total_nbins != b->total_nbins || b->pdfs[j]->nobs != b->nobs) {
+      delete b;
+      SXMC_INVAL("sxmc_batch_create: all signal PDFs must share the observables' binning");
+    }
+    if (b->source_id[j] < 0 || b->source_id[j] >= b->nsources) { delete b; SXMC_INVAL("sxmc_batch_create: source_id out of range"); }
+    if (b->pdfs[j]->dataset != b->pdfs[0]->dataset) b->shared_rb = false;
+  }
+  b->hist_words = (size_t)b->nsignals * ((size_t)b->total_nbins + 1);
+  b->slots.resize(max_chains);
+  cudaError_t e = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMalloc(&b->st_dev, sizeof(ChainState) * max_chains);
+  if (e == cudaSuccess) e = cudaMallocHost(&b->st_host, sizeof(ChainState) * max_chains);
+  if (e == cudaSuccess) e = cudaMalloc(&b->hist_dev, sizeof(unsigned) * b->hist_words * max_chains);
+  if (e == cudaSuccess) e = cudaMalloc(&b->sigs_dev, sizeof(NllSignal) * b->nsignals * max_chains);
+  if (e == cudaSuccess) e = cudaMalloc(&b->nevents_dev, sizeof(long long) * max_chains);
+  if (e == cudaSuccess) e = cudaMalloc(&b->sync_dev, sizeof(unsigned) * 4);
+  if (e == cudaSuccess) e = cudaMallocHost(&b->sync_host, sizeof(unsigned) * 4);
+  if (e == cudaSuccess) e = cudaEventCreate(&b->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&b->ev1);
+  if (e != cudaSuccess) { sxmc_batch_destroy(b); return cuda_fail(e, "sxmc_batch_create", __FILE__, __LINE__); }
+  // the binning jobs (columns, systematic programs); outputs are addressed by the kernel itself
+  int rc = b->jobs.reserve(b->nsignals);
+  for (int j = 0; j < b->nsignals && !rc; ++j)
+    rc = fill_job(b->pdfs[j], b->jobs.host[j], nullptr, nullptr, nullptr, 1);
+  if (!rc) { b->jobs.n_ep = 0; plan_launch(b->jobs, b->nsignals); }
+  if (rc) { sxmc_batch_destroy(b); return rc; }
+  *out = b;
+  return SXMC_OK;
+}
+
+static int batch_slot(sxmc_batch* b, int slot, BatchSlot** out) {
+  if (!b || slot < 0 || slot >= b->max_chains) SXMC_INVAL("sxmc_batch: slot out of range");
+  *out = &b->slots[slot];
+  return SXMC_OK;
+}
+
+int sxmc_batch_set_seed(sxmc_batch* b, int slot, uint64_t seed, uint64_t stream_id) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  s->seed = seed; s->stream_id = stream_id;
+  return SXMC_OK;
+}
+
+int sxmc_batch_set_tapes(sxmc_batch* b, int slot, const double* normals, size_t n_normals,
+                         const double* uniforms, size_t n_uniforms) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  cudaFree(s->tape_n); cudaFree(s->tape_u);
+  s->tape_n = nullptr; s->tape_u = nullptr; s->n_tape_n = 0; s->n_tape_u = 0;
+  if (normals && uniforms) {
+    SXMC_CUDA(cudaMalloc(&s->tape_n, sizeof(double) * std::max<size_t>(1, n_normals)));
+    SXMC_CUDA(cudaMalloc(&s->tape_u, sizeof(double) * std::max<size_t>(1, n_uniforms)));
+    SXMC_CUDA(cudaMemcpy(s->tape_n, normals, sizeof(double) * n_normals, cudaMemcpyHostToDevice));
+    SXMC_CUDA(cudaMemcpy(s->tape_u, uniforms, sizeof(double) * n_uniforms, cudaMemcpyHostToDevice));
+    s->n_tape_n = n_normals; s->n_tape_u = n_uniforms;
+  }
+  return SXMC_OK;
+}
+
+// SetEvalPoints of every PDF for one slot, from DEVICE rows (src/pdfz.cpp:245-302)
+static int batch_slot_points(sxmc_batch* b, BatchSlot* s, const float* points_dev, size_t nevents) {
+  const int nrb = b->shared_rb ? 1 : b->nsignals;
+  if (s->rb_cap < nevents || !s->read_bins) {
+    cudaFree(s->read_bins);
+    s->read_bins = nullptr;
+    s->rb_cap = std::max<size_t>(nevents + nevents / 8 + 64, 256);
+    SXMC_CUDA(cudaMalloc(&s->read_bins, sizeof(int) * s->rb_cap * nrb));
+  }
+  s->nevents = nevents;
+  for (int j = 0; j < nrb; ++j) {
+    PrepGeo g;
+    fill_prep_geo(b->pdfs[j], g);
+    SXMC_TRY(launch_read_bins(points_dev, (long long)nevents, b->nobs, g, b->pdfs[j]->dataset,
+                              s->read_bins + (size_t)j * s->rb_cap, b->stream));
+  }
+  return SXMC_OK;
+}
+
+int sxmc_batch_set_data(sxmc_batch* b, int slot, const float* data, size_t data_nfloats) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  if (data_nfloats % (size_t)(b->nobs + 1) != 0)
+    SXMC_INVAL("Number of entries in evaluation points array not divisible by number of observables.");
+  if (b->points_cap < data_nfloats) {
+    SXMC_CUDA(cudaStreamSynchronize(b->stream));
+    cudaFree(b->points_dev);
+    b->points_dev = nullptr;
+    b->points_cap = data_nfloats + data_nfloats / 4 + 1024;
+    SXMC_CUDA(cudaMalloc(&b->points_dev, sizeof(float) * b->points_cap));
+  }
+  if (data_nfloats)
+    SXMC_CUDA(cudaMemcpyAsync(b->points_dev, data, sizeof(float) * data_nfloats, cudaMemcpyHostToDevice, b->stream));
+  SXMC_TRY(batch_slot_points(b, s, b->points_dev, data_nfloats / (size_t)(b->nobs + 1)));
+  SXMC_CUDA(cudaStreamSynchronize(b->stream));   // points_dev is reused by the next slot
+  return SXMC_OK;
+}
+
+int sxmc_batch_generate_data(sxmc_batch* b, int slot, sxmc_generator* g, int poisson, uint64_t seed,
+                             uint64_t stream_id, unsigned* observed_out) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  if (!g || g->nobs != b->nobs) SXMC_INVAL("sxmc_batch_generate_data: generator does not match the fit");
+  unsigned long long ne = 0;
+  SXMC_TRY(generator_draw(g, poisson, seed, stream_id, &ne));   // synchronises the generator's stream
+  if (observed_out) for (int j = 0; j < g->n; ++j) observed_out[j] = (unsigned)g->counts_host[j];
+  SXMC_TRY(batch_slot_points(b, s, g->events_dev, (size_t)ne));
+  SXMC_CUDA(cudaStreamSynchronize(b->stream));   // the generator's buffer is overwritten by the next draw
+  return SXMC_OK;
+}
+
+int sxmc_batch_enable_trace(sxmc_batch* b, int on) { b->trace = on != 0; return SXMC_OK; }
+
+// MCMC::operator() (src/mcmc.cpp:143-387) for slots [0, nchains) at once.
+int sxmc_batch_run(sxmc_batch* b, int nchains, unsigned nsteps, float burnin_fraction, int debug_mode) {
+  if (!b || nchains < 1 || nchains > b->max_chains) SXMC_INVAL("sxmc_batch_run: nchains out of range");
+  const int np = b->nparameters, ns = b->nsignals;
+  BatchPlan plan;
+  SXMC_TRY(plan_chain_batch(b->jobs.launch, nchains, &plan));
+  std::vector<NllSignal> sg((size_t)nchains * ns);
+  std::vector<long long> nev(nchains);
+  for (int e = 0; e < nchains; ++e) {
+    BatchSlot& s = b->slots[e];
+    if (!s.read_bins) { set_error("sxmc_batch_run: a slot has no data (sxmc_batch_set_data)"); return SXMC_ESTATE; }
+    if (s.row_cap < (long long)nsteps || !s.rows) {
+      cudaFree(s.rows);
+      s.rows = nullptr;
+      s.row_cap = std::max<long long>(1, nsteps);
+      SXMC_CUDA(cudaMalloc(&s.rows, sizeof(float) * (size_t)s.row_cap * (np + 1)));
+    }
+    if (b->trace && s.trace_steps < nsteps) {
+      cudaFree(s.nll_trace); cudaFree(s.prop_trace);
+      s.nll_trace = nullptr; s.prop_trace = nullptr;
+      SXMC_CUDA(cudaMalloc(&s.nll_trace, sizeof(double) * std::max(1u, nsteps)));
+      SXMC_CUDA(cudaMalloc(&s.prop_trace, sizeof(double) * std::max(1u, nsteps) * np));
+      s.trace_steps = nsteps;
+    }
+    ChainState& st = b->st_host[e];
+    init_state_common(st, np, b->nsources, ns, b->means.data(), b->sigmas.data(), b->fixed.data(), nsteps,
+                      burnin_fraction, debug_mode);
+    st.seed = s.seed; st.stream_id = s.stream_id;
+    st.tape_normals = s.tape_n; st.n_normals = s.n_tape_n;
+    st.tape_uniforms = s.tape_u; st.n_uniforms = s.n_tape_u;
+    st.rows = s.rows; st.row_cap = s.row_cap;
+    st.nll_trace = b->trace ? s.nll_trace : nullptr;
+    st.prop_trace = b->trace ? s.prop_trace : nullptr;
+    for (int j = 0; j < ns; ++j) {
+      NllSignal& q = sg[(size_t)e * ns + j];
+      memset(&q, 0, sizeof q);
+      q.read_bins = s.read_bins + (b->shared_rb ? 0 : (size_t)j * s.rb_cap);
+      q.nexpected = b->nexpected[j];
+      q.bin_volume = b->pdfs[j]->bin_volume;
+      q.n_mc = b->n_mc[j];
+      q.total_nbins = b->total_nbins;
+      q.source_id = b->source_id[j];
+    }
+    nev[e] = (long long)s.nevents;
+  }
+  SXMC_CUDA(cudaMemcpyAsync(b->st_dev, b->st_host, sizeof(ChainState) * nchains, cudaMemcpyHostToDevice, b->stream));
+  SXMC_CUDA(cudaMemcpyAsync(b->sigs_dev, sg.data(), sizeof(NllSignal) * sg.size(), cudaMemcpyHostToDevice, b->stream));
+  SXMC_CUDA(cudaMemcpyAsync(b->nevents_dev, nev.data(), sizeof(long long) * nchains, cudaMemcpyHostToDevice, b->stream));
+  SXMC_CUDA(cudaMemsetAsync(b->hist_dev, 0, sizeof(unsigned) * b->hist_words * nchains, b->stream));
+  SXMC_CUDA(cudaMemsetAsync(b->sync_dev, 0, sizeof(unsigned) * 4, b->stream));
+  BatchParams Q;
+  memset(&Q, 0, sizeof Q);
+  Q.st = b->st_dev; Q.sigs = b->sigs_dev; Q.hist = b->hist_dev; Q.hist_words = b->hist_words;
+  Q.nevents = b->nevents_dev; Q.sync = b->sync_dev;
+  Q.nchains = nchains; Q.ns = ns; Q.np = np; Q.nsources = b->nsources;
+  Q.nsteps = nsteps; Q.do_init = 1;
+  Q.rebin = (b->nsystematics > 0 && !b->systematics_fixed) ? 1 : 0;   // src/mcmc.cpp:264
+  SXMC_CUDA(cudaEventRecord(b->ev0, b->stream));
+  SXMC_TRY(launch_chain_batch(plan, Q, b->stream));
+  SXMC_CUDA(cudaEventRecord(b->ev1, b->stream));
+  SXMC_CUDA(cudaMemcpyAsync(b->sync_host, b->sync_dev, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost, b->stream));
+  SXMC_CUDA(cudaMemcpyAsync(b->st_host, b->st_dev, sizeof(ChainState) * nchains, cudaMemcpyDeviceToHost, b->stream));
+  SXMC_CUDA(cudaStreamSynchronize(b->stream));
+  if (b->sync_host[3]) { set_error("chain batch kernel timed out at a grid barrier"); return SXMC_ESTATE; }
+  SXMC_CUDA(cudaEventElapsedTime(&b->loop_ms, b->ev0, b->ev1));
+  for (int e = 0; e < nchains; ++e) {
+    b->slots[e].nrows = b->st_host[e].nrows;
+    b->slots[e].accepted = b->st_host[e].accepted;
+  }
+  b->last_n = nchains;
+  return SXMC_OK;
+}
+
+int sxmc_batch_nrows(sxmc_batch* b, int slot, long* nrows_out, long* accepted_out) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  if (nrows_out) *nrows_out = (long)std::min(s->nrows, s->row_cap);
+  if (accepted_out) *accepted_out = (long)s->accepted;
+  return SXMC_OK;
+}
+
+int sxmc_batch_read(sxmc_batch* b, int slot, float* rows_out, long max_rows) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  const long long n = std::min<long long>(std::min(s->nrows, s->row_cap), max_rows);
+  if (n > 0)
+    SXMC_CUDA(cudaMemcpy(rows_out, s->rows, sizeof(float) * (size_t)n * (b->nparameters + 1), cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+
+int sxmc_batch_read_trace(sxmc_batch* b, int slot, double* nll_trace_out, double* proposed_out, unsigned nsteps) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  if (!s->nll_trace || nsteps > s->trace_steps) { set_error("sxmc_batch_read_trace: trace not enabled"); return SXMC_ESTATE; }
+  SXMC_CUDA(cudaMemcpy(nll_trace_out, s->nll_trace, sizeof(double) * nsteps, cudaMemcpyDeviceToHost));
+  SXMC_CUDA(cudaMemcpy(proposed_out, s->prop_trace, sizeof(double) * nsteps * b->nparameters, cudaMemcpyDeviceToHost));
+  return SXMC_OK;
+}
+
+int sxmc_batch_contour(sxmc_batch* b, int slot, float delta, float* lower_out, float* upper_out,
+                       float* point_out, float* lmin_out, long* ncontour_out) {
+  BatchSlot* s; SXMC_TRY(batch_slot(b, slot, &s));
+  const long n = (long)std::min(s->nrows, s->row_cap);
+  return sxmc_rows_contour(s->rows, n, b->nparameters, delta, lower_out, upper_out, point_out, lmin_out,
+                           ncontour_out);
+}
+
+int sxmc_batch_loop_ms(sxmc_batch* b, float* ms_out) { *ms_out = b->loop_ms; return SXMC_OK; }
 
 }  // extern "C"

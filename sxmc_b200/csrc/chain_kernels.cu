@@ -24,24 +24,13 @@
 #include "kernels.h"
 #include "bin_device.cuh"
 #include "nll_device.cuh"
+#include "grid_sync.cuh"
 
 #include <cstring>
 
 namespace sxmc {
 
 constexpr int PK_MAX_SIGNALS = 128;
-constexpr long long PK_TIMEOUT_CYCLES = 4000000000ll;   // ~2 s at 1.9 GHz
-
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
 // phase stamps of CTA 0 (debug/profiling): [step][8] ns, first PK_STAMP_STEPS steps of a launch
 constexpr unsigned PK_STAMP_STEPS = 64;
 #define PK_STAMP(slot)                                                                       \
@@ -56,37 +45,6 @@ constexpr unsigned PK_CTA_STEP = 20;
     if (Q.stamps && threadIdx.x == 0 && s == PK_CTA_STEP && blockIdx.x < 256)                 \
       Q.stamps[512 + blockIdx.x * 4 + (slot)] = globaltimer_ns();                             \
   } while (0)
-__device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// thread 0 spins until *p >= target (wrap-safe); false on abort/timeout.  Ends with a CTA barrier.
-__device__ __forceinline__ bool cta_wait_ge(const unsigned* p, unsigned target, unsigned* abort_flag,
-                                            int* s_ok) {
-  if (threadIdx.x == 0) {
-    int ok = 1;
-    const long long t0 = clock64();
-    unsigned n = 0;
-    while ((int)(ld_acquire_u32(p) - target) < 0) {
-      if ((++n & 255u) == 0) {
-        if (ld_acquire_u32(abort_flag)) { ok = 0; break; }
-        if (clock64() - t0 > PK_TIMEOUT_CYCLES) { atomicExch(abort_flag, 1u); ok = 0; break; }
-      }
-    }
-    *s_ok = ok;
-  }
-  __syncthreads();
-  return *s_ok != 0;
-}
-
-// all threads' prior global writes become visible before the counter moves
-__device__ __forceinline__ void cta_arrive(unsigned* counter) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(counter, 1u);
-  }
-}
 
 template <int NOBS, int NS, bool SMEM, int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(FAST_THREADS, 1)

@@ -113,6 +113,23 @@ struct PersistParams {
   unsigned long long* stamps;   // optional [64][8] phase timestamps of CTA 0 (ns), profiling only
 };
 
+// Arguments of the chain batch kernel (batch_kernels.cu), by value.
+constexpr int BATCH_MAX_CHAINS = 148;   // one chain per SM in the lookup/tail phase
+constexpr int BATCH_MAX_GROUP = 8;      // chains binned per shared-memory histogram pass
+struct BatchParams {
+  ChainState* st;               // [nchains]
+  const NllSignal* sigs;        // [nchains][ns]: per-chain read_bins; bins/norm unused here
+  unsigned* hist;               // [nchains][hist_words]: [ns][total_nbins] bins + norms[ns]
+  unsigned long long hist_words;
+  const long long* nevents;     // [nchains]
+  unsigned* sync;               // [0] barrier counter, [3] abort
+  int nchains, ns, np, nsources;
+  unsigned nsteps;              // MCMC steps of every chain in this launch
+  int do_init;                  // first super-step = initial evaluation + first proposal
+  int rebin;
+  int group;
+};
+
 // One signal as seen by the lookup + event-likelihood kernel.
 struct NllSignal {
   const unsigned* bins;       // histogram of this step

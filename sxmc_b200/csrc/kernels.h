@@ -87,6 +87,15 @@ int launch_nll_lut(const float* lut, size_t ne, size_t ns, const double* pars, s
                    const double* nexpected, const unsigned* n_mc, const short* source_id,
                    const unsigned* norms, double* out2_dev, cudaStream_t stream);
 
+// ---- batch_kernels.cu ----
+struct BatchPlan {
+  BinLaunch launch;   // shared-memory plan of the resident samples beside `group` histograms
+  int group;
+  int grid;
+};
+int plan_chain_batch(const BinLaunch& L, int nchains, BatchPlan* plan);
+int launch_chain_batch(const BatchPlan& plan, const BatchParams& Q, cudaStream_t stream);
+
 // ---- ensemble_kernels.cu ----
 int launch_cum(const unsigned* bins_dev, int nb, unsigned* cum_dev, cudaStream_t stream);
 int launch_generate(const GenSignal* sigs_dev, int n, const GenGeo& geo, int poisson,

@@ -71,6 +71,12 @@ class MCMC:
     """MCMC(sources, signals, systematics, observables) (src/mcmc.cpp:28-130)."""
 
     def __init__(self, sources, signals, systematics, observables):
+        self._configure(sources, signals, systematics, observables)
+        self._c = c_vp()
+        _check(lib().sxmc_chain_create(C.byref(self._cfg), C.byref(self._c)))
+        self.nrows = 0
+
+    def _configure(self, sources, signals, systematics, observables):
         self.nsources, self.nsignals = len(sources), len(signals)
         self.nsystematics, self.nobservables = len(systematics), len(observables)
         means, sigmas, fixed = [], [], []
@@ -99,13 +105,10 @@ class MCMC:
         self._sid = np.asarray([s.source.index for s in signals], dtype=np.int16)
         self._pdfs = [s.histogram for s in signals]
         self._harr = (c_vp * self.nsignals)(*[h._h for h in self._pdfs])
-        cfg = ChainConfig(self.nsources, self.nsignals, self.nparameters, self.nobservables,
-                          ptr(self._means, c_dp), ptr(self._sigmas, c_dp), ptr(self._fixed, c_ip),
-                          int(self.systematics_fixed), self.nsystematics, self._harr,
-                          ptr(self._nexp, c_dp), ptr(self._n_mc, c_up), ptr(self._sid, c_sp))
-        self._c = c_vp()
-        _check(lib().sxmc_chain_create(C.byref(cfg), C.byref(self._c)))
-        self.nrows = 0
+        self._cfg = ChainConfig(self.nsources, self.nsignals, self.nparameters, self.nobservables,
+                                ptr(self._means, c_dp), ptr(self._sigmas, c_dp), ptr(self._fixed, c_ip),
+                                int(self.systematics_fixed), self.nsystematics, self._harr,
+                                ptr(self._nexp, c_dp), ptr(self._n_mc, c_up), ptr(self._sid, c_sp))
 
     def close(self):
         if self._c:
@@ -246,7 +249,92 @@ class MCMC:
         return out
 
 
-def build_fit(fit, sort=True):
+class MCMCBatch:
+    """Up to 148 MCMC objects over the same signals advanced by one launch (`sxmc_batch_*`):
+    the experiments of an ensemble.  Constructor arguments as for ``MCMC``."""
+
+    def __init__(self, sources, signals, systematics, observables, max_chains=148):
+        proto = MCMC.__new__(MCMC)
+        proto._c = c_vp()
+        MCMC._configure(proto, sources, signals, systematics, observables)
+        self._proto = proto
+        self.nparameters, self.nobservables = proto.nparameters, proto.nobservables
+        self.parameter_names = proto.parameter_names
+        self.max_chains = int(max_chains)
+        self._b = c_vp()
+        _check(lib().sxmc_batch_create(C.byref(proto._cfg), self.max_chains, C.byref(self._b)))
+
+    def close(self):
+        if self._b:
+            lib().sxmc_batch_destroy(self._b)
+            self._b = c_vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_seed(self, slot, seed, stream_id=0):
+        _check(lib().sxmc_batch_set_seed(self._b, int(slot), int(seed), int(stream_id)))
+
+    def set_tapes(self, slot, normals, uniforms):
+        n = np.ascontiguousarray(normals, dtype=np.float64)
+        u = np.ascontiguousarray(uniforms, dtype=np.float64)
+        _check(lib().sxmc_batch_set_tapes(self._b, int(slot), ptr(n, c_dp), n.size, ptr(u, c_dp), u.size))
+
+    def set_data(self, slot, data):
+        d = np.ascontiguousarray(data, dtype=np.float32).ravel()
+        dd = d if d.size else np.zeros(1, np.float32)
+        _check(lib().sxmc_batch_set_data(self._b, int(slot), ptr(dd, c_fp), d.size))
+
+    def generate_data(self, slot, generator, poisson=True, seed=0, experiment=0):
+        observed = np.zeros(generator.nsignals, dtype=np.uint32)
+        _check(lib().sxmc_batch_generate_data(self._b, int(slot), generator._g, int(bool(poisson)), int(seed),
+                                              int(experiment), ptr(observed, c_up)))
+        return observed
+
+    def enable_trace(self, on=True):
+        _check(lib().sxmc_batch_enable_trace(self._b, int(on)))
+
+    def run(self, nchains, nsteps, burnin_fraction, debug_mode=False):
+        _check(lib().sxmc_batch_run(self._b, int(nchains), int(nsteps), float(burnin_fraction), int(debug_mode)))
+
+    def nrows(self, slot):
+        a, b = C.c_long(0), C.c_long(0)
+        _check(lib().sxmc_batch_nrows(self._b, int(slot), C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def rows(self, slot):
+        n, _ = self.nrows(slot)
+        rows = np.zeros((max(1, n), self.nparameters + 1), dtype=np.float32)
+        _check(lib().sxmc_batch_read(self._b, int(slot), ptr(rows, c_fp), rows.shape[0]))
+        return rows[:n]
+
+    def likelihood_space(self, slot):
+        return LikelihoodSpace(self.rows(slot), self.parameter_names)
+
+    def read_trace(self, slot, nsteps):
+        nll = np.zeros(max(1, nsteps), dtype=np.float64)
+        prop = np.zeros((max(1, nsteps), self.nparameters), dtype=np.float64)
+        _check(lib().sxmc_batch_read_trace(self._b, int(slot), ptr(nll, c_dp), ptr(prop, c_dp), int(nsteps)))
+        return nll[:nsteps], prop[:nsteps]
+
+    def contour(self, slot, delta):
+        np_ = self.nparameters
+        lo, up, pt = (np.zeros(np_, np.float32) for _ in range(3))
+        lmin, nc = C.c_float(0), C.c_long(0)
+        _check(lib().sxmc_batch_contour(self._b, int(slot), float(delta), ptr(lo, c_fp), ptr(up, c_fp),
+                                        ptr(pt, c_fp), C.byref(lmin), C.byref(nc)))
+        return lo, up, pt, float(lmin.value), int(nc.value)
+
+    def loop_ms(self):
+        v = C.c_float(0)
+        _check(lib().sxmc_batch_loop_ms(self._b, C.byref(v)))
+        return v.value
+
+
+def build_fit(fit, sort=True, batch=0):
     """FitSpec (sxmc_b200.workloads) -> (hists, MCMC), the way src/signal.cpp:112-169 and
     src/sxmc.cpp:96 wire the reference objects."""
     hists = []
@@ -272,5 +360,8 @@ def build_fit(fit, sort=True):
              for i, y in enumerate(fit.systematics)]
     signals = [Signal("sig%d" % j, hists[j], sig.nexpected, sig.n_mc, sources[sig.source])
                for j, sig in enumerate(fit.signals)]
-    mc = MCMC(sources, signals, systs, [Observable("o%d" % i) for i in range(fit.nobs)])
+    observables = [Observable("o%d" % i, float(fit.lower[i]), float(fit.upper[i])) for i in range(fit.nobs)]
+    if batch:
+        return hists, MCMCBatch(sources, signals, systs, observables, batch)
+    mc = MCMC(sources, signals, systs, observables)
     return hists, mc

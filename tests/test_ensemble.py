@@ -149,3 +149,113 @@ def test_ensemble_limits_are_reproducible_and_cover_the_truth():
     assert np.array_equal(lim[1::2], np.asarray(b["limits"]))
     assert np.mean(lim > 1.0) >= 0.7          # upper edge of a 90 % contour: mostly above truth
     assert np.all(lim < 2.0)
+
+
+# ---------------------------------------------------------------------------------------
+# chain batch: many chains over the same samples in one cooperative launch
+# ---------------------------------------------------------------------------------------
+def _with_data(fit, data):
+    import copy
+    f = copy.copy(fit)
+    f.data = np.ascontiguousarray(data, dtype=np.float32)
+    return f
+
+
+@pytest.mark.parametrize("name,scale,nchains", [("B", 0.005, 5), ("A", 0.004, 3)])
+def test_batch_tape_driven_chains_match_oracle_chains(name, scale, nchains):
+    """Every chain of a batch, fed its own tape and its own data events, reproduces the oracle
+    chain of the same inputs: proposals and accepted rows bit-identical, NLL within 1e-6."""
+    from sxmc_b200 import mcmc
+    fit = W.WORKLOADS[name](scale)
+    nsteps = 300
+    hists, batch = mcmc.build_fit(fit, batch=nchains)
+    batch.enable_trace()
+    wants = []
+    for k in range(nchains):
+        rng = np.random.default_rng(100 + k)
+        normals = rng.normal(size=(nsteps + 1) * fit.nparameters)
+        uniforms = rng.random(nsteps)
+        data = fit.data[k::nchains] if k else fit.data[:0]          # slot 0: no events at all
+        wants.append(port.mcmc(_with_data(fit, data), nsteps, 0.1, normals, uniforms, trace=True))
+        batch.set_tapes(k, normals, uniforms)
+        batch.set_data(k, data)
+    batch.run(nchains, nsteps, 0.1)
+    for k in range(nchains):
+        want = wants[k]
+        got = batch.rows(k)
+        nll_tr, prop_tr = batch.read_trace(k, nsteps)
+        assert got.shape == want["chain"].shape
+        assert batch.nrows(k)[1] == want["accepted"]
+        assert np.array_equal(prop_tr, want["prop_trace"])
+        assert np.allclose(nll_tr, want["nll_trace"], rtol=1e-6, atol=0)
+        assert np.array_equal(got[:, :-1], want["chain"][:, :-1])
+        assert np.allclose(got[:, -1], want["chain"][:, -1], rtol=1e-6)
+    batch.close()
+    for h in hists:
+        h.close()
+
+
+def test_batch_fixed_systematics_and_debug_mode():
+    from sxmc_b200 import mcmc
+    fit = W.config_A(0.004)
+    for y in fit.systematics:
+        y.fixed = True
+    nsteps = 200
+    for debug in (False, True):
+        hists, batch = mcmc.build_fit(fit, batch=2)
+        wants = []
+        for k in range(2):
+            rng = np.random.default_rng(7 + k)
+            normals = rng.normal(size=(nsteps + 1) * fit.nparameters)
+            uniforms = rng.random(nsteps)
+            wants.append(port.mcmc(fit, nsteps, 0.1, normals, uniforms, debug_mode=debug))
+            batch.set_tapes(k, normals, uniforms)
+            batch.set_data(k, fit.data)
+        batch.run(2, nsteps, 0.1, debug)
+        for k in range(2):
+            got = batch.rows(k)
+            assert got.shape == wants[k]["chain"].shape
+            assert np.array_equal(got[:, :-1], wants[k]["chain"][:, :-1])
+        batch.close()
+        for h in hists:
+            h.close()
+
+
+def test_batch_philox_chain_equals_single_chain_and_full_width_batch():
+    """148 chains at once; chain k of the batch = the one-chain path with the same (seed, stream)."""
+    from sxmc_b200 import mcmc
+    fit = W.config_B(0.01)
+    nsteps = 500
+    hists, batch = mcmc.build_fit(fit, batch=148)
+    for k in range(148):
+        batch.set_seed(k, 77, k)
+        batch.set_data(k, fit.data[(k % 7)::7])
+    batch.run(148, nsteps, 0.1)
+    h2, chain = mcmc.build_fit(fit)
+    for k in (0, 1, 73, 147):
+        chain.set_seed(77, k)
+        want = chain(fit.data[(k % 7)::7], nsteps, 0.1).get_samples()
+        got = batch.rows(k)
+        assert got.shape == want.shape and got.shape[0] == nsteps - 2 * 50
+        assert np.array_equal(got[:, :-1], want[:, :-1])
+        assert np.allclose(got[:, -1], want[:, -1], rtol=1e-6)
+        assert batch.nrows(k)[1] == chain.accepted()
+    # different streams really are different chains
+    assert not np.array_equal(batch.rows(3), batch.rows(10))
+    chain.close()
+    batch.close()
+    for h in hists + h2:
+        h.close()
+
+
+def test_batch_rejects_fits_whose_samples_do_not_fit_on_chip():
+    from sxmc_b200 import mcmc
+    from sxmc_b200._lib import SxmcError
+    fit = W.config_C(0.05)
+    hists, batch = mcmc.build_fit(fit, batch=4)
+    batch.set_data(0, fit.data)
+    with pytest.raises(SxmcError):
+        batch.run(1, 10, 0.1)
+    batch.close()
+    for h in hists:
+        h.close()
