@@ -111,7 +111,8 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * smem_hist_max_bins: histograms up to this many bins are privatised in shared memory;
  * blocks_per_sm <= 0 keeps the default;  kernel_select: 0 = automatic, bit 0 = force the
  * generic (interpreting) kernel, bit 1 = force run-time systematic dispatch in the fast
- * kernel (no compile-time program) -- both used by the parity tests to cover every path. */
+ * kernel (no compile-time program), bit 2 = the chain batch never takes its monotone endpoint
+ * path -- used by the parity tests to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
@@ -276,6 +277,9 @@ int sxmc_batch_contour(sxmc_batch* b, int slot, float delta, float* lower_out, f
                        float* point_out, float* lmin_out, long* ncontour_out);
 /* device time of the last sxmc_batch_run launch (all chains, all steps) */
 int sxmc_batch_loop_ms(sxmc_batch* b, float* ms_out);
+/* profiling hook: every CTA stamps %globaltimer at the phase boundaries of super-step 20
+ * ([148][8] ns: start, bin done, barrier out, lookup done, tail done, barrier out) */
+int sxmc_batch_phase_stamps(sxmc_batch* b, int enable, unsigned long long* out148x8);
 
 /* ---- multi-GPU (no reference counterpart) ------------------------------- */
 int sxmc_comm_unique_id(void* id128_out);                 /* ncclGetUniqueId, 128 bytes */

@@ -31,6 +31,71 @@ namespace sxmc {
 
 constexpr int BK_MAX_SIGNALS = 128;
 
+// ---- monotone programs ------------------------------------------------------------------------
+// A 1-D PDF whose systematics are all SHIFT / SCALE / CTSCALE of the observable maps a sample x
+// to its bin through a chain of monotone roundings: x -> x' -> (int)((x' - lo) * scale).  The
+// samples are sorted by x, so every thread's sequence of samples is sorted too and its bin
+// codes form contiguous runs: two samples with the same code bracket only samples with that
+// code.  The thread evaluates the two ends of its sequence (the usual case: one bin, 2
+// evaluations instead of 4 * R * chunks) and finds run boundaries by galloping + binary search.
+// Every evaluation is the reference's arithmetic on the reference's value, so the counts are
+// bit-identical to the sample-by-sample pass.  (Host-side preconditions: sorted layout, no NaN
+// and no -inf in the column -- see plan_chain_batch.)
+// code: -1 below the domain (or NaN), -2 at/above the upper edge, else the bin index.
+template <int NOPS, unsigned CODES>
+__device__ __forceinline__ int mono_code(float xf, const int (&op_code)[FAST_MAX_OPS],
+                                         const double (&op_c0)[FAST_MAX_OPS],
+                                         const double (&op_onep)[FAST_MAX_OPS], int nsyst, const Geo& geo) {
+  double f[1][4];
+  f[0][0] = f[0][1] = f[0][2] = f[0][3] = (double)xf;
+  if constexpr (NOPS < 0) {
+#pragma unroll
+    for (int k = 0; k < FAST_MAX_OPS; ++k)
+      if (k < nsyst) apply_op<1>(f, op_code[k], op_c0[k], op_onep[k]);
+  } else {
+    if constexpr (NOPS > 0) apply_static<1, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
+    if constexpr (NOPS > 1) apply_static<1, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
+    if constexpr (NOPS > 2) apply_static<1, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
+    if constexpr (NOPS > 3) apply_static<1, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
+  }
+  const double x = f[0][0];
+  if (!(x >= geo.lo[0])) return -1;
+  if (!(x < geo.hi[0])) return -2;
+  return trunc_nonneg(__dmul_rn(__dadd_rn(x, -geo.lo[0]), geo.sc[0]));
+}
+
+// k samples of code c (c < 0: outside the domain) appended to a thread's run
+__device__ __forceinline__ void run_push_n(RunAcc& r, int c, unsigned k, unsigned* hist, int total_nbins) {
+  if (c != r.cur) {
+    run_flush<true>(r, hist, total_nbins);
+    r.cur = c;
+    r.cnt = 0;
+  }
+  r.cnt += k;
+}
+
+// run_push4 with a short straight-line slow path: the run is flushed, three samples go
+// straight to the histogram, the fourth starts the new run.  (A warp executes the slow path
+// whenever ANY lane crosses a bin edge, so its length matters wherever bins are sparse.)
+__device__ __forceinline__ void run_push4_direct(RunAcc& r, const int (&b)[4], unsigned* hist, int total_nbins) {
+  if (b[0] == r.cur && b[1] == r.cur && b[2] == r.cur && b[3] == r.cur) {
+    r.cnt += 4;
+  } else {
+    run_flush<true>(r, hist, total_nbins);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      if (b[k] >= 0) { r.norm += 1; if (b[k] < total_nbins) atomicAdd(hist + b[k], 1u); }
+    r.cur = b[3];
+    r.cnt = 1;
+  }
+}
+
+__device__ __forceinline__ float lds32(unsigned addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
 template <int NOBS, int NS, int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(FAST_THREADS, 1)
 chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__ BatchParams Q) {
@@ -71,7 +136,7 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
   const bool have_work = t0 < t1;
   const int R = P.R;
   const unsigned col_bytes = (unsigned)R * 512u, stage_bytes = NS * col_bytes;
-  int nmine = 0;
+  int nmine = 0, ca_mod = 0;
   if (have_work) {
     const FastJob& job = P.job[job_j];
     const unsigned long long jbeg = P.prefix[job_j];
@@ -79,6 +144,7 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
     const unsigned long long ca = (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
     const unsigned long long cb = (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
     nmine = (int)(cb - ca);                     // <= P.S (checked on the host)
+    ca_mod = (int)(ca % (unsigned)(WT_ROWS / R));
     if (lane == 0) {
       for (int i = 0; i < nmine; ++i) {
         const unsigned b = cx.my_bar0 + 8u * i;
@@ -116,9 +182,14 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
   const int nsyst = have_work ? P.job[job_j].nsyst : 0;
   const unsigned total_super = Q.nsteps + (Q.do_init ? 1u : 0u);
 
+#define BK_STAMP(slot)                                                              \
+  do {                                                                              \
+    if (Q.stamps && tid == 0 && s == 20u) Q.stamps[blockIdx.x * 8 + (slot)] = globaltimer_ns(); \
+  } while (0)
   for (unsigned s = 0; s < total_super; ++s) {
     const int mode = (Q.do_init && s == 0) ? NLL_MODE_INIT : NLL_MODE_STEP;
     const bool bin_now = Q.rebin || mode == NLL_MODE_INIT;
+    BK_STAMP(0);
 
     // ---- bin: every chain's histogram from the resident samples ------------------------------
     if (bin_now) {
@@ -152,37 +223,86 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
             unsigned* hist = s_hist + h * tnb;
             RunAcc acc;
             acc.norm = 0; acc.cur = -1; acc.cnt = 0;
+            // one row of 4 samples per lane, sample by sample (the reference's arithmetic)
+            auto bin_row = [&](unsigned src) {
+              double f[NS][4];
+#pragma unroll
+              for (int k = 0; k < NS; ++k) {
+                const float4 v = lds128(src + k * col_bytes);
+                f[k][0] = (double)v.x; f[k][1] = (double)v.y; f[k][2] = (double)v.z; f[k][3] = (double)v.w;
+              }
+              if constexpr (NOPS < 0) {
+#pragma unroll
+                for (int k = 0; k < FAST_MAX_OPS; ++k)
+                  if (k < nsyst) apply_op<NS>(f, op_code[k], op_c0[k], op_onep[k]);
+              } else {
+                if constexpr (NOPS > 0) apply_static<NS, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
+                if constexpr (NOPS > 1) apply_static<NS, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
+                if constexpr (NOPS > 2) apply_static<NS, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
+                if constexpr (NOPS > 3) apply_static<NS, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
+              }
+              int bq[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                double x[NOBS];
+#pragma unroll
+                for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
+                bq[k] = flat_bin<NOBS>(x, geo);
+              }
+              run_push4_direct(acc, bq, hist, tnb);
+            };
+            if constexpr (NOBS == 1 && NS == 1) {
+              if (Q.mono) {
+                // Segments: this lane's samples inside ONE warp-tile are consecutive in the sort
+                // order (32 per tile); the warp's chunk range [ca, ca + nmine) is cut at tile
+                // boundaries.  Sample p of a segment starting at chunk i0: chunk i0 + p / (4R),
+                // row (p / 4) % R, component p % 4.
+                const int lgr = R == 2 ? 1 : 0;
+                const int cpt = WT_ROWS >> lgr;            // chunks per warp-tile
+                const unsigned base = cx.my_stage0 + (unsigned)lane * 16u;
+                int i0 = 0;
+                while (i0 < nmine) {
+                  const int i1 = min(nmine, i0 + cpt - ((ca_mod + i0) % cpt));
+                  const int n = (i1 - i0) << (2 + lgr);
+                  const unsigned sbase = base + (unsigned)i0 * stage_bytes;
+                  auto code_at = [&](int p) {
+                    const unsigned a = sbase + (unsigned)(p >> (2 + lgr)) * stage_bytes +
+                                       (unsigned)((p >> 2) & (R - 1)) * 512u + (unsigned)(p & 3) * 4u;
+                    return mono_code<NOPS, CODES>(lds32(a), op_code, op_c0, op_onep, nsyst, geo);
+                  };
+                  int c_lo = code_at(0);
+                  const int c_end = code_at(n - 1);
+                  // sparse region (a lane's 32 samples span several bins): row by row is cheaper
+                  // than searching; decided per warp so that the lanes stay together
+                  const bool far = c_lo != c_end && !(c_lo >= 0 && c_end >= 0 && abs(c_end - c_lo) == 1);
+                  if (__any_sync(0xffffffffu, far)) {
+                    for (int i = i0; i < i1; ++i)
+                      for (int r = 0; r < R; ++r) bin_row(base + (unsigned)i * stage_bytes + (unsigned)r * 512u);
+                  } else if (c_lo == c_end) {
+                    run_push_n(acc, c_lo, (unsigned)n, hist, tnb);
+                  } else {
+                    // exactly one boundary: bisect for the first sample of the second bin
+                    int l = 1, r = n - 1;
+                    while (l < r) {
+                      const int m = (l + r) >> 1;
+                      if (code_at(m) == c_lo) l = m + 1; else r = m;
+                    }
+                    run_push_n(acc, c_lo, (unsigned)l, hist, tnb);
+                    run_push_n(acc, c_end, (unsigned)(n - l), hist, tnb);
+                  }
+                  i0 = i1;
+                }
+                run_flush<true>(acc, hist, tnb);
+                const unsigned wn = __reduce_add_sync(0xffffffffu, acc.norm);
+                if (lane == 0 && wn) atomicAdd(&s_norm[h], wn);
+                continue;
+              }
+            }
 #pragma unroll 1
             for (int i = 0; i < nmine; ++i) {
-              const unsigned src = cx.my_stage0 + i * stage_bytes + (unsigned)lane * 16u;
+              const unsigned src0 = cx.my_stage0 + i * stage_bytes + (unsigned)lane * 16u;
 #pragma unroll 1
-              for (int r = 0; r < R; ++r) {
-                double f[NS][4];
-#pragma unroll
-                for (int k = 0; k < NS; ++k) {
-                  const float4 v = lds128(src + k * col_bytes + r * 512u);
-                  f[k][0] = (double)v.x; f[k][1] = (double)v.y; f[k][2] = (double)v.z; f[k][3] = (double)v.w;
-                }
-                if constexpr (NOPS < 0) {
-#pragma unroll
-                  for (int k = 0; k < FAST_MAX_OPS; ++k)
-                    if (k < nsyst) apply_op<NS>(f, op_code[k], op_c0[k], op_onep[k]);
-                } else {
-                  if constexpr (NOPS > 0) apply_static<NS, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
-                  if constexpr (NOPS > 1) apply_static<NS, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
-                  if constexpr (NOPS > 2) apply_static<NS, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
-                  if constexpr (NOPS > 3) apply_static<NS, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
-                }
-                int bq[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  double x[NOBS];
-#pragma unroll
-                  for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
-                  bq[k] = flat_bin<NOBS>(x, geo);
-                }
-                run_push4<true>(acc, bq, hist, tnb);
-              }
+              for (int r = 0; r < R; ++r) bin_row(src0 + (unsigned)r * 512u);
             }
             run_flush<true>(acc, hist, tnb);
             const unsigned wnorm = __reduce_add_sync(0xffffffffu, acc.norm);
@@ -206,9 +326,11 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
         }
         __syncthreads();
       }
+      BK_STAMP(1);
       cta_arrive(bar);
       ++bar_count;
       if (!cta_wait_ge(bar, bar_count * G, abort_flag, &s_ok)) break;
+      BK_STAMP(2);
     }
 
     // ---- lookup + event likelihood + tail of the chain this CTA owns ---------------------------
@@ -247,6 +369,7 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
       }
       const double total = block_sum<FAST_THREADS>(sum, s_warp);   // ends past a CTA barrier: lookups done
       if (tid == 0) s_warp[0] = total;
+      BK_STAMP(3);
       // the histogram is rebuilt from zero by the next super-step's bin phase
       if (Q.rebin || mode == NLL_MODE_INIT) {
         if (Q.rebin)
@@ -256,12 +379,44 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
       if (tid < 32) finish_step(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid);
       __syncthreads();
     }
+    BK_STAMP(4);
     if (Q.rebin && s + 1 < total_super) {      // proposals published, histograms cleared
       cta_arrive(bar);
       ++bar_count;
       if (!cta_wait_ge(bar, bar_count * G, abort_flag, &s_ok)) break;
     }
+    BK_STAMP(5);
   }
+}
+
+// precondition of the monotone path: the column holds no NaN and no -inf
+__global__ void column_check_kernel(const float* __restrict__ col, unsigned long long n, unsigned* flag) {
+  bool bad = false;
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+       i += (unsigned long long)gridDim.x * blockDim.x)
+    bad |= !(col[i] > __int_as_float(0xff800000));
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1u);
+}
+
+int column_has_nan_or_neginf(const float* col_dev, unsigned long long n, bool* out, cudaStream_t stream) {
+  *out = false;
+  if (n == 0) return SXMC_OK;
+  unsigned* flag = nullptr;
+  SXMC_CUDA(cudaMalloc(&flag, sizeof(unsigned)));
+  cudaError_t e = cudaMemsetAsync(flag, 0, sizeof(unsigned), stream);
+  unsigned long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (e == cudaSuccess) {
+    column_check_kernel<<<(unsigned)blocks, 256, 0, stream>>>(col_dev, n, flag);
+    e = cudaGetLastError();
+  }
+  unsigned h = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&h, flag, sizeof(unsigned), cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  cudaFree(flag);
+  if (e != cudaSuccess) return cuda_fail(e, "column_has_nan_or_neginf", __FILE__, __LINE__);
+  *out = h != 0;
+  return SXMC_OK;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -29,6 +29,7 @@ static int g_smem_hist_max_bins = 8192;
 static int g_blocks_per_sm = 0;
 static int g_force_generic = 0;
 static int g_force_dynamic = 0;
+static int g_no_mono = 0;        // chain batch: never take the monotone endpoint path (tests)
 static long long g_persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent   // fast kernel with run-time systematic dispatch only
 static int g_timing = 0;
 static float g_last_bin_ms = -1.f, g_last_nll_ms = -1.f;
@@ -380,6 +381,7 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_blocks_per_sm = blocks_per_sm;
   g_force_generic = force_generic & 1;
   g_force_dynamic = (force_generic >> 1) & 1;
+  g_no_mono = (force_generic >> 2) & 1;
   return SXMC_OK;
 }
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
@@ -1630,6 +1632,8 @@ struct sxmc_batch {
   bool trace = false;
   float loop_ms = 0;
   int last_n = 0;
+  unsigned long long* stamps_dev = nullptr;   // profiling hook
+  bool mono = false;                // 1-D monotone program on sorted, NaN-free samples
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -1643,7 +1647,7 @@ int sxmc_batch_destroy(sxmc_batch* b) {
     cudaFree(s.nll_trace); cudaFree(s.prop_trace);
   }
   cudaFree(b->st_dev); cudaFree(b->hist_dev); cudaFree(b->sigs_dev); cudaFree(b->nevents_dev);
-  cudaFree(b->sync_dev); cudaFree(b->points_dev);
+  cudaFree(b->sync_dev); cudaFree(b->points_dev); cudaFree(b->stamps_dev);
   if (b->st_host) cudaFreeHost(b->st_host);
   if (b->sync_host) cudaFreeHost(b->sync_host);
   b->jobs.release();
@@ -1702,6 +1706,24 @@ int sxmc_batch_create(const sxmc_chain_config* cfg, int max_chains, sxmc_batch**
   for (int j = 0; j < b->nsignals && !rc; ++j)
     rc = fill_job(b->pdfs[j], b->jobs.host[j], nullptr, nullptr, nullptr, 1);
   if (!rc) { b->jobs.n_ep = 0; plan_launch(b->jobs, b->nsignals); }
+  // monotone endpoint path (batch_kernels.cu): one observable in one column, every systematic a
+  // SHIFT / SCALE / CTSCALE of it, samples sorted by it, no NaN / -inf among them
+  if (!rc) {
+    const BinLaunch& L = b->jobs.launch;
+    bool mono = L.fast && L.nobs == 1 && L.nslots == 1;
+    for (int j = 0; j < b->nsignals && mono && !rc; ++j) {
+      sxmc_hist* h = b->pdfs[j];
+      if (!h->sort || !h->prepared || h->primary != 0) mono = false;
+      for (const SystDesc& d : h->systs)
+        if (d.type == SXMC_SYST_RESOLUTION_SCALE || d.obs != 0 || d.npars > 1) mono = false;
+      if (mono) {
+        bool bad = false;
+        rc = column_has_nan_or_neginf(h->cols_dev, h->col_pitch, &bad, b->stream);
+        if (bad) mono = false;
+      }
+    }
+    b->mono = mono && !rc;
+  }
   if (rc) { sxmc_batch_destroy(b); return rc; }
   *out = b;
   return SXMC_OK;
@@ -1842,6 +1864,8 @@ int sxmc_batch_run(sxmc_batch* b, int nchains, unsigned nsteps, float burnin_fra
   Q.nchains = nchains; Q.ns = ns; Q.np = np; Q.nsources = b->nsources;
   Q.nsteps = nsteps; Q.do_init = 1;
   Q.rebin = (b->nsystematics > 0 && !b->systematics_fixed) ? 1 : 0;   // src/mcmc.cpp:264
+  Q.stamps = b->stamps_dev;
+  Q.mono = (b->mono && !g_no_mono) ? 1 : 0;
   SXMC_CUDA(cudaEventRecord(b->ev0, b->stream));
   SXMC_TRY(launch_chain_batch(plan, Q, b->stream));
   SXMC_CUDA(cudaEventRecord(b->ev1, b->stream));
@@ -1890,5 +1914,16 @@ int sxmc_batch_contour(sxmc_batch* b, int slot, float delta, float* lower_out, f
 }
 
 int sxmc_batch_loop_ms(sxmc_batch* b, float* ms_out) { *ms_out = b->loop_ms; return SXMC_OK; }
+
+int sxmc_batch_phase_stamps(sxmc_batch* b, int enable, unsigned long long* out148x8) {
+  if (enable && !b->stamps_dev) {
+    SXMC_CUDA(cudaMalloc(&b->stamps_dev, sizeof(unsigned long long) * 148 * 8));
+    SXMC_CUDA(cudaMemset(b->stamps_dev, 0, sizeof(unsigned long long) * 148 * 8));
+  }
+  if (out148x8 && b->stamps_dev)
+    SXMC_CUDA(cudaMemcpy(out148x8, b->stamps_dev, sizeof(unsigned long long) * 148 * 8, cudaMemcpyDeviceToHost));
+  if (!enable && b->stamps_dev) { cudaFree(b->stamps_dev); b->stamps_dev = nullptr; }
+  return SXMC_OK;
+}
 
 }  // extern "C"

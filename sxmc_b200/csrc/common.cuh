@@ -128,6 +128,8 @@ struct BatchParams {
   int do_init;                  // first super-step = initial evaluation + first proposal
   int rebin;
   int group;
+  int mono;                     // 1-D monotone program on sorted samples: endpoint evaluation (batch_kernels.cu)
+  unsigned long long* stamps;   // optional [grid][8] %globaltimer stamps of super-step 20 (profiling)
 };
 
 // One signal as seen by the lookup + event-likelihood kernel.

@@ -95,6 +95,7 @@ struct BatchPlan {
 };
 int plan_chain_batch(const BinLaunch& L, int nchains, BatchPlan* plan);
 int launch_chain_batch(const BatchPlan& plan, const BatchParams& Q, cudaStream_t stream);
+int column_has_nan_or_neginf(const float* col_dev, unsigned long long n, bool* out, cudaStream_t stream);
 
 // ---- ensemble_kernels.cu ----
 int launch_cum(const unsigned* bins_dev, int nb, unsigned* cum_dev, cudaStream_t stream);

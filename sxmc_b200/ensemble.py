@@ -149,43 +149,83 @@ def rows_contour(rows, cl):
     return lo, up, pt, float(lmin.value), int(nc.value)
 
 
-def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps=None,
-             burnin_fraction=None, rank=0, world=1, observables=None, keep_chains=False, built=None):
-    """The loop of src/sxmc.cpp:62-134 over this rank's experiments.  Returns a dict with the
-    experiment indices run here, their upper limits (`limits.push_back(bfi.upper)`, :126),
-    per-experiment observed counts and wall times.  Use ``sharding.gather_limits`` +
-    ``sharding.median`` for the ensemble-wide result (:218-226)."""
+def _fit_objects(fit, hists):
     from . import mcmc
-    nsteps = fit.nsteps if nsteps is None else int(nsteps)
-    burnin = fit.burnin_fraction if burnin_fraction is None else float(burnin_fraction)
-    hists, chain = built if built is not None else mcmc.build_fit(fit)
-    if observables is None:
-        observables = [mcmc.Observable("o%d" % i, float(fit.lower[i]), float(fit.upper[i]))
-                       for i in range(fit.nobs)]
+    observables = [mcmc.Observable("o%d" % i, float(fit.lower[i]), float(fit.upper[i]))
+                   for i in range(fit.nobs)]
     signals = [mcmc.Signal("sig%d" % j, hists[j], s.nexpected, s.n_mc, None) for j, s in enumerate(fit.signals)]
     systs = [mcmc.Systematic("y%d" % i, y.npars, list(y.means), list(y.sigmas), y.fixed)
              for i, y in enumerate(fit.systematics)]
-    gen = FakeDataGenerator(signals, systs, observables)
+    return signals, systs, observables
+
+
+def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps=None,
+             burnin_fraction=None, rank=0, world=1, keep_chains=False, batch=148):
+    """The loop of src/sxmc.cpp:62-134 over this rank's experiments.  Returns a dict with the
+    experiment indices run here, their upper limits (`limits.push_back(bfi.upper)`, :126),
+    per-experiment observed counts and timings.  Use ``sharding.gather_limits`` +
+    ``sharding.median`` for the ensemble-wide result (:218-226).
+
+    ``batch`` > 1: the fits of up to that many experiments advance together in one cooperative
+    launch (``MCMCBatch``) when the fit is small enough for its samples to stay on chip;
+    otherwise (or with batch <= 1) one chain at a time.  Both give the same chains: experiment
+    ``i`` always uses Philox stream ``i``."""
+    from . import mcmc
+    from ._lib import SxmcError
+    nsteps = fit.nsteps if nsteps is None else int(nsteps)
+    burnin = fit.burnin_fraction if burnin_fraction is None else float(burnin_fraction)
     mine = sharding.experiments_for_rank(nexperiments, rank, world)
-    out = {"experiments": mine, "limits": [], "observed": [], "seconds": [], "loop_ms": [], "chains": []}
+    out = {"experiments": mine, "limits": [], "observed": [], "chains": [], "loop_ms": 0.0,
+           "seconds": 0.0, "mode": "single", "launches": 0}
+    delta = contour_delta(confidence)
+    t_all = time.perf_counter()
+    if batch > 1 and mine:
+        hists, mb = mcmc.build_fit(fit, batch=min(int(batch), 148))
+        gen = FakeDataGenerator(*_fit_objects(fit, hists))
+        try:
+            k = mb.parameter_names.index(signal_name) if signal_name in mb.parameter_names[:-1] else -1
+            for c0 in range(0, len(mine), mb.max_chains):
+                group = mine[c0:c0 + mb.max_chains]
+                obs = []
+                for slot, i in enumerate(group):
+                    obs.append(mb.generate_data(slot, gen, True, seed, i))   # make_fake_dataset(..., true)
+                    mb.set_seed(slot, seed, i)
+                mb.run(len(group), nsteps, burnin)                           # MCMC::operator() x len(group)
+                out["loop_ms"] += mb.loop_ms()
+                out["launches"] += 1
+                for slot, i in enumerate(group):
+                    _, up, _, _, _ = mb.contour(slot, delta)                 # ls->get_best_fit()
+                    out["limits"].append(float(up[k]) if k >= 0 else float("nan"))
+                    out["observed"].append(obs[slot])
+                    if keep_chains:
+                        out["chains"].append(mb.rows(slot))
+            out["mode"] = "batch"
+            out["seconds"] = time.perf_counter() - t_all
+            return out
+        except SxmcError as e:
+            if e.code != 3 or out["limits"]:      # only "not a small fit" falls back
+                raise
+        finally:
+            gen.close()
+            mb.close()
+            for h in hists:
+                h.close()
+    hists, chain = mcmc.build_fit(fit)
+    gen = FakeDataGenerator(*_fit_objects(fit, hists))
     for i in mine:
-        t0 = time.perf_counter()
         events, observed = gen(True, seed, i)                   # make_fake_dataset(..., true)
         chain.set_seed(seed, i)
-        ls = chain.run_resident(events, nsteps, burnin)         # MCMC::operator(), rows stay on the device
+        chain.run_resident(events, nsteps, burnin)              # MCMC::operator(), rows stay on the device
         best_fit, _ = contour_intervals(chain, confidence)      # ls->get_best_fit()
-        if signal_name in best_fit:
-            out["limits"].append(best_fit[signal_name].upper)
-        else:
-            out["limits"].append(float("nan"))
+        out["limits"].append(best_fit[signal_name].upper if signal_name in best_fit else float("nan"))
         out["observed"].append(observed)
-        out["seconds"].append(time.perf_counter() - t0)
-        out["loop_ms"].append(chain.loop_ms())
+        out["loop_ms"] += chain.loop_ms()
+        out["launches"] += chain.launches()
         if keep_chains:
             out["chains"].append(chain.rows())
     gen.close()
-    if built is None:
-        chain.close()
-        for h in hists:
-            h.close()
+    chain.close()
+    for h in hists:
+        h.close()
+    out["seconds"] = time.perf_counter() - t_all
     return out

@@ -137,15 +137,19 @@ def test_contour_matches_restatement_on_a_real_chain_and_on_edge_cases():
 
 
 def test_ensemble_limits_are_reproducible_and_cover_the_truth():
-    """A small ensemble: upper limits on source 0 (true rate 1.0 x nexpected) at 90 % CL."""
+    """A small ensemble: upper limits on source 0 (true rate 1.0 x nexpected) at 90 % CL; the
+    batched launch, the one-chain-at-a-time loop and a rank of a 2-rank run agree exactly."""
     from sxmc_b200 import ensemble
     fit = W.config_B(0.02)
     a = ensemble.ensemble(fit, 12, "s0", 0.9, seed=42, nsteps=4000, burnin_fraction=0.1)
+    s = ensemble.ensemble(fit, 12, "s0", 0.9, seed=42, nsteps=4000, burnin_fraction=0.1, batch=0)
     b = ensemble.ensemble(fit, 12, "s0", 0.9, seed=42, nsteps=4000, burnin_fraction=0.1, rank=1, world=2)
+    assert a["mode"] == "batch" and s["mode"] == "single" and a["launches"] == 1
     assert a["experiments"] == list(range(12)) and b["experiments"] == list(range(1, 12, 2))
     lim = np.asarray(a["limits"])
     assert np.all(np.isfinite(lim))
-    # a rank of a 2-rank run reproduces exactly the experiments it owns
+    assert np.array_equal(lim, np.asarray(s["limits"]))
+    assert np.array_equal(np.stack(a["observed"]), np.stack(s["observed"]))
     assert np.array_equal(lim[1::2], np.asarray(b["limits"]))
     assert np.mean(lim > 1.0) >= 0.7          # upper edge of a 90 % contour: mostly above truth
     assert np.all(lim < 2.0)
@@ -161,8 +165,18 @@ def _with_data(fit, data):
     return f
 
 
-@pytest.mark.parametrize("name,scale,nchains", [("B", 0.005, 5), ("A", 0.004, 3)])
-def test_batch_tape_driven_chains_match_oracle_chains(name, scale, nchains):
+@pytest.fixture(params=[False, True], ids=["mono", "nomono"])
+def bin_path(request):
+    """Both binning paths of the batch kernel: monotone endpoint evaluation (1-D shift/scale
+    fits) and the sample-by-sample pass."""
+    from sxmc_b200 import pdfz
+    pdfz.set_bin_tuning(8192, 0, False, False, request.param)
+    yield request.param
+    pdfz.set_bin_tuning(8192, 0, False, False, False)
+
+
+@pytest.mark.parametrize("name,scale,nchains", [("B", 0.005, 5), ("A", 0.004, 3), ("B", 0.0002, 3)])
+def test_batch_tape_driven_chains_match_oracle_chains(name, scale, nchains, bin_path):
     """Every chain of a batch, fed its own tape and its own data events, reproduces the oracle
     chain of the same inputs: proposals and accepted rows bit-identical, NLL within 1e-6."""
     from sxmc_b200 import mcmc
@@ -190,6 +204,60 @@ def test_batch_tape_driven_chains_match_oracle_chains(name, scale, nchains):
         assert np.allclose(nll_tr, want["nll_trace"], rtol=1e-6, atol=0)
         assert np.array_equal(got[:, :-1], want["chain"][:, :-1])
         assert np.allclose(got[:, -1], want["chain"][:, -1], rtol=1e-6)
+    batch.close()
+    for h in hists:
+        h.close()
+
+
+def _scale_ctscale_fit(special, reverse=False):
+    """1-D fit with scale + ctscale + shift on the observable (a monotone program with a
+    decreasing piece when 1+p < 0); `special` adds +-inf / NaN / -0 samples."""
+    from sxmc_b200.workloads import CTSCALE, SCALE, SHIFT, FitSpec, SignalSpec, SystSpec
+    rng = np.random.default_rng(77)
+    sigs = []
+    for j, mu in enumerate((-0.3, 0.4)):
+        x = rng.normal(mu, 0.5, 40_000).astype(np.float32)
+        if special:
+            x[:6] = [np.inf, -0.0, 0.0, np.inf, 1.0, -1.0]
+            if special == "nan":
+                x[6:9] = [np.nan, -np.inf, np.nan]
+        rows = np.stack([x, np.zeros_like(x)], axis=1)
+        sigs.append(SignalSpec(samples=rows, nexpected=300.0, source=j))
+    ev = np.clip(rng.normal(0, 0.5, 600), -0.999, 0.999)
+    data = np.stack([ev, np.zeros_like(ev)], axis=1).astype(np.float32)
+    systs = [SystSpec(type=SCALE, obs=0, means=[-2.0 if reverse else 0.0], sigmas=[0.3]),   # 1+p < 0: order reversed
+             SystSpec(type=CTSCALE, obs=0, means=[0.0], sigmas=[0.05]),
+             SystSpec(type=SHIFT, obs=0, means=[0.0], sigmas=[0.02])]
+    return FitSpec(name="mono", lower=[-1.0], upper=[1.0], nbins=[200], source_means=[1.0, 1.0],
+                   source_sigmas=[0.0, 0.0], source_fixed=[False, False], systematics=systs,
+                   signals=sigs, data=data, nsteps=100)
+
+
+@pytest.mark.parametrize("special,reverse", [(None, False), ("inf", False), ("inf", True), ("nan", True)])
+def test_batch_monotone_program_with_negative_scale_and_special_values(special, reverse, bin_path):
+    """Negative scale factors reverse the order of the transformed samples; +inf, -0 and (with
+    "nan": NaN / -inf, which switch the endpoint path off) must be binned as the oracle does."""
+    from sxmc_b200 import mcmc
+    fit = _scale_ctscale_fit(special, reverse)
+    nsteps = 250
+    hists, batch = mcmc.build_fit(fit, batch=2)
+    batch.enable_trace()
+    wants = []
+    for k in range(2):
+        rng = np.random.default_rng(500 + k)
+        normals = rng.normal(size=(nsteps + 1) * fit.nparameters) * (3.0 if k else 1.0)
+        uniforms = rng.random(nsteps)
+        wants.append(port.mcmc(fit, nsteps, 0.1, normals, uniforms, trace=True))
+        batch.set_tapes(k, normals, uniforms)
+        batch.set_data(k, fit.data)
+    batch.run(2, nsteps, 0.1)
+    for k in range(2):
+        nll_tr, prop_tr = batch.read_trace(k, nsteps)
+        assert np.array_equal(prop_tr, wants[k]["prop_trace"])
+        assert np.all(1.0 + prop_tr[:, fit.nsources] < 0) == reverse
+        ok = np.isfinite(wants[k]["nll_trace"])
+        assert np.allclose(nll_tr[ok], wants[k]["nll_trace"][ok], rtol=1e-6, atol=0)
+        assert np.array_equal(batch.rows(k)[:, :-1], wants[k]["chain"][:, :-1])
     batch.close()
     for h in hists:
         h.close()
