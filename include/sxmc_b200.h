@@ -277,6 +277,10 @@ int sxmc_batch_contour(sxmc_batch* b, int slot, float delta, float* lower_out, f
                        float* point_out, float* lmin_out, long* ncontour_out);
 /* device time of the last sxmc_batch_run launch (all chains, all steps) */
 int sxmc_batch_loop_ms(sxmc_batch* b, float* ms_out);
+/* which kernel the last run used: 1 = monotone edge search (1-D fits whose systematics are all
+ * shift / scale / ctscale: bin edges are bisected over the sorted samples), 2 = sample by sample;
+ * *max_edges_out = largest number of nominal bin edges in one CTA's sample range (path 1) */
+int sxmc_batch_last_path(sxmc_batch* b, int* path_out, int* max_edges_out);
 /* profiling hook: every CTA stamps %globaltimer at the phase boundaries of super-step 20
  * ([148][8] ns: start, bin done, barrier out, lookup done, tail done, barrier out) */
 int sxmc_batch_phase_stamps(sxmc_batch* b, int enable, unsigned long long* out148x8);

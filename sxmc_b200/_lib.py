@@ -123,6 +123,7 @@ SYMBOLS = {
     "sxmc_batch_read_trace": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_uint]),
     "sxmc_batch_contour": (C.c_int, [c_vp, C.c_int, C.c_float, c_fp, c_fp, c_fp, c_fp, C.POINTER(C.c_long)]),
     "sxmc_batch_loop_ms": (C.c_int, [c_vp, c_fp]),
+    "sxmc_batch_last_path": (C.c_int, [c_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "sxmc_batch_phase_stamps": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_uint64)]),
     "sxmc_comm_unique_id": (C.c_int, [c_vp]),
     "sxmc_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, C.POINTER(c_vp)]),

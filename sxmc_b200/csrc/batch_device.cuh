@@ -1,0 +1,92 @@
+// batch_device.cuh -- the lookup + tail phase shared by the chain batch kernels
+// (batch_kernels.cu, batch_mono_kernels.cu): CTA e owns chain e of the batch.
+#pragma once
+#include "common.cuh"
+#include "nll_device.cuh"
+#include "grid_sync.cuh"
+
+namespace sxmc {
+
+constexpr int BK_MAX_SIGNALS = 128;
+
+struct BatchShared {
+  double c[BK_MAX_SIGNALS];        // rate * efficiency of every signal at the proposed point
+  double bn[BK_MAX_SIGNALS];       // norm * bin_volume
+  double nexp[BK_MAX_SIGNALS];
+  double binvol[BK_MAX_SIGNALS];
+  const int* rb[BK_MAX_SIGNALS];
+  unsigned nmc[BK_MAX_SIGNALS];
+  short sid[BK_MAX_SIGNALS];
+  double warp[FAST_THREADS / 32];
+  double term[BK_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
+  FinState F;
+  int ok;
+  long long ne;
+};
+
+// once per launch: the owned chain's state and signal tables into shared memory
+__device__ __forceinline__ void batch_owner_init(BatchShared& S, const BatchParams& Q, int mine, int tid) {
+  if (mine < 0) return;
+  prefetch_state(S.F, Q.st + mine, Q.np, tid, FAST_THREADS);
+  if (tid < Q.ns) {
+    const NllSignal sg = Q.sigs[(size_t)mine * Q.ns + tid];
+    S.nexp[tid] = sg.nexpected;
+    S.binvol[tid] = sg.bin_volume;
+    S.rb[tid] = sg.read_bins;
+    S.nmc[tid] = sg.n_mc;
+    S.sid[tid] = sg.source_id;
+  }
+  if (tid == 0) S.ne = Q.nevents[mine];
+}
+
+// One step of the owned chain after its histograms are complete: eval_pdf + nll_event_chunks +
+// reduce (src/pdfz.cpp:411-436, src/nll_kernels.cpp:89-146), then finish_step; the histogram is
+// cleared for the next super-step's bin phase.  All threads of the CTA call it.
+__device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchParams& Q, int mine, int mode,
+                                                  int tnb, int tid) {
+  const int ns = Q.ns, np = Q.np;
+  unsigned* const my_hist = Q.hist + (size_t)mine * Q.hist_words;
+  FinState& F = S.F;
+  if (tid < ns) {
+    const unsigned norm = __ldcg(my_hist + (size_t)ns * tnb + tid);
+    const float eff = (float)(1.0 * norm / S.nmc[tid]);                    // nll_kernels.cpp:105
+    const double rate = __dmul_rn(F.proposed[S.sid[tid]], S.nexp[tid]);
+    S.c[tid] = __dmul_rn(rate, (double)eff);
+    S.bn[tid] = __dmul_rn((double)norm, S.binvol[tid]);                    // pdfz.cpp:417
+    S.term[tid] = __dmul_rn(rate, (double)norm) / (double)S.nmc[tid];      // nll_kernels.cpp:167-171
+  }
+  for (int i = tid; i < np; i += FAST_THREADS) {       // Gaussian constraints (nll_kernels.cpp:176-185)
+    const double sg = F.sigmas[i];
+    double t = 0;
+    if (sg > 0) {
+      const double x = __dadd_rn(F.proposed[i], -F.means[i]) / sg;
+      t = __dmul_rn(__dmul_rn(0.5, x), x);
+    }
+    S.term[ns + i] = t;
+  }
+  __syncthreads();
+  const long long my_ne = S.ne;
+  double sum = 0;
+  for (long long i = tid; i < my_ne; i += FAST_THREADS) {
+    double acc = 0;
+    for (int j = 0; j < ns; ++j) {
+      const int rb = S.rb[j][i];
+      float v = 0.0f;
+      if (rb >= 0 && rb < tnb) {
+        v = (float)((double)__ldcg(my_hist + (size_t)j * tnb + rb) / S.bn[j]);   // pdfz.cpp:429-432
+        if (isnan(v)) v = 0.0f;                                                  // nll_kernels.cpp:107
+      }
+      acc = __dadd_rn(acc, __dmul_rn(S.c[j], (double)v));
+    }
+    if (acc > 0) sum += log(acc);
+  }
+  const double total = block_sum<FAST_THREADS>(sum, S.warp);   // ends past a CTA barrier: lookups done
+  if (tid == 0) S.warp[0] = total;
+  if (Q.rebin)   // rebuilt from zero by the next super-step's bin phase
+    for (unsigned long long w = tid; w < Q.hist_words; w += FAST_THREADS) my_hist[w] = 0u;
+  __syncthreads();
+  if (tid < 32) finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid);
+  __syncthreads();
+}
+
+}  // namespace sxmc

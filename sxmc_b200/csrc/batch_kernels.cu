@@ -24,55 +24,11 @@
 #include "bin_device.cuh"
 #include "nll_device.cuh"
 #include "grid_sync.cuh"
+#include "batch_device.cuh"
 
 #include <cstring>
 
 namespace sxmc {
-
-constexpr int BK_MAX_SIGNALS = 128;
-
-// ---- monotone programs ------------------------------------------------------------------------
-// A 1-D PDF whose systematics are all SHIFT / SCALE / CTSCALE of the observable maps a sample x
-// to its bin through a chain of monotone roundings: x -> x' -> (int)((x' - lo) * scale).  The
-// samples are sorted by x, so every thread's sequence of samples is sorted too and its bin
-// codes form contiguous runs: two samples with the same code bracket only samples with that
-// code.  The thread evaluates the two ends of its sequence (the usual case: one bin, 2
-// evaluations instead of 4 * R * chunks) and finds run boundaries by galloping + binary search.
-// Every evaluation is the reference's arithmetic on the reference's value, so the counts are
-// bit-identical to the sample-by-sample pass.  (Host-side preconditions: sorted layout, no NaN
-// and no -inf in the column -- see plan_chain_batch.)
-// code: -1 below the domain (or NaN), -2 at/above the upper edge, else the bin index.
-template <int NOPS, unsigned CODES>
-__device__ __forceinline__ int mono_code(float xf, const int (&op_code)[FAST_MAX_OPS],
-                                         const double (&op_c0)[FAST_MAX_OPS],
-                                         const double (&op_onep)[FAST_MAX_OPS], int nsyst, const Geo& geo) {
-  double f[1][4];
-  f[0][0] = f[0][1] = f[0][2] = f[0][3] = (double)xf;
-  if constexpr (NOPS < 0) {
-#pragma unroll
-    for (int k = 0; k < FAST_MAX_OPS; ++k)
-      if (k < nsyst) apply_op<1>(f, op_code[k], op_c0[k], op_onep[k]);
-  } else {
-    if constexpr (NOPS > 0) apply_static<1, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
-    if constexpr (NOPS > 1) apply_static<1, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
-    if constexpr (NOPS > 2) apply_static<1, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
-    if constexpr (NOPS > 3) apply_static<1, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
-  }
-  const double x = f[0][0];
-  if (!(x >= geo.lo[0])) return -1;
-  if (!(x < geo.hi[0])) return -2;
-  return trunc_nonneg(__dmul_rn(__dadd_rn(x, -geo.lo[0]), geo.sc[0]));
-}
-
-// k samples of code c (c < 0: outside the domain) appended to a thread's run
-__device__ __forceinline__ void run_push_n(RunAcc& r, int c, unsigned k, unsigned* hist, int total_nbins) {
-  if (c != r.cur) {
-    run_flush<true>(r, hist, total_nbins);
-    r.cur = c;
-    r.cnt = 0;
-  }
-  r.cnt += k;
-}
 
 // run_push4 with a short straight-line slow path: the run is flushed, three samples go
 // straight to the histogram, the fourth starts the new run.  (A warp executes the slow path
@@ -90,36 +46,20 @@ __device__ __forceinline__ void run_push4_direct(RunAcc& r, const int (&b)[4], u
   }
 }
 
-__device__ __forceinline__ float lds32(unsigned addr) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-  return v;
-}
-
 template <int NOBS, int NS, int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(FAST_THREADS, 1)
 chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__ BatchParams Q) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long s_bar[FAST_WARPS * FAST_MAX_STAGES];
-  __shared__ double s_c[BK_MAX_SIGNALS];
-  __shared__ double s_bn[BK_MAX_SIGNALS];
-  __shared__ double s_nexp[BK_MAX_SIGNALS];
-  __shared__ double s_binvol[BK_MAX_SIGNALS];
-  __shared__ const int* s_rb[BK_MAX_SIGNALS];
-  __shared__ unsigned s_nmc[BK_MAX_SIGNALS];
-  __shared__ short s_sid[BK_MAX_SIGNALS];
-  __shared__ double s_warp[FAST_THREADS / 32];
-  __shared__ double s_term[BK_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
+  __shared__ BatchShared S;
   __shared__ double s_par[BATCH_MAX_CHAINS][FAST_MAX_OPS];   // every chain's systematic coefficients
   __shared__ unsigned s_norm[BATCH_MAX_GROUP];
-  __shared__ FinState F;
-  __shared__ int s_ok;
   unsigned* s_hist = reinterpret_cast<unsigned*>(smem_raw);
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   const unsigned G = gridDim.x;
-  const int ns = Q.ns, np = Q.np, nsources = Q.nsources, nch = Q.nchains;
+  const int ns = Q.ns, nsources = Q.nsources, nch = Q.nchains;
   const int tnb = P.geo.total_nbins;
   const Geo& geo = P.geo;
   unsigned* const bar = Q.sync + 0;
@@ -136,7 +76,7 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
   const bool have_work = t0 < t1;
   const int R = P.R;
   const unsigned col_bytes = (unsigned)R * 512u, stage_bytes = NS * col_bytes;
-  int nmine = 0, ca_mod = 0;
+  int nmine = 0;
   if (have_work) {
     const FastJob& job = P.job[job_j];
     const unsigned long long jbeg = P.prefix[job_j];
@@ -144,7 +84,6 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
     const unsigned long long ca = (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
     const unsigned long long cb = (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
     nmine = (int)(cb - ca);                     // <= P.S (checked on the host)
-    ca_mod = (int)(ca % (unsigned)(WT_ROWS / R));
     if (lane == 0) {
       for (int i = 0; i < nmine; ++i) {
         const unsigned b = cx.my_bar0 + 8u * i;
@@ -160,21 +99,7 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
 
   // ---- the chain this CTA owns in the lookup/tail phase
   const int mine = blockIdx.x < (unsigned)nch ? (int)blockIdx.x : -1;
-  ChainState* const st = mine >= 0 ? Q.st + mine : nullptr;
-  unsigned* const my_hist = mine >= 0 ? Q.hist + (size_t)mine * Q.hist_words : nullptr;
-  long long my_ne = 0;
-  if (mine >= 0) {
-    prefetch_state(F, st, np, tid, FAST_THREADS);
-    if (tid < ns) {
-      const NllSignal sg = Q.sigs[(size_t)mine * ns + tid];
-      s_nexp[tid] = sg.nexpected;
-      s_binvol[tid] = sg.bin_volume;
-      s_rb[tid] = sg.read_bins;
-      s_nmc[tid] = sg.n_mc;
-      s_sid[tid] = sg.source_id;
-    }
-    my_ne = Q.nevents[mine];
-  }
+  batch_owner_init(S, Q, mine, tid);
   // the samples have landed (waited for once; the stages are never refilled)
   for (int i = 0; i < nmine; ++i) mbar_wait(cx.my_bar0 + 8u * i, 0u);
   __syncthreads();
@@ -251,53 +176,6 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
               }
               run_push4_direct(acc, bq, hist, tnb);
             };
-            if constexpr (NOBS == 1 && NS == 1) {
-              if (Q.mono) {
-                // Segments: this lane's samples inside ONE warp-tile are consecutive in the sort
-                // order (32 per tile); the warp's chunk range [ca, ca + nmine) is cut at tile
-                // boundaries.  Sample p of a segment starting at chunk i0: chunk i0 + p / (4R),
-                // row (p / 4) % R, component p % 4.
-                const int lgr = R == 2 ? 1 : 0;
-                const int cpt = WT_ROWS >> lgr;            // chunks per warp-tile
-                const unsigned base = cx.my_stage0 + (unsigned)lane * 16u;
-                int i0 = 0;
-                while (i0 < nmine) {
-                  const int i1 = min(nmine, i0 + cpt - ((ca_mod + i0) % cpt));
-                  const int n = (i1 - i0) << (2 + lgr);
-                  const unsigned sbase = base + (unsigned)i0 * stage_bytes;
-                  auto code_at = [&](int p) {
-                    const unsigned a = sbase + (unsigned)(p >> (2 + lgr)) * stage_bytes +
-                                       (unsigned)((p >> 2) & (R - 1)) * 512u + (unsigned)(p & 3) * 4u;
-                    return mono_code<NOPS, CODES>(lds32(a), op_code, op_c0, op_onep, nsyst, geo);
-                  };
-                  int c_lo = code_at(0);
-                  const int c_end = code_at(n - 1);
-                  // sparse region (a lane's 32 samples span several bins): row by row is cheaper
-                  // than searching; decided per warp so that the lanes stay together
-                  const bool far = c_lo != c_end && !(c_lo >= 0 && c_end >= 0 && abs(c_end - c_lo) == 1);
-                  if (__any_sync(0xffffffffu, far)) {
-                    for (int i = i0; i < i1; ++i)
-                      for (int r = 0; r < R; ++r) bin_row(base + (unsigned)i * stage_bytes + (unsigned)r * 512u);
-                  } else if (c_lo == c_end) {
-                    run_push_n(acc, c_lo, (unsigned)n, hist, tnb);
-                  } else {
-                    // exactly one boundary: bisect for the first sample of the second bin
-                    int l = 1, r = n - 1;
-                    while (l < r) {
-                      const int m = (l + r) >> 1;
-                      if (code_at(m) == c_lo) l = m + 1; else r = m;
-                    }
-                    run_push_n(acc, c_lo, (unsigned)l, hist, tnb);
-                    run_push_n(acc, c_end, (unsigned)(n - l), hist, tnb);
-                  }
-                  i0 = i1;
-                }
-                run_flush<true>(acc, hist, tnb);
-                const unsigned wn = __reduce_add_sync(0xffffffffu, acc.norm);
-                if (lane == 0 && wn) atomicAdd(&s_norm[h], wn);
-                continue;
-              }
-            }
 #pragma unroll 1
             for (int i = 0; i < nmine; ++i) {
               const unsigned src0 = cx.my_stage0 + i * stage_bytes + (unsigned)lane * 16u;
@@ -329,61 +207,17 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
       BK_STAMP(1);
       cta_arrive(bar);
       ++bar_count;
-      if (!cta_wait_ge(bar, bar_count * G, abort_flag, &s_ok)) break;
+      if (!cta_wait_ge(bar, bar_count * G, abort_flag, &S.ok)) break;
       BK_STAMP(2);
     }
 
     // ---- lookup + event likelihood + tail of the chain this CTA owns ---------------------------
-    if (mine >= 0) {
-      if (tid < ns) {
-        const unsigned norm = __ldcg(my_hist + (size_t)ns * tnb + tid);
-        const float eff = (float)(1.0 * norm / s_nmc[tid]);                    // nll_kernels.cpp:105
-        const double rate = __dmul_rn(F.proposed[s_sid[tid]], s_nexp[tid]);
-        s_c[tid] = __dmul_rn(rate, (double)eff);
-        s_bn[tid] = __dmul_rn((double)norm, s_binvol[tid]);                    // pdfz.cpp:417
-        s_term[tid] = __dmul_rn(rate, (double)norm) / (double)s_nmc[tid];      // nll_kernels.cpp:167-171
-      }
-      for (int i = tid; i < np; i += FAST_THREADS) {       // Gaussian constraints (nll_kernels.cpp:176-185)
-        const double sg = F.sigmas[i];
-        double t = 0;
-        if (sg > 0) {
-          const double x = __dadd_rn(F.proposed[i], -F.means[i]) / sg;
-          t = __dmul_rn(__dmul_rn(0.5, x), x);
-        }
-        s_term[ns + i] = t;
-      }
-      __syncthreads();
-      double sum = 0;
-      for (long long i = tid; i < my_ne; i += FAST_THREADS) {
-        double acc = 0;
-        for (int j = 0; j < ns; ++j) {
-          const int rb = s_rb[j][i];
-          float v = 0.0f;
-          if (rb >= 0 && rb < tnb) {
-            v = (float)((double)__ldcg(my_hist + (size_t)j * tnb + rb) / s_bn[j]);   // pdfz.cpp:429-432
-            if (isnan(v)) v = 0.0f;                                                  // nll_kernels.cpp:107
-          }
-          acc = __dadd_rn(acc, __dmul_rn(s_c[j], (double)v));
-        }
-        if (acc > 0) sum += log(acc);
-      }
-      const double total = block_sum<FAST_THREADS>(sum, s_warp);   // ends past a CTA barrier: lookups done
-      if (tid == 0) s_warp[0] = total;
-      BK_STAMP(3);
-      // the histogram is rebuilt from zero by the next super-step's bin phase
-      if (Q.rebin || mode == NLL_MODE_INIT) {
-        if (Q.rebin)
-          for (unsigned long long w = tid; w < Q.hist_words; w += FAST_THREADS) my_hist[w] = 0u;
-      }
-      __syncthreads();
-      if (tid < 32) finish_step(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid);
-      __syncthreads();
-    }
+    if (mine >= 0) batch_lookup_tail(S, Q, mine, mode, tnb, tid);
     BK_STAMP(4);
     if (Q.rebin && s + 1 < total_super) {      // proposals published, histograms cleared
       cta_arrive(bar);
       ++bar_count;
-      if (!cta_wait_ge(bar, bar_count * G, abort_flag, &s_ok)) break;
+      if (!cta_wait_ge(bar, bar_count * G, abort_flag, &S.ok)) break;
     }
     BK_STAMP(5);
   }

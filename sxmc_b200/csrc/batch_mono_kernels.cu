@@ -1,0 +1,340 @@
+// batch_mono_kernels.cu -- the chain batch kernel for MONOTONE fits: one observable whose
+// systematics are all SHIFT / SCALE / CTSCALE (workloads B and E of SURVEY 8: the ensemble
+// configuration of BASELINE.json).
+//
+// For such a fit a sample x reaches its bin through monotone roundings only,
+//     x -> x' = syst(x) -> (int)((x' - lo) * scale)            (src/pdfz.cpp:306-331, :386-398)
+// so over samples SORTED by x the bin index is a monotone step function, and a histogram is
+// fully described by the positions at which the index changes.  Every CTA keeps a contiguous
+// range of the sorted samples in shared memory (plain float array, loaded once per launch).
+// For one chain, a warp evaluates the two ends of the range and then each lane bisects for one
+// bin edge: ~log2(n) evaluations per EDGE instead of one per SAMPLE, every evaluation being the
+// reference's arithmetic on an actual sample, so the counts are bit-identical to the
+// sample-by-sample pass.  The 16 warps of a CTA work on 16 different chains at once.
+// The host cuts the ranges so that every CTA sees about the same number of edges (sparse tails
+// get few samples, the dense core is limited by shared-memory capacity) -- plan_chain_batch_mono.
+//
+// Preconditions (checked on the host): samples sorted by the observable, no NaN / -inf among
+// them.  Fits that do not qualify run chain_batch_kernel (batch_kernels.cu).
+#include "common.cuh"
+#include "kernels.h"
+#include "bin_device.cuh"
+#include "nll_device.cuh"
+#include "grid_sync.cuh"
+#include "batch_device.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+namespace sxmc {
+
+// code of a transformed sample: -1 below the domain (or NaN), -2 at/above the upper edge, else
+// the bin index (which can be total_nbins for x' within an ulp of the edge: counted in the norm
+// but not in a bin, as the sample-by-sample kernels do)
+template <int NOPS, unsigned CODES>
+__device__ __forceinline__ int mono_code(float xf, const int (&op_code)[FAST_MAX_OPS],
+                                         const double (&op_c0)[FAST_MAX_OPS],
+                                         const double (&op_onep)[FAST_MAX_OPS], int nsyst, const Geo& geo) {
+  double f[1][4];
+  f[0][0] = f[0][1] = f[0][2] = f[0][3] = (double)xf;
+  if constexpr (NOPS < 0) {
+#pragma unroll
+    for (int k = 0; k < FAST_MAX_OPS; ++k)
+      if (k < nsyst) apply_op<1>(f, op_code[k], op_c0[k], op_onep[k]);
+  } else {
+    if constexpr (NOPS > 0) apply_static<1, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
+    if constexpr (NOPS > 1) apply_static<1, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
+    if constexpr (NOPS > 2) apply_static<1, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
+    if constexpr (NOPS > 3) apply_static<1, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
+  }
+  const double x = f[0][0];
+  if (!(x >= geo.lo[0])) return -1;
+  if (!(x < geo.hi[0])) return -2;
+  return trunc_nonneg(__dmul_rn(__dadd_rn(x, -geo.lo[0]), geo.sc[0]));
+}
+
+// position of a code along the x' axis: below < bin 0 < ... < bin tnb < at/above the edge
+__device__ __forceinline__ int mono_rank(int code, int tnb) {
+  return code == -1 ? 0 : (code == -2 ? tnb + 2 : code + 1);
+}
+
+template <int NOPS, unsigned CODES>
+__global__ void __launch_bounds__(FAST_THREADS, 1)
+chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_constant__ BatchParams Q) {
+  extern __shared__ __align__(16) float s_x[];       // this CTA's sorted samples
+  __shared__ BatchShared S;
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const unsigned G = gridDim.x;
+  const int ns = Q.ns, nsources = Q.nsources, nch = Q.nchains;
+  const int tnb = M.geo.total_nbins;
+  const Geo& geo = M.geo;
+  unsigned* const bar = Q.sync + 0;
+  unsigned* const abort_flag = Q.sync + 3;
+  unsigned bar_count = 0;
+
+  const int n = (int)M.n[blockIdx.x];
+  const int job_j = M.jobof[blockIdx.x];
+  const MonoJob& job = M.job[job_j];
+  {
+    const unsigned long long s0 = M.s0[blockIdx.x];
+    for (int p = tid; p < n; p += FAST_THREADS) s_x[p] = __ldg(job.col + tiled_offset(s0 + p));
+  }
+  const int mine = blockIdx.x < (unsigned)nch ? (int)blockIdx.x : -1;
+  batch_owner_init(S, Q, mine, tid);
+  __syncthreads();
+
+  const int nsyst = job.nsyst;
+  int op_code[FAST_MAX_OPS];
+#pragma unroll
+  for (int k = 0; k < FAST_MAX_OPS; ++k) op_code[k] = k < nsyst ? job.code[k] : 0;
+  const unsigned total_super = Q.nsteps + (Q.do_init ? 1u : 0u);
+
+#define BKM_STAMP(slot)                                                              \
+  do {                                                                               \
+    if (Q.stamps && tid == 0 && s == 20u) Q.stamps[blockIdx.x * 8 + (slot)] = globaltimer_ns(); \
+  } while (0)
+  for (unsigned s = 0; s < total_super; ++s) {
+    const int mode = (Q.do_init && s == 0) ? NLL_MODE_INIT : NLL_MODE_STEP;
+    const bool bin_now = Q.rebin || mode == NLL_MODE_INIT;
+    BKM_STAMP(0);
+
+    // ---- bin: warp w takes chains w, w + 16, ... ---------------------------------------------
+    if (bin_now) {
+      if (n > 0) {
+        for (int e = warp; e < nch; e += FAST_WARPS) {
+          double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
+#pragma unroll
+          for (int k = 0; k < FAST_MAX_OPS; ++k) {
+            op_c0[k] = 0.0; op_onep[k] = 1.0;
+            if (k < nsyst) {
+              const double par = job.npars[k] ? __ldcg(&Q.st[e].proposed[nsources + job.pidx[k]]) : 0.0;
+              op_c0[k] = __dadd_rn(0.0, __dmul_rn(par, 1.0));      // src/pdfz.cpp:310-314
+              op_onep[k] = __dadd_rn(1.0, op_c0[k]);
+            }
+          }
+          auto rank_at = [&](int p) {
+            return mono_rank(mono_code<NOPS, CODES>(s_x[p], op_code, op_c0, op_onep, nsyst, geo), tnb);
+          };
+          unsigned* const hist = Q.hist + (size_t)e * Q.hist_words + (size_t)job_j * tnb;
+          unsigned norm = 0;
+          auto add = [&](int rank, unsigned k) {      // k samples whose code has this rank
+            if (k && rank >= 1 && rank <= tnb + 1) {
+              norm += k;
+              if (rank <= tnb) atomicAdd(hist + (rank - 1), k);
+            }
+          };
+          const int r_first = rank_at(0), r_last = rank_at(n - 1);
+          const int dir = r_last >= r_first ? 1 : -1;
+          const int nedges = (r_last - r_first) * dir;
+          int prev = 0;                               // start of the run that is still open
+          for (int e0 = 0; e0 < nedges; e0 += 32) {
+            const int k = e0 + lane;
+            const bool active = k < nedges;
+            const int t = r_first + dir * (k + 1);
+            // first position whose rank has reached t (exists: the last sample has rank r_last)
+            int lo = 0, hi = n - 1;
+            if (active) {
+              while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if ((rank_at(mid) - t) * dir >= 0) hi = mid; else lo = mid + 1;
+              }
+            }
+            const int pos = active ? lo : n;
+            const int up = __shfl_up_sync(0xffffffffu, pos, 1);
+            const int start = lane == 0 ? prev : up;
+            if (active) add(t - dir, (unsigned)(pos - start));
+            const int lastk = min(31, nedges - 1 - e0);
+            prev = __shfl_sync(0xffffffffu, pos, lastk);
+          }
+          if (lane == 0) add(r_last, (unsigned)(n - prev));
+          const unsigned wn = __reduce_add_sync(0xffffffffu, norm);
+          if (lane == 0 && wn) atomicAdd(Q.hist + (size_t)e * Q.hist_words + (size_t)ns * tnb + job_j, wn);
+        }
+      }
+      BKM_STAMP(1);
+      cta_arrive(bar);
+      ++bar_count;
+      if (!cta_wait_ge(bar, bar_count * G, abort_flag, &S.ok)) break;
+      BKM_STAMP(2);
+    }
+
+    // ---- lookup + event likelihood + tail of the chain this CTA owns ---------------------------
+    if (mine >= 0) batch_lookup_tail(S, Q, mine, mode, tnb, tid);
+    BKM_STAMP(4);
+    if (Q.rebin && s + 1 < total_super) {      // proposals published, histograms cleared
+      cta_arrive(bar);
+      ++bar_count;
+      if (!cta_wait_ge(bar, bar_count * G, abort_flag, &S.ok)) break;
+    }
+    BKM_STAMP(5);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+typedef void (*MonoKernel)(const MonoParams, const BatchParams);
+struct MonoEntry {
+  int nops;
+  unsigned codes;
+  MonoKernel k;
+};
+static const MonoEntry g_mono_table[] = {
+    {-1, 0u, chain_batch_mono_kernel<-1, 0u>},
+    {0, 0u, chain_batch_mono_kernel<0, 0u>},
+    {1, OPC(SXMC_SYST_SHIFT, 0, 0), chain_batch_mono_kernel<1, OPC(SXMC_SYST_SHIFT, 0, 0)>},
+    {1, OPC(SXMC_SYST_SCALE, 0, 0), chain_batch_mono_kernel<1, OPC(SXMC_SYST_SCALE, 0, 0)>},
+};
+
+constexpr size_t MONO_STATIC_RESERVE = 36 * 1024;   // BatchShared + slack
+constexpr size_t MONO_CAP_SAMPLES = (227 * 1024 - MONO_STATIC_RESERVE) / sizeof(float);
+
+// nominal (no systematics) rank of a sample, on the host: only used to balance the ranges
+static int host_rank(float xf, const BinLaunch& L) {
+  const double x = (double)xf;
+  if (!(x >= L.lower[0])) return 0;
+  if (!(x < L.upper[0])) return L.max_total_nbins + 2;
+  return (int)((x - L.lower[0]) * L.scale[0]) + 1;
+}
+
+// Cut every job's sorted samples into contiguous ranges, one per CTA, so that no range holds
+// more than `cap` samples and the largest number of bin edges inside a range is as small as
+// possible.  nsamples[j] = real (unpadded) samples of job j.
+int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples, int nchains, MonoPlan* plan) {
+  if (!L.fast || L.nobs != 1 || L.nslots != 1 || L.njobs > FAST_MAX_JOBS || nchains < 1 ||
+      nchains > BATCH_MAX_CHAINS) {
+    set_error("monotone chain batch: fit shape not supported");
+    return SXMC_ESTATE;
+  }
+  int dev = 0, sms = 0;
+  SXMC_CUDA(cudaGetDevice(&dev));
+  SXMC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  if (sms > MONO_MAX_CTAS) sms = MONO_MAX_CTAS;
+  if (nchains > sms) { set_error("monotone chain batch: more chains than SMs"); return SXMC_ESTATE; }
+  const int nj = L.njobs;
+  const int nranks = L.max_total_nbins + 3;
+  // sorted samples of every job on the host, and the first position of every nominal rank
+  std::vector<std::vector<unsigned>> edge(nj);
+  std::vector<int> span(nj, 1);
+  std::vector<unsigned long long> need(nj);
+  unsigned long long need_total = 0, span_total = 0;
+  for (int j = 0; j < nj; ++j) {
+    const BinJob& job = L.jobs_host[j];
+    const unsigned long long n = nsamples[j];
+    if (n >= (1ull << 31)) { set_error("monotone chain batch: too many samples"); return SXMC_ESTATE; }
+    std::vector<float> tiled((size_t)job.nwtiles * WT_SAMPLES);
+    if (!tiled.empty())
+      SXMC_CUDA(cudaMemcpy(tiled.data(), job.cols[job.slot_field[0]], sizeof(float) * tiled.size(),
+                           cudaMemcpyDeviceToHost));
+    std::vector<int> rk((size_t)n);
+    for (unsigned long long s = 0; s < n; ++s) rk[(size_t)s] = host_rank(tiled[(size_t)tiled_offset(s)], L);
+    if (!std::is_sorted(rk.begin(), rk.end())) {
+      set_error("monotone chain batch: samples are not sorted by the observable");
+      return SXMC_ESTATE;
+    }
+    edge[j].resize(nranks + 1);
+    for (int t = 0; t <= nranks; ++t)
+      edge[j][t] = (unsigned)(std::lower_bound(rk.begin(), rk.end(), t) - rk.begin());
+    if (n) span[j] = std::max(1, rk[(size_t)n - 1] - rk[0] + 1);
+    need[j] = (n + MONO_CAP_SAMPLES - 1) / MONO_CAP_SAMPLES;
+    need_total += need[j];
+    span_total += n ? span[j] : 0;
+  }
+  if (need_total > (unsigned long long)sms) {
+    set_error("chain batch: the samples do not fit in shared memory (not a small fit)");
+    return SXMC_ESTATE;
+  }
+  // CTAs per job: its capacity minimum, the rest in proportion to the bin edges it spans
+  std::vector<int> ctas(nj);
+  int used = 0;
+  for (int j = 0; j < nj; ++j) { ctas[j] = (int)need[j]; used += ctas[j]; }
+  while (used < sms) {
+    int best = -1;
+    double score = 0;
+    for (int j = 0; j < nj; ++j) {
+      if (!nsamples[j]) continue;
+      const double sc = (double)span[j] / ctas[j];
+      if (best < 0 || sc > score) { best = j; score = sc; }
+    }
+    if (best < 0) break;
+    ctas[best] += 1;
+    used += 1;
+  }
+  MonoParams& M = plan->params;
+  memset(&M, 0, sizeof M);
+  for (int i = 0; i < 3; ++i) { M.geo.lo[i] = L.lower[i]; M.geo.hi[i] = L.upper[i]; M.geo.sc[i] = L.scale[i]; M.geo.st[i] = L.stride[i]; }
+  M.geo.total_nbins = L.max_total_nbins;
+  M.njobs = nj;
+  unsigned max_n = 0;
+  int cta = 0, max_edges = 0;
+  for (int j = 0; j < nj; ++j) {
+    const BinJob& src = L.jobs_host[j];
+    MonoJob& d = M.job[j];
+    d.col = src.cols[src.slot_field[0]];
+    d.nsyst = src.nsyst;
+    for (int k = 0; k < src.nsyst && k < FAST_MAX_OPS; ++k) {
+      d.code[k] = (unsigned short)(src.syst[k].type | (src.syst[k].obs_slot << 4) | (src.syst[k].extra_slot << 8));
+      d.pidx[k] = src.syst[k].pidx[0];
+      d.npars[k] = (unsigned char)(src.syst[k].npars > 0);
+    }
+    const unsigned n = (unsigned)nsamples[j];
+    if (!n) continue;
+    // greedy cut for a given edge budget E: ranges needed
+    auto cut = [&](int E, std::vector<unsigned>* out) {
+      int count = 0;
+      unsigned pos = 0;
+      while (pos < n) {
+        // rank at pos = largest t with edge[t] <= pos
+        const int r = (int)(std::upper_bound(edge[j].begin(), edge[j].end(), pos) - edge[j].begin()) - 1;
+        const int lim = std::min(nranks, r + E);
+        unsigned next = edge[j][lim];
+        if (next <= pos) next = n;
+        next = std::min<unsigned>(next, pos + (unsigned)MONO_CAP_SAMPLES);
+        next = std::min(next, n);
+        if (out) { out->push_back(pos); out->push_back(next - pos); }
+        pos = next;
+        ++count;
+      }
+      return count;
+    };
+    int lo = 1, hi = nranks;
+    while (lo < hi) {
+      const int mid = (lo + hi) / 2;
+      if (cut(mid, nullptr) <= ctas[j]) hi = mid; else lo = mid + 1;
+    }
+    std::vector<unsigned> ranges;
+    const int got = cut(lo, &ranges);
+    if (got > ctas[j]) { set_error("monotone chain batch: partition failed"); return SXMC_ESTATE; }
+    max_edges = std::max(max_edges, lo);
+    for (int q = 0; q < ctas[j]; ++q, ++cta) {
+      M.jobof[cta] = (unsigned char)j;
+      if (q < got) { M.s0[cta] = ranges[2 * q]; M.n[cta] = ranges[2 * q + 1]; max_n = std::max(max_n, M.n[cta]); }
+    }
+  }
+  plan->grid = sms;
+  plan->smem_bytes = ((size_t)max_n * sizeof(float) + 127) & ~(size_t)127;
+  plan->max_edges = max_edges;
+  plan->prog_nops = L.prog_nops;
+  plan->prog_codes = L.prog_codes;
+  return SXMC_OK;
+}
+
+int launch_chain_batch_mono(const MonoPlan& plan, const BatchParams& Q0, cudaStream_t stream) {
+  MonoKernel fk = nullptr;
+  for (const MonoEntry& e : g_mono_table)
+    if (e.nops == plan.prog_nops && (plan.prog_nops <= 0 || e.codes == plan.prog_codes)) fk = e.k;
+  if (!fk) fk = g_mono_table[0].k;      // run-time dispatch of the systematics
+  const size_t smem = std::max<size_t>(plan.smem_bytes, 128);
+  SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fk, FAST_THREADS, smem));
+  if (occ < 1) { set_error("monotone chain batch kernel does not fit on an SM"); return SXMC_ESTATE; }
+  BatchParams Q = Q0;
+  void* args[2] = {(void*)&plan.params, (void*)&Q};
+  SXMC_CUDA(cudaLaunchCooperativeKernel((const void*)fk, dim3((unsigned)plan.grid), dim3(FAST_THREADS), args, smem,
+                                        stream));
+  return SXMC_OK;
+}
+
+}  // namespace sxmc

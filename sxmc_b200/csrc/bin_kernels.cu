@@ -292,14 +292,6 @@ __global__ void iota_kernel(unsigned* idx, unsigned long long n) {
   if (i < n) idx[i] = (unsigned)i;
 }
 
-// sorted position s -> tiled position (see common.cuh)
-__host__ __device__ __forceinline__ unsigned long long tiled_offset(unsigned long long s) {
-  const unsigned long long wt = s / WT_SAMPLES;
-  const unsigned r = (unsigned)(s % WT_SAMPLES);
-  const unsigned lane = r / LANE_RUN, i = r % LANE_RUN;
-  return ((wt * WT_ROWS + (i >> 2)) * 32ull + lane) * 4ull + (i & 3);
-}
-
 __global__ void gather_tiled_kernel(const float* __restrict__ aos, const unsigned* __restrict__ idx,
                                     unsigned long long n, unsigned long long npad, int nfields,
                                     int nobs, float* cols, unsigned long long col_pitch,

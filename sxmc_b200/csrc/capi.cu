@@ -1634,6 +1634,9 @@ struct sxmc_batch {
   int last_n = 0;
   unsigned long long* stamps_dev = nullptr;   // profiling hook
   bool mono = false;                // 1-D monotone program on sorted, NaN-free samples
+  MonoPlan* mono_plan = nullptr;    // built on the first run (host partition of the sorted samples)
+  bool mono_plan_failed = false;
+  int last_path = 0;                // 1 = monotone kernel, 2 = sample-by-sample kernel
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -1651,6 +1654,7 @@ int sxmc_batch_destroy(sxmc_batch* b) {
   if (b->st_host) cudaFreeHost(b->st_host);
   if (b->sync_host) cudaFreeHost(b->sync_host);
   b->jobs.release();
+  delete b->mono_plan;
   if (b->ev0) cudaEventDestroy(b->ev0);
   if (b->ev1) cudaEventDestroy(b->ev1);
   if (b->stream) cudaStreamDestroy(b->stream);
@@ -1811,8 +1815,22 @@ int sxmc_batch_enable_trace(sxmc_batch* b, int on) { b->trace = on != 0; return 
 int sxmc_batch_run(sxmc_batch* b, int nchains, unsigned nsteps, float burnin_fraction, int debug_mode) {
   if (!b || nchains < 1 || nchains > b->max_chains) SXMC_INVAL("sxmc_batch_run: nchains out of range");
   const int np = b->nparameters, ns = b->nsignals;
+  // monotone fits: edge search over sorted samples (batch_mono_kernels.cu); others: the
+  // sample-by-sample batch kernel (batch_kernels.cu)
+  bool use_mono = b->mono && !g_no_mono && !b->mono_plan_failed;
+  if (use_mono && !b->mono_plan) {
+    std::vector<unsigned long long> nsamp(ns);
+    for (int j = 0; j < ns; ++j) nsamp[j] = b->pdfs[j]->nsamples;
+    b->mono_plan = new MonoPlan;
+    if (plan_chain_batch_mono(b->jobs.launch, nsamp.data(), b->max_chains, b->mono_plan) != SXMC_OK) {
+      delete b->mono_plan;
+      b->mono_plan = nullptr;
+      b->mono_plan_failed = true;
+      use_mono = false;
+    }
+  }
   BatchPlan plan;
-  SXMC_TRY(plan_chain_batch(b->jobs.launch, nchains, &plan));
+  if (!use_mono) SXMC_TRY(plan_chain_batch(b->jobs.launch, nchains, &plan));
   std::vector<NllSignal> sg((size_t)nchains * ns);
   std::vector<long long> nev(nchains);
   for (int e = 0; e < nchains; ++e) {
@@ -1867,7 +1885,9 @@ int sxmc_batch_run(sxmc_batch* b, int nchains, unsigned nsteps, float burnin_fra
   Q.stamps = b->stamps_dev;
   Q.mono = (b->mono && !g_no_mono) ? 1 : 0;
   SXMC_CUDA(cudaEventRecord(b->ev0, b->stream));
-  SXMC_TRY(launch_chain_batch(plan, Q, b->stream));
+  if (use_mono) SXMC_TRY(launch_chain_batch_mono(*b->mono_plan, Q, b->stream));
+  else SXMC_TRY(launch_chain_batch(plan, Q, b->stream));
+  b->last_path = use_mono ? 1 : 2;
   SXMC_CUDA(cudaEventRecord(b->ev1, b->stream));
   SXMC_CUDA(cudaMemcpyAsync(b->sync_host, b->sync_dev, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost, b->stream));
   SXMC_CUDA(cudaMemcpyAsync(b->st_host, b->st_dev, sizeof(ChainState) * nchains, cudaMemcpyDeviceToHost, b->stream));
@@ -1914,6 +1934,11 @@ int sxmc_batch_contour(sxmc_batch* b, int slot, float delta, float* lower_out, f
 }
 
 int sxmc_batch_loop_ms(sxmc_batch* b, float* ms_out) { *ms_out = b->loop_ms; return SXMC_OK; }
+int sxmc_batch_last_path(sxmc_batch* b, int* path_out, int* max_edges_out) {
+  *path_out = b->last_path;
+  if (max_edges_out) *max_edges_out = b->mono_plan ? b->mono_plan->max_edges : 0;
+  return SXMC_OK;
+}
 
 int sxmc_batch_phase_stamps(sxmc_batch* b, int enable, unsigned long long* out148x8) {
   if (enable && !b->stamps_dev) {

@@ -27,6 +27,14 @@ constexpr int BIN_WARPS = BIN_THREADS / 32;     // warp-tiles per block-tile
 #endif
 constexpr int FAST_WARPS = SXMC_FAST_WARPS;     // warps of the persistent fast binning CTA
 constexpr int FAST_THREADS = FAST_WARPS * 32;
+// sorted position s -> offset inside a tiled column
+__host__ __device__ __forceinline__ unsigned long long tiled_offset(unsigned long long s) {
+  const unsigned long long wt = s / WT_SAMPLES;
+  const unsigned r = (unsigned)(s % WT_SAMPLES);
+  const unsigned lane = r / LANE_RUN, i = r % LANE_RUN;
+  return ((wt * WT_ROWS + (i >> 2)) * 32ull + lane) * 4ull + (i & 3);
+}
+
 constexpr int FAST_MAX_STAGES = 8;              // bulk-copy pipeline stages per warp
 
 constexpr int MAX_SLOTS = 6;                    // columns the fast kernel keeps in registers
@@ -130,6 +138,25 @@ struct BatchParams {
   int group;
   int mono;                     // 1-D monotone program on sorted samples: endpoint evaluation (batch_kernels.cu)
   unsigned long long* stamps;   // optional [grid][8] %globaltimer stamps of super-step 20 (profiling)
+};
+
+// Arguments of the monotone chain batch kernel (batch_mono_kernels.cu), by value: every CTA
+// holds the sorted samples [s0, s0 + n) of one job as a plain float array in shared memory.
+constexpr int MONO_MAX_CTAS = 160;
+struct MonoJob {
+  const float* col;                    // the observable's column (tiled layout)
+  int nsyst;
+  unsigned short code[FAST_MAX_OPS];   // type | obs_slot << 4 | extra_slot << 8 (as FastJob)
+  short pidx[FAST_MAX_OPS];
+  unsigned char npars[FAST_MAX_OPS];
+};
+struct MonoParams {
+  FastGeo geo;
+  MonoJob job[FAST_MAX_JOBS];
+  unsigned s0[MONO_MAX_CTAS];
+  unsigned n[MONO_MAX_CTAS];
+  unsigned char jobof[MONO_MAX_CTAS];
+  int njobs;
 };
 
 // One signal as seen by the lookup + event-likelihood kernel.

@@ -95,6 +95,17 @@ struct BatchPlan {
 };
 int plan_chain_batch(const BinLaunch& L, int nchains, BatchPlan* plan);
 int launch_chain_batch(const BatchPlan& plan, const BatchParams& Q, cudaStream_t stream);
+// ---- batch_mono_kernels.cu ----
+struct MonoPlan {
+  MonoParams params;
+  int grid;
+  size_t smem_bytes;
+  int max_edges;          // largest number of nominal bin edges inside one CTA's range
+  int prog_nops;
+  unsigned prog_codes;
+};
+int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples, int nchains, MonoPlan* plan);
+int launch_chain_batch_mono(const MonoPlan& plan, const BatchParams& Q, cudaStream_t stream);
 int column_has_nan_or_neginf(const float* col_dev, unsigned long long n, bool* out, cudaStream_t stream);
 
 // ---- ensemble_kernels.cu ----

@@ -333,6 +333,12 @@ class MCMCBatch:
         _check(lib().sxmc_batch_loop_ms(self._b, C.byref(v)))
         return v.value
 
+    def last_path(self):
+        """(1 = monotone edge-search kernel | 2 = sample-by-sample kernel, max edges per CTA)"""
+        a, b = C.c_int(0), C.c_int(0)
+        _check(lib().sxmc_batch_last_path(self._b, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
 
 def build_fit(fit, sort=True, batch=0):
     """FitSpec (sxmc_b200.workloads) -> (hists, MCMC), the way src/signal.cpp:112-169 and

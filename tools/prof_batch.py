@@ -31,7 +31,8 @@ def main():
     base = t[:, 0].min()
     rel = (t[:, :6] - base) / 1e3
     per = 1e3 * mb.loop_ms() / (a.steps + 1)
-    print("workload %s, %d chains: %.1f us/super-step = %.3f us/chain-step" % (a.workload, a.chains, per, per / a.chains))
+    print("workload %s, %d chains: %.1f us/super-step = %.3f us/chain-step (path, max edges = %s)" %
+          (a.workload, a.chains, per, per / a.chains, mb.last_path()))
     names = ["start", "bin done", "barrier1 out", "lookup done", "tail done", "barrier2 out"]
     for k, n in enumerate(names):
         print("  %-13s min/mean/max %8.2f %8.2f %8.2f us" % (n, rel[:, k].min(), rel[:, k].mean(), rel[:, k].max()))
