@@ -22,6 +22,7 @@ struct BatchShared {
   FinState F;
   int ok;
   long long ne;
+  float pdf[BATCH_PDF_TABLE];      // PDF values of every (signal, bin) at the proposed point (grouped lookup)
 };
 
 // once per launch: the owned chain's state and signal tables into shared memory
@@ -67,6 +68,27 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
   __syncthreads();
   const long long my_ne = S.ne;
   double sum = 0;
+  if (Q.mult) {
+    // Grouped lookup.  Every signal reads the same dataset, so events in the same bin have the
+    // same likelihood: sum_i log(s_i) = sum_b m_b log(s_b), m_b = events of this chain in bin b
+    // (counted once when the data were set).  eval_pdf's division runs once per (signal, bin)
+    // instead of once per (signal, event), and the values live in shared memory.
+    for (int q = tid; q < ns * tnb; q += FAST_THREADS) {
+      const int j = q / tnb;
+      float v = (float)((double)__ldcg(my_hist + q) / S.bn[j]);              // pdfz.cpp:429-432
+      if (isnan(v)) v = 0.0f;                                                  // nll_kernels.cpp:107
+      S.pdf[q] = v;
+    }
+    __syncthreads();
+    const unsigned* mult = Q.mult + (size_t)mine * tnb;
+    for (int b = tid; b < tnb; b += FAST_THREADS) {
+      const unsigned m = mult[b];
+      if (!m) continue;
+      double acc = 0;
+      for (int j = 0; j < ns; ++j) acc = __dadd_rn(acc, __dmul_rn(S.c[j], (double)S.pdf[j * tnb + b]));
+      if (acc > 0) sum += (double)m * log(acc);
+    }
+  } else
   for (long long i = tid; i < my_ne; i += FAST_THREADS) {
     double acc = 0;
     for (int j = 0; j < ns; ++j) {

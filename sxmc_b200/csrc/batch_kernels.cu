@@ -264,7 +264,7 @@ struct BatchEntry {
 static const BatchEntry g_batch_table[] = { SXMC_FAST_TABLE(FE) };
 #undef FE
 
-constexpr size_t BK_STATIC_RESERVE = 40 * 1024;   // static shared memory of the kernel above
+constexpr size_t BK_STATIC_RESERVE = 56 * 1024;   // static shared memory of the kernel above
 
 // Shared-memory plan: GROUP histograms + resident stages.  Fails when the samples of a CTA do
 // not fit (the fit is not "small": run its chains one at a time with the streaming kernels).

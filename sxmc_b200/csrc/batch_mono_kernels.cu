@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 1)
 chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_constant__ BatchParams Q) {
   extern __shared__ __align__(16) float s_x[];       // this CTA's sorted samples
   __shared__ BatchShared S;
+  __shared__ double s_par[BATCH_MAX_CHAINS][FAST_MAX_OPS];   // every chain's systematic coefficients
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -104,15 +105,37 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
     // ---- bin: warp w takes chains w, w + 16, ... ---------------------------------------------
     if (bin_now) {
       if (n > 0) {
+        // all chains' coefficients in one round of loads (a warp would otherwise pay an L2 round
+        // trip per chain)
+        for (int q = tid; q < nch * FAST_MAX_OPS; q += FAST_THREADS) {
+          const int e = q / FAST_MAX_OPS, k = q % FAST_MAX_OPS;
+          double par = 0.0;
+          if (k < nsyst && job.npars[k]) par = __ldcg(&Q.st[e].proposed[nsources + job.pidx[k]]);
+          s_par[e][k] = par;
+        }
+        __syncthreads();
         for (int e = warp; e < nch; e += FAST_WARPS) {
+          const bool dbg = Q.stamps && s == 20u && blockIdx.x == 70 && tid == 0 && e == 0;
+          long long tq0 = 0, tq1 = 0, tq2 = 0, tq3 = 0;
+          if (dbg) tq0 = clock64();
           double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
 #pragma unroll
           for (int k = 0; k < FAST_MAX_OPS; ++k) {
             op_c0[k] = 0.0; op_onep[k] = 1.0;
             if (k < nsyst) {
-              const double par = job.npars[k] ? __ldcg(&Q.st[e].proposed[nsources + job.pidx[k]]) : 0.0;
-              op_c0[k] = __dadd_rn(0.0, __dmul_rn(par, 1.0));      // src/pdfz.cpp:310-314
+              op_c0[k] = __dadd_rn(0.0, __dmul_rn(s_par[e][k], 1.0));      // src/pdfz.cpp:310-314
               op_onep[k] = __dadd_rn(1.0, op_c0[k]);
+            }
+          }
+          // the program as an affine map (guesses only; never decides a count)
+          double aff_a = 1.0, aff_b = 0.0;
+#pragma unroll
+          for (int k = 0; k < FAST_MAX_OPS; ++k) {
+            if (k < nsyst) {
+              const int type = op_code[k] & 15;
+              if (type == SXMC_SYST_SHIFT) aff_b += op_c0[k];
+              else if (type == SXMC_SYST_SCALE) { aff_a *= op_onep[k]; aff_b *= op_onep[k]; }
+              else if (type == SXMC_SYST_CTSCALE) { aff_a *= op_onep[k]; aff_b = 1.0 + (aff_b - 1.0) * op_onep[k]; }
             }
           }
           auto rank_at = [&](int p) {
@@ -129,17 +152,67 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
           const int r_first = rank_at(0), r_last = rank_at(n - 1);
           const int dir = r_last >= r_first ? 1 : -1;
           const int nedges = (r_last - r_first) * dir;
+          if (dbg) tq1 = clock64();
           int prev = 0;                               // start of the run that is still open
           for (int e0 = 0; e0 < nedges; e0 += 32) {
             const int k = e0 + lane;
             const bool active = k < nedges;
             const int t = r_first + dir * (k + 1);
-            // first position whose rank has reached t (exists: the last sample has rank r_last)
+            // first position whose rank has reached t (exists: the last sample has rank r_last).
+            // A guess comes from inverting the affine map x' = aff_a x + aff_b in plain floating
+            // point and a float-only bisection of the samples; the answer is then settled with
+            // the exact arithmetic: gallop away from the guess, bisect what is left (usually two
+            // evaluations in all).
             int lo = 0, hi = n - 1;
             if (active) {
+              auto pred = [&](int p) { return (rank_at(p) - t) * dir >= 0; };
+              const int rb = dir > 0 ? t : t + 1;          // rank whose lower boundary is crossed
+              const double bv = rb <= tnb + 1 ? geo.lo[0] + (double)(rb - 1) / geo.sc[0] : geo.hi[0];
+              const float thr = (float)((bv - aff_b) / aff_a);
+              int p0 = n >> 1;
+              if (thr == thr) {
+                int a0 = 0, a1 = n;                        // first sample >= thr (floats only)
+                while (a0 < a1) {
+                  const int mid = (a0 + a1) >> 1;
+                  if (s_x[mid] < thr) a0 = mid + 1; else a1 = mid;
+                }
+                p0 = min(a0, n - 1);
+              }
+              if (dbg) tq2 = clock64();
+              // the guess and its two neighbours, evaluated together (the answer is almost
+              // always one of them)
+              const int pm = max(p0 - 1, 0), pp = min(p0 + 1, n - 1);
+              const bool f_m = pred(pm), f_0 = pred(p0), f_p = pred(pp);
+              if (f_0) {
+                hi = p0;
+                if (p0 == 0) {
+                  lo = 0;
+                } else if (!f_m) {
+                  lo = p0;
+                } else {
+                  hi = pm;
+                  int step = 1;
+                  while (hi > 0) {
+                    const int q = max(hi - step, 0);
+                    if (pred(q)) { hi = q; step <<= 1; } else { lo = q + 1; break; }
+                  }
+                  if (hi == 0) lo = 0;
+                }
+              } else if (f_p) {
+                lo = hi = pp;
+              } else {
+                lo = pp + 1;
+                int step = 1;
+                while (lo < hi) {
+                  const int q = min(lo + step - 1, hi);
+                  if (pred(q)) { hi = q; break; }
+                  lo = q + 1;
+                  step <<= 1;
+                }
+              }
               while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
-                if ((rank_at(mid) - t) * dir >= 0) hi = mid; else lo = mid + 1;
+                if (pred(mid)) hi = mid; else lo = mid + 1;
               }
             }
             const int pos = active ? lo : n;
@@ -149,9 +222,16 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
             const int lastk = min(31, nedges - 1 - e0);
             prev = __shfl_sync(0xffffffffu, pos, lastk);
           }
+          if (dbg) tq3 = clock64();
           if (lane == 0) add(r_last, (unsigned)(n - prev));
           const unsigned wn = __reduce_add_sync(0xffffffffu, norm);
           if (lane == 0 && wn) atomicAdd(Q.hist + (size_t)e * Q.hist_words + (size_t)ns * tnb + job_j, wn);
+          if (dbg) {
+            unsigned long long* d = Q.stamps + 148 * 8;
+            d[0] = (unsigned long long)(tq1 - tq0); d[1] = (unsigned long long)(tq2 - tq1);
+            d[2] = (unsigned long long)(tq3 - tq2); d[3] = (unsigned long long)(clock64() - tq3);
+            d[4] = (unsigned long long)nedges; d[5] = (unsigned long long)n;
+          }
         }
       }
       BKM_STAMP(1);
@@ -187,7 +267,7 @@ static const MonoEntry g_mono_table[] = {
     {1, OPC(SXMC_SYST_SCALE, 0, 0), chain_batch_mono_kernel<1, OPC(SXMC_SYST_SCALE, 0, 0)>},
 };
 
-constexpr size_t MONO_STATIC_RESERVE = 36 * 1024;   // BatchShared + slack
+constexpr size_t MONO_STATIC_RESERVE = 52 * 1024;   // BatchShared + slack
 constexpr size_t MONO_CAP_SAMPLES = (227 * 1024 - MONO_STATIC_RESERVE) / sizeof(float);
 
 // nominal (no systematics) rank of a sample, on the host: only used to balance the ranges

@@ -1634,6 +1634,7 @@ struct sxmc_batch {
   int last_n = 0;
   unsigned long long* stamps_dev = nullptr;   // profiling hook
   bool mono = false;                // 1-D monotone program on sorted, NaN-free samples
+  unsigned* mult_dev = nullptr;     // [max_chains][total_nbins] events per bin, when the grouped lookup applies
   MonoPlan* mono_plan = nullptr;    // built on the first run (host partition of the sorted samples)
   bool mono_plan_failed = false;
   int last_path = 0;                // 1 = monotone kernel, 2 = sample-by-sample kernel
@@ -1650,7 +1651,7 @@ int sxmc_batch_destroy(sxmc_batch* b) {
     cudaFree(s.nll_trace); cudaFree(s.prop_trace);
   }
   cudaFree(b->st_dev); cudaFree(b->hist_dev); cudaFree(b->sigs_dev); cudaFree(b->nevents_dev);
-  cudaFree(b->sync_dev); cudaFree(b->points_dev); cudaFree(b->stamps_dev);
+  cudaFree(b->sync_dev); cudaFree(b->points_dev); cudaFree(b->stamps_dev); cudaFree(b->mult_dev);
   if (b->st_host) cudaFreeHost(b->st_host);
   if (b->sync_host) cudaFreeHost(b->sync_host);
   b->jobs.release();
@@ -1704,6 +1705,9 @@ int sxmc_batch_create(const sxmc_chain_config* cfg, int max_chains, sxmc_batch**
   if (e == cudaSuccess) e = cudaMallocHost(&b->sync_host, sizeof(unsigned) * 4);
   if (e == cudaSuccess) e = cudaEventCreate(&b->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&b->ev1);
+  // grouped lookup: one dataset for all signals and a (signal, bin) table that fits on chip
+  if (e == cudaSuccess && b->shared_rb && (size_t)b->nsignals * b->total_nbins <= (size_t)BATCH_PDF_TABLE)
+    e = cudaMalloc(&b->mult_dev, sizeof(unsigned) * (size_t)b->total_nbins * max_chains);
   if (e != cudaSuccess) { sxmc_batch_destroy(b); return cuda_fail(e, "sxmc_batch_create", __FILE__, __LINE__); }
   // the binning jobs (columns, systematic programs); outputs are addressed by the kernel itself
   int rc = b->jobs.reserve(b->nsignals);
@@ -1776,6 +1780,9 @@ static int batch_slot_points(sxmc_batch* b, BatchSlot* s, const float* points_de
     SXMC_TRY(launch_read_bins(points_dev, (long long)nevents, b->nobs, g, b->pdfs[j]->dataset,
                               s->read_bins + (size_t)j * s->rb_cap, b->stream));
   }
+  if (b->mult_dev)
+    SXMC_TRY(launch_event_mult(s->read_bins, (long long)nevents, b->total_nbins,
+                               b->mult_dev + (size_t)(s - b->slots.data()) * b->total_nbins, b->stream));
   return SXMC_OK;
 }
 
@@ -1883,6 +1890,7 @@ int sxmc_batch_run(sxmc_batch* b, int nchains, unsigned nsteps, float burnin_fra
   Q.nsteps = nsteps; Q.do_init = 1;
   Q.rebin = (b->nsystematics > 0 && !b->systematics_fixed) ? 1 : 0;   // src/mcmc.cpp:264
   Q.stamps = b->stamps_dev;
+  Q.mult = b->mult_dev;
   Q.mono = (b->mono && !g_no_mono) ? 1 : 0;
   SXMC_CUDA(cudaEventRecord(b->ev0, b->stream));
   if (use_mono) SXMC_TRY(launch_chain_batch_mono(*b->mono_plan, Q, b->stream));
@@ -1942,11 +1950,11 @@ int sxmc_batch_last_path(sxmc_batch* b, int* path_out, int* max_edges_out) {
 
 int sxmc_batch_phase_stamps(sxmc_batch* b, int enable, unsigned long long* out148x8) {
   if (enable && !b->stamps_dev) {
-    SXMC_CUDA(cudaMalloc(&b->stamps_dev, sizeof(unsigned long long) * 148 * 8));
-    SXMC_CUDA(cudaMemset(b->stamps_dev, 0, sizeof(unsigned long long) * 148 * 8));
+    SXMC_CUDA(cudaMalloc(&b->stamps_dev, sizeof(unsigned long long) * (148 * 8 + 16)));
+    SXMC_CUDA(cudaMemset(b->stamps_dev, 0, sizeof(unsigned long long) * (148 * 8 + 16)));
   }
-  if (out148x8 && b->stamps_dev)
-    SXMC_CUDA(cudaMemcpy(out148x8, b->stamps_dev, sizeof(unsigned long long) * 148 * 8, cudaMemcpyDeviceToHost));
+  if (out148x8 && b->stamps_dev)   // + 16 words of per-chain clock deltas of one warp (monotone kernel)
+    SXMC_CUDA(cudaMemcpy(out148x8, b->stamps_dev, sizeof(unsigned long long) * (148 * 8 + 16), cudaMemcpyDeviceToHost));
   if (!enable && b->stamps_dev) { cudaFree(b->stamps_dev); b->stamps_dev = nullptr; }
   return SXMC_OK;
 }

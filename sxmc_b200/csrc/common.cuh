@@ -124,6 +124,7 @@ struct PersistParams {
 // Arguments of the chain batch kernel (batch_kernels.cu), by value.
 constexpr int BATCH_MAX_CHAINS = 148;   // one chain per SM in the lookup/tail phase
 constexpr int BATCH_MAX_GROUP = 8;      // chains binned per shared-memory histogram pass
+constexpr int BATCH_PDF_TABLE = 4096;   // (signal, bin) PDF values kept in shared memory by the grouped lookup
 struct BatchParams {
   ChainState* st;               // [nchains]
   const NllSignal* sigs;        // [nchains][ns]: per-chain read_bins; bins/norm unused here
@@ -136,6 +137,7 @@ struct BatchParams {
   int do_init;                  // first super-step = initial evaluation + first proposal
   int rebin;
   int group;
+  const unsigned* mult;         // optional [nchains][total_nbins] events per bin (grouped lookup), else NULL
   int mono;                     // 1-D monotone program on sorted samples: endpoint evaluation (batch_kernels.cu)
   unsigned long long* stamps;   // optional [grid][8] %globaltimer stamps of super-step 20 (profiling)
 };

@@ -172,6 +172,23 @@ int launch_generate(const GenSignal* sigs_dev, int n, const GenGeo& geo, int poi
   return SXMC_OK;
 }
 
+// events per bin of one dataset (grouped lookup of the chain batch kernels)
+__global__ void event_mult_kernel(const int* __restrict__ read_bins, long long n, int tnb, unsigned* mult) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int b = read_bins[i];
+    if (b >= 0 && b < tnb) atomicAdd(mult + b, 1u);
+  }
+}
+int launch_event_mult(const int* read_bins_dev, long long nevents, int tnb, unsigned* mult_dev, cudaStream_t stream) {
+  SXMC_CUDA(cudaMemsetAsync(mult_dev, 0, sizeof(unsigned) * (size_t)tnb, stream));
+  if (nevents <= 0) return SXMC_OK;
+  long long blocks = (nevents + 255) / 256;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  event_mult_kernel<<<(unsigned)blocks, 256, 0, stream>>>(read_bins_dev, nevents, tnb, mult_dev);
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
 // inclusive prefix sums of one histogram, single block (histograms are small and this runs once
 // per generator, not per experiment)
 __global__ void cum_kernel(const unsigned* __restrict__ bins, int nb, unsigned* __restrict__ cum) {

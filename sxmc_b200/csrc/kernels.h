@@ -109,6 +109,7 @@ int launch_chain_batch_mono(const MonoPlan& plan, const BatchParams& Q, cudaStre
 int column_has_nan_or_neginf(const float* col_dev, unsigned long long n, bool* out, cudaStream_t stream);
 
 // ---- ensemble_kernels.cu ----
+int launch_event_mult(const int* read_bins_dev, long long nevents, int tnb, unsigned* mult_dev, cudaStream_t stream);
 int launch_cum(const unsigned* bins_dev, int nb, unsigned* cum_dev, cudaStream_t stream);
 int launch_generate(const GenSignal* sigs_dev, int n, const GenGeo& geo, int poisson,
                     unsigned long long seed, unsigned long long stream_id, unsigned long long* counts_dev,

@@ -25,9 +25,10 @@ def main():
     _lib.check(L.sxmc_batch_phase_stamps(mb._b, 1, None))
     mb.run(a.chains, a.steps, 0.1)
     mb.run(a.chains, a.steps, 0.1)
-    raw = np.zeros(148 * 8, dtype=np.uint64)
+    raw = np.zeros(148 * 8 + 16, dtype=np.uint64)
     _lib.check(L.sxmc_batch_phase_stamps(mb._b, 1, raw.ctypes.data_as(C.POINTER(C.c_uint64))))
-    t = raw.reshape(148, 8).astype(np.int64)
+    t = raw[:148 * 8].reshape(148, 8).astype(np.int64)
+    print("  one chain in one warp (CTA 70) [clk]: setup+ends %d, guess %d, exact+add %d, tail %d; edges %d, n %d" % tuple(int(v) for v in raw[148 * 8:148 * 8 + 6]))
     base = t[:, 0].min()
     rel = (t[:, :6] - base) / 1e3
     per = 1e3 * mb.loop_ms() / (a.steps + 1)
