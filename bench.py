@@ -52,6 +52,9 @@ WORKLOAD_TEXT = {
          "resolution_scale systematics, 100k data events",
     "D": "D: 3-D energy x radius x costheta (50x25x20 bins), 30 signals, 100M MC samples in "
          "total, scale + resolution_scale + shift systematics, 100k data events",
+    "E": "E: ensemble of fake experiments on the workload-B fit (Poisson fake data, mean 10k events; "
+         "20000 MCMC steps, burn-in 0.1, 90 % contour limit per experiment), experiments sharded "
+         "round-robin over the GPUs",
 }
 
 
@@ -66,7 +69,10 @@ def parse_args():
     ap.add_argument("--cpu-budget-s", type=float, default=20.0,
                     help="CPU seconds the cpu_baseline / reference arm may spend stepping")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extra", action="store_true", help="skip the extra workload-C line")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra workload-C / ensemble objects")
+    ap.add_argument("--experiments", type=int, default=296,
+                    help="workload E: fake experiments per GPU (whole batches of 148)")
+    ap.add_argument("--esteps", type=int, default=20000, help="workload E: MCMC steps per experiment")
     return ap.parse_args()
 
 
@@ -81,7 +87,7 @@ def measured_peak():
 
 def make_fit(name, scale):
     from sxmc_b200 import workloads
-    return workloads.WORKLOADS[name](scale)
+    return workloads.WORKLOADS["B" if name == "E" else name](scale)
 
 
 def algorithmic_bytes_per_step(fit):
@@ -187,6 +193,23 @@ def run_reference_arm(args, rank, world):
         return
     fit = make_fit(args.workload, args.scale)
     rate, kind, n, what = cpu_steps_per_s(fit, args.cpu_budget_s, want_steps=args.steps)
+    if args.workload == "E":
+        # one experiment = esteps full-size steps (fake-data generation and the limit are
+        # negligible beside them on the CPU): experiments/s from the measured step rate
+        erate = rate / args.esteps
+        what_e = what + "; experiments/s = steps/s / %d steps per experiment" % args.esteps
+        print(json.dumps({
+            "impl": "reference", "metric": "ensemble_experiments_per_sec", "value": erate,
+            "unit": "experiments/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 / rate, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic (seeded numpy, SURVEY 8 distributions)",
+            "config": {"workload": WORKLOAD_TEXT["E"], "steps_per_experiment": args.esteps},
+            "chain_steps_per_s": rate,
+            "cpu_baseline": {"value": erate, "unit": "experiments/s", "cores": 1, "kind": kind,
+                             "sample": what_e, "host_cores_available": os.cpu_count()},
+            "e2e": {"value": erate, "unit": "experiments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}), flush=True)
+        return
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / rate,
@@ -276,6 +299,70 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     return out
 
 
+def measure_ensemble(fit, nexperiments, esteps, rank, world, seed=20261104):
+    """Config E on this rank: its share of `nexperiments * world` experiments through
+    sxmc_b200.ensemble.ensemble() -- fake data drawn on the device, chains advanced 148 at a time by
+    the batch kernel, contour limit per experiment.  Wall clock of the whole call (host logic,
+    data generation, launches, limit extraction)."""
+    import torch
+    from sxmc_b200 import ensemble
+    ensemble.ensemble(fit, 4 * world, nsteps=200, burnin_fraction=0.1, rank=rank, world=world)   # warm-up
+    torch.cuda.synchronize()
+    if torch.distributed.is_initialized():
+        torch.distributed.barrier()
+    t0 = time.perf_counter()
+    r = ensemble.ensemble(fit, nexperiments * world, "s0", 0.9, seed=seed, nsteps=esteps,
+                          burnin_fraction=0.1, rank=rank, world=world)
+    torch.cuda.synchronize()
+    r["wall_s"] = time.perf_counter() - t0
+    return r
+
+
+def run_ensemble_arm(args, rank, world, local):
+    import torch
+    from sxmc_b200 import _lib, sharding
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the b200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.check(_lib.lib().sxmc_init(local))
+    sampler = ClockSampler(local)
+    fit = make_fit("E", args.scale)
+    sampler.start()
+    r = measure_ensemble(fit, args.experiments, args.esteps, rank, world)
+    sampler.stop()
+    wall = allreduce_max(r["wall_s"])
+    loop_ms = allreduce_max(r["loop_ms"])
+    limits = sharding.gather_limits(r["experiments"], r["limits"], args.experiments * world)
+    total = args.experiments * world
+    line = {
+        "metric": "ensemble_experiments_per_sec", "value": total / wall, "unit": "experiments/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * wall / (total * args.esteps), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic (seeded numpy, SURVEY 8 distributions; "
+        "Poisson fake data drawn on the device)",
+        "config": {"workload": WORKLOAD_TEXT["E"], "experiments": total, "steps_per_experiment": args.esteps,
+                   "parallelism": "experiment i on GPU i mod N, Philox stream i; one gather of the limits",
+                   "l2": "not applicable: the samples are resident in shared memory for the whole launch"},
+        "chain_steps_per_s": total * args.esteps / wall,
+        "us_per_chain_step_device": 1e3 * loop_ms / (args.experiments * args.esteps),
+        "time_to_4096_experiments_s": 4096.0 / (total / wall),
+        "median_upper_limit": sharding.median(limits), "mode": r["mode"],
+        "gpu_launches": r["launches"],
+        "e2e": {"value": total / wall, "unit": "experiments/s", "h2d_bytes_per_step": 0.0,
+                "d2h_bytes_per_step": 64.0 / args.esteps,
+                "what": "ensemble.ensemble(): the value above IS the end-to-end wall clock (fake data are "
+                        "generated on the device; per experiment the limit comes back)"},
+        "clocks": sampler.summary(),
+    }
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if torch.distributed.is_initialized():
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
 def allreduce_max(x):
     import torch
     if not torch.distributed.is_initialized():
@@ -346,6 +433,9 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
+    if args.workload == "E":
+        run_ensemble_arm(args, rank, world, local)
+        return
     line, fit, sampler, peak, peak_src = run_own_arm(args, rank, world, local)
     import torch
 
@@ -371,6 +461,19 @@ def main():
             del fitc
         except Exception as e:      # the headline must still print
             line["workload_C"] = {"error": repr(e)}
+
+    # extra: config E (ensemble) on the same fit, one batch of 148 experiments, N=1 only
+    if world == 1 and not args.no_extra and args.workload == "B" and args.scale == 1.0:
+        try:
+            re_ = measure_ensemble(fit, 148, 20000, 0, 1)
+            line["ensemble_E"] = {
+                "workload": WORKLOAD_TEXT["E"], "experiments": 148, "steps_per_experiment": 20000,
+                "experiments_per_s": 148 / re_["wall_s"], "chain_steps_per_s": 148 * 20000 / re_["wall_s"],
+                "us_per_chain_step_device": 1e3 * re_["loop_ms"] / (148 * 20000), "mode": re_["mode"],
+                "gpu_launches": re_["launches"],
+                "note": "148 chains advance in lockstep in one cooperative launch (chain batch kernel)"}
+        except Exception as e:
+            line["ensemble_E"] = {"error": repr(e)}
 
     line["clocks"] = sampler.summary()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
