@@ -85,6 +85,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(name):
+    """dram bytes per launch of the binning kernel from the committed ncu --set full capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01b_ncu_traffic.json")) as f:
+            return json.load(f).get(name)
+    except Exception:
+        return None
+
+
 def make_fit(name, scale):
     from sxmc_b200 import workloads
     return workloads.WORKLOADS["B" if name == "E" else name](scale)
@@ -414,7 +423,9 @@ def run_own_arm(args, rank, world, local):
         "gpu_launches": r["gpu_launches"],
         "roofline": {"bound": "hbm", "kernel": "bin_fast_kernel (transform + binning, all signals "
                      "in one launch)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak,
+                     "traffic": ncu_traffic(args.workload) if args.scale == 1.0 else None,
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "avg_launch_ms": bin_avg_ms, "share_of_step": r["bin_ms"] / r["step_ms"]},
         "kernels_ms_per_step": {"bin": bin_avg_ms, "lookup_nll_metropolis": r["nll_ms"] / K},
@@ -454,7 +465,8 @@ def main():
                 "steps_per_s": a2.steps / (rc["step_ms"] * 1e-3),
                 "samples_binned_per_s": a2.steps / (rc["step_ms"] * 1e-3) * fitc.total_samples(),
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                             "frac": ach / peak, "algorithmic_bytes_per_launch": ab,
+                             "frac": ach / peak, "traffic": ncu_traffic("C"),
+                             "algorithmic_bytes_per_launch": ab,
                              "avg_launch_ms": rc["bin_ms"] / a2.steps},
                 "nll_ms_per_step": rc["nll_ms"] / a2.steps,
                 "build_s": rc["build_s"]}
