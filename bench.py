@@ -278,7 +278,7 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     barrier()
     out.update(step_ms=step_ms, bin_ms=bin_ms, nll_ms=nll_ms)
 
-    # (2) the production form: CUDA-graph chain, steps back to back (L2 stays warm)
+    # (2) the production form: sxmc_chain_advance picks the kernel (monotone / persistent / graph)
     chain.advance(Wm)
     barrier()
     ms0 = chain.loop_ms()
@@ -431,7 +431,7 @@ def run_own_arm(args, rank, world, local):
         "kernels_ms_per_step": {"bin": bin_avg_ms, "lookup_nll_metropolis": r["nll_ms"] / K},
         "chain_back_to_back": {"value": world * K / (warm_ms * 1e-3), "unit": UNIT,
                                "ms_per_step": warm_ms / K,
-                               "note": "CUDA-graph chain, steps back to back, L2 warm (production form)"},
+                               "note": "production form: chain.advance(K), steps back to back (monotone / persistent kernel for small fits, CUDA graph otherwise)"},
         "accept_rate": r["accepted"] / float(2 * K + 2 * args.warmup),
         "build_s": r["build_s"],
     }

@@ -203,11 +203,15 @@ int sxmc_chain_nll_at(sxmc_chain* c, const double* pars, int rebin, double* nll_
 int sxmc_chain_get_norms(sxmc_chain* c, unsigned* norms_out);
 int sxmc_chain_get_lut(sxmc_chain* c, float* lut_out);
 int sxmc_chain_get_bins(sxmc_chain* c, unsigned* bins_out);   /* [nsignals][total_nbins] */
-/* chain execution mode: 0 = automatic (default): the persistent cooperative chain kernel
+/* chain execution mode: 0 = automatic (default): the monotone edge-search kernel for 1-D fits
+ * whose systematics are all shift / scale / ctscale, else the persistent cooperative chain kernel
  * when a step streams < 64 MB (the fit is latency-bound), else a CUDA graph of the per-step
  * kernel sequence; 1 = plain stream launches (debugging / profiling); 2 = persistent kernel
- * or fail; 3 = CUDA graph.  Sample-sharded chains (sxmc_chain_set_comm) never run persistent. */
+ * or fail; 3 = CUDA graph; 4 = monotone kernel or fail.  Sample-sharded chains
+ * (sxmc_chain_set_comm) run 1 or 3 only. */
 int sxmc_chain_set_mode(sxmc_chain* c, int mode);
+/* what the last sxmc_chain_advance used: 1 graph / stream launches, 2 persistent, 4 monotone */
+int sxmc_chain_last_path(sxmc_chain* c, int* path_out);
 /* profiling hook of the persistent kernel: CTA 0 stamps %globaltimer at 8 phase boundaries of
  * the first 64 steps of each launch ([64][8] ns), followed at index 512 by [ncta][4] stamps of
  * every CTA in step 20; out64x8 (may be NULL, else 2048 entries) receives the last launch's. */

@@ -44,7 +44,7 @@ __device__ __forceinline__ void batch_owner_init(BatchShared& S, const BatchPara
 // reduce (src/pdfz.cpp:411-436, src/nll_kernels.cpp:89-146), then finish_step; the histogram is
 // cleared for the next super-step's bin phase.  All threads of the CTA call it.
 __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchParams& Q, int mine, int mode,
-                                                  int tnb, int tid) {
+                                                  int tnb, int tid, bool clear) {
   const int ns = Q.ns, np = Q.np;
   unsigned* const my_hist = Q.hist + (size_t)mine * Q.hist_words;
   FinState& F = S.F;
@@ -104,7 +104,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
   }
   const double total = block_sum<FAST_THREADS>(sum, S.warp);   // ends past a CTA barrier: lookups done
   if (tid == 0) S.warp[0] = total;
-  if (Q.rebin)   // rebuilt from zero by the next super-step's bin phase
+  if (clear)     // rebuilt from zero by the next super-step's bin phase (the last one is kept)
     for (unsigned long long w = tid; w < Q.hist_words; w += FAST_THREADS) my_hist[w] = 0u;
   __syncthreads();
   if (tid < 32) finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid);

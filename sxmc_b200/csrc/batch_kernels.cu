@@ -212,7 +212,7 @@ chain_batch_kernel(const __grid_constant__ FastParams P, const __grid_constant__
     }
 
     // ---- lookup + event likelihood + tail of the chain this CTA owns ---------------------------
-    if (mine >= 0) batch_lookup_tail(S, Q, mine, mode, tnb, tid);
+    if (mine >= 0) batch_lookup_tail(S, Q, mine, mode, tnb, tid, Q.rebin && s + 1 < total_super);
     BK_STAMP(4);
     if (Q.rebin && s + 1 < total_super) {      // proposals published, histograms cleared
       cta_arrive(bar);

@@ -700,6 +700,12 @@ struct sxmc_chain {
   unsigned* sync_host = nullptr;    // pinned readback of the above
   long long step_bytes = 0;         // algorithmic bytes one binning pass streams
   bool used_persistent = false;
+  // monotone one-chain path (batch_mono_kernels.cu with a batch of one)
+  MonoPlan* mono_plan = nullptr;
+  bool mono_checked = false;
+  unsigned* mult_dev = nullptr;     // events per bin (grouped lookup), when every signal reads one dataset
+  long long* nevents_dev = nullptr;
+  int last_path = 0;                // 1 graph/stream, 2 persistent, 4 monotone
   unsigned long long* stamps_dev = nullptr;   // persistent kernel phase stamps (profiling hook)
   std::vector<cudaEvent_t> tev;
 };
@@ -898,6 +904,8 @@ int sxmc_chain_destroy(sxmc_chain* c) {
   chain_drop_graph(c);
   cudaFree(c->flush_buf);
   cudaFree(c->bcast_dev); cudaFree(c->sync_dev); cudaFree(c->stamps_dev);
+  cudaFree(c->mult_dev); cudaFree(c->nevents_dev);
+  delete c->mono_plan;
   if (c->sync_host) cudaFreeHost(c->sync_host);
   for (auto& e : c->tev) cudaEventDestroy(e);
   cudaFree(c->st_dev);
@@ -956,6 +964,19 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
   c->lut_dev = nullptr;
   SXMC_CUDA(cudaMalloc(&c->lut_dev, sizeof(float) * std::max<size_t>(1, c->nevents * c->nsignals)));
   SXMC_TRY(chain_build_tables(c));
+  // grouped lookup of the monotone path: events per bin, when all signals read one dataset
+  bool shared = true;
+  for (int j = 1; j < c->nsignals; ++j) shared = shared && c->pdfs[j]->dataset == c->pdfs[0]->dataset;
+  cudaFree(c->mult_dev);
+  c->mult_dev = nullptr;
+  if (shared && (size_t)c->nsignals * c->total_nbins <= (size_t)BATCH_PDF_TABLE) {
+    SXMC_CUDA(cudaMalloc(&c->mult_dev, sizeof(unsigned) * (size_t)c->total_nbins));
+    SXMC_TRY(launch_event_mult(c->pdfs[0]->read_bins_dev, (long long)c->nevents, c->total_nbins, c->mult_dev, c->stream));
+  }
+  if (!c->nevents_dev) SXMC_CUDA(cudaMalloc(&c->nevents_dev, sizeof(long long)));
+  const long long ne = (long long)c->nevents;
+  SXMC_CUDA(cudaMemcpyAsync(c->nevents_dev, &ne, sizeof ne, cudaMemcpyHostToDevice, c->stream));
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
   c->have_data = true;
   return SXMC_OK;
 }
@@ -1091,6 +1112,58 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
   const BinLaunch& BL = c->batch[0].launch;
   const bool persistent_ok = BL.fast && BL.njobs <= FAST_MAX_JOBS && !has_comm && c->nsignals <= 128 &&
                              c->pdfs.size() && nsteps > 0;
+  // Monotone fits (one observable, shift / scale / ctscale only): the edge-search kernel of
+  // batch_mono_kernels.cu with a batch of one chain.
+  if ((c->mode == 0 || c->mode == 4) && !has_comm && nsteps > 0 && c->pdfs.size()) {
+    if (!c->mono_checked) {
+      c->mono_checked = true;
+      bool mono = BL.fast && BL.nobs == 1 && BL.nslots == 1;
+      for (int j = 0; j < c->nsignals && mono; ++j) {
+        sxmc_hist* h = c->pdfs[j];
+        if (!h->sort || !h->prepared || h->primary != 0) mono = false;
+        for (const SystDesc& d : h->systs)
+          if (d.type == SXMC_SYST_RESOLUTION_SCALE || d.obs != 0 || d.npars > 1) mono = false;
+        bool bad = false;
+        if (mono) SXMC_TRY(column_has_nan_or_neginf(h->cols_dev, h->col_pitch, &bad, c->stream));
+        if (bad) mono = false;
+      }
+      if (mono) {
+        std::vector<unsigned long long> nsamp(c->nsignals);
+        for (int j = 0; j < c->nsignals; ++j) nsamp[j] = c->pdfs[j]->nsamples;
+        c->mono_plan = new MonoPlan;
+        if (plan_chain_batch_mono(BL, nsamp.data(), 1, c->mono_plan) != SXMC_OK) { delete c->mono_plan; c->mono_plan = nullptr; }
+      }
+    }
+    if (c->mono_plan && !g_no_mono) {
+      BatchParams Q;
+      memset(&Q, 0, sizeof Q);
+      Q.st = c->st_dev; Q.sigs = c->sigs_dev[0]; Q.hist = c->hist_buf[0]; Q.hist_words = c->hist_words;
+      Q.nevents = c->nevents_dev; Q.sync = c->sync_dev;
+      Q.nchains = 1; Q.ns = c->nsignals; Q.np = c->nparameters; Q.nsources = c->nsources;
+      Q.nsteps = nsteps; Q.do_init = 0; Q.rebin = rebin ? 1 : 0; Q.mult = c->mult_dev; Q.mono = 1;
+      if (rebin) SXMC_CUDA(cudaMemsetAsync(c->hist_buf[0], 0, sizeof(unsigned) * c->hist_words, c->stream));
+      else if (c->last_buf != 0) {   // fixed systematics: the lookups read the initial evaluation
+        SXMC_CUDA(cudaMemcpyAsync(c->hist_buf[0], c->hist_buf[c->last_buf], sizeof(unsigned) * c->hist_words,
+                                  cudaMemcpyDeviceToDevice, c->stream));
+      }
+      SXMC_CUDA(cudaMemsetAsync(c->sync_dev, 0, sizeof(unsigned) * 4, c->stream));
+      SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
+      SXMC_TRY(launch_chain_batch_mono(*c->mono_plan, Q, c->stream));
+      SXMC_CUDA(cudaEventRecord(c->ev1, c->stream));
+      SXMC_CUDA(cudaMemcpyAsync(c->sync_host, c->sync_dev, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost, c->stream));
+      SXMC_CUDA(cudaStreamSynchronize(c->stream));
+      if (c->sync_host[3]) { set_error("monotone chain kernel timed out at a grid barrier"); return SXMC_ESTATE; }
+      float ms = 0;
+      SXMC_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+      c->loop_ms += ms;
+      c->launches += 1;
+      c->steps_done += nsteps;
+      c->last_buf = 0;
+      c->last_path = 4;
+      return SXMC_OK;
+    }
+    if (c->mode == 4) { set_error("sxmc_chain_set_mode(4): the fit is not monotone (or does not fit on chip)"); return SXMC_ESTATE; }
+  }
   const bool want_persistent = c->mode == 2 || (c->mode == 0 && c->step_bytes <= g_persistent_max_bytes);
   if (persistent_ok && want_persistent) {
     PersistParams Q;
@@ -1124,6 +1197,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
       c->steps_done += nsteps;
       if (rebin && c->steps_done > 0) c->last_buf = (int)(c->steps_done & 1);
       c->used_persistent = true;
+      c->last_path = 2;
       return SXMC_OK;
     }
     if (c->mode == 2) return rc;     // explicitly requested: report why it cannot run
@@ -1169,6 +1243,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
   float ms = 0;
   SXMC_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
   c->loop_ms += ms;
+  c->last_path = 1;
   return SXMC_OK;
 }
 
@@ -1255,6 +1330,7 @@ int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows) {
 int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out) { *accepted_out = (long)c->accepted; return SXMC_OK; }
 int sxmc_chain_loop_ms(sxmc_chain* c, float* ms_out) { *ms_out = c->loop_ms; return SXMC_OK; }
 int sxmc_chain_launches(sxmc_chain* c, long* launches_out) { *launches_out = c->launches; return SXMC_OK; }
+int sxmc_chain_last_path(sxmc_chain* c, int* path_out) { *path_out = c->last_path; return SXMC_OK; }
 
 int sxmc_chain_read_trace(sxmc_chain* c, double* nll_trace_out, double* proposed_out, unsigned nsteps) {
   if (!c->nll_trace_dev || nsteps > c->trace_steps) { set_error("trace was not enabled for that many steps"); return SXMC_ESTATE; }

@@ -213,6 +213,12 @@ class MCMC:
         _check(lib().sxmc_chain_launches(self._c, C.byref(v)))
         return v.value
 
+    def last_path(self):
+        """1 graph / stream launches, 2 persistent kernel, 4 monotone edge-search kernel"""
+        v = C.c_int(0)
+        _check(lib().sxmc_chain_last_path(self._c, C.byref(v)))
+        return v.value
+
     def read_trace(self, nsteps):
         nll = np.zeros(max(1, nsteps), dtype=np.float64)
         prop = np.zeros((max(1, nsteps), self.nparameters), dtype=np.float64)

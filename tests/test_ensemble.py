@@ -300,6 +300,7 @@ def test_batch_philox_chain_equals_single_chain_and_full_width_batch():
         batch.set_data(k, fit.data[(k % 7)::7])
     batch.run(148, nsteps, 0.1)
     h2, chain = mcmc.build_fit(fit)
+    chain.set_mode(2)            # the persistent one-chain kernel: a different binning path
     for k in (0, 1, 73, 147):
         chain.set_seed(77, k)
         want = chain(fit.data[(k % 7)::7], nsteps, 0.1).get_samples()

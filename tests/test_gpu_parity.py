@@ -259,7 +259,7 @@ def test_empty_and_ragged_inputs():
 # ---------------------------------------------------------------------------------------
 # chains
 # ---------------------------------------------------------------------------------------
-@pytest.mark.parametrize("mode", [0, 1, 2, 3], ids=["auto", "stream", "persistent", "graph"])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4], ids=["auto", "stream", "persistent", "graph", "monotone"])
 def test_tape_driven_chain_matches_oracle_chain(mode):
     """Same random numbers in => same accept/reject sequence and the same float rows out."""
     from sxmc_b200 import mcmc
@@ -275,6 +275,7 @@ def test_tape_driven_chain_matches_oracle_chain(mode):
     chain.enable_trace()
     ls = chain(fit.data, nsteps, 0.1)
     got = ls.get_samples()
+    assert chain.last_path() == {0: 4, 1: 1, 2: 2, 3: 1, 4: 4}[mode]
     nll_tr, prop_tr = chain.read_trace(nsteps)
     assert got.shape == want["chain"].shape
     assert chain.accepted() == want["accepted"]
