@@ -487,6 +487,20 @@ def main():
         except Exception as e:
             line["ensemble_E"] = {"error": repr(e)}
 
+    # extra: the reference's own published benchmark (bench/bench_sxmc.cpp:34-102)
+    if world == 1 and not args.no_extra and args.workload == "B" and args.scale == 1.0:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_pdfz
+            bp = bench_pdfz.run("bench_pdfz", 50)
+            line["bench_pdfz"] = {"samples_per_s": bp["samples_per_s_batched_call"], "reps": 50,
+                                  "what": "10M samples, 1-D, 1000 bins, 100k eval points: reps x (EvalAsync + "
+                                          "EvalFinished) wall clock, the reference's metric",
+                                  "published_best": bp["published_best"],
+                                  "vs_published_best": bp["vs_published_best"]}
+        except Exception as e:
+            line["bench_pdfz"] = {"error": repr(e)}
+
     line["clocks"] = sampler.summary()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         rate, kind, n, what = cpu_steps_per_s(fit, args.cpu_budget_s)

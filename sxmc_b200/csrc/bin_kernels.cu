@@ -255,6 +255,21 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
   return SXMC_OK;
 }
 
+// zero_hist (src/pdfz.cpp:334-346) for every job of a batch in one launch: block j clears
+// jobs[j].bins and jobs[j].norm
+__global__ void zero_jobs_kernel(const BinJob* __restrict__ jobs) {
+  const BinJob& job = jobs[blockIdx.x];
+  for (int b = threadIdx.x; b < job.total_nbins; b += blockDim.x) job.bins[b] = 0u;
+  if (threadIdx.x == 0) *job.norm = 0u;
+}
+
+int launch_zero_jobs(const BinJob* jobs_dev, int njobs, cudaStream_t stream) {
+  if (njobs <= 0) return SXMC_OK;
+  zero_jobs_kernel<<<njobs, 256, 0, stream>>>(jobs_dev);
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
 // =========================================================================================
 // layout preparation: sort key, gather into the tiled SoA layout
 // =========================================================================================

@@ -537,9 +537,6 @@ static int hists_eval_on(sxmc_hist* const* hs, int n, int do_eval_pdf, cudaStrea
     if (!h->systs.empty() && !h->param_dev) { set_error("EvalAsync: no parameter buffer bound"); return SXMC_ESTATE; }
     SXMC_TRY(fill_job(h, b.host[j], h->bins_dev, h->norm_dev + h->norm_offset,
                       h->param_dev ? h->param_dev + h->param_offset : nullptr, h->param_stride));
-    // zero_hist (src/pdfz.cpp:334-346)
-    SXMC_CUDA(cudaMemsetAsync(h->bins_dev, 0, sizeof(unsigned) * (size_t)h->total_nbins, stream));
-    SXMC_CUDA(cudaMemsetAsync(h->norm_dev + h->norm_offset, 0, sizeof(unsigned), stream));
     if (do_eval_pdf && h->read_bins_dev && h->npoints > 0) {   // :474 guard
       if (!h->pdf_dev) { set_error("EvalAsync: no PDF value buffer bound"); return SXMC_ESTATE; }
       EvalPdfJob& e = b.ep_host[b.n_ep++];
@@ -556,6 +553,7 @@ static int hists_eval_on(sxmc_hist* const* hs, int n, int do_eval_pdf, cudaStrea
   }
   plan_launch(b, n);
   SXMC_TRY(upload_batch(b, n, stream));
+  SXMC_TRY(launch_zero_jobs(b.dev, n, stream));   // zero_hist (src/pdfz.cpp:334-346), all PDFs at once
   SXMC_TRY(launch_bin(b.launch, stream));
   SXMC_TRY(launch_eval_pdf(b.ep_dev, b.n_ep, b.max_points, stream));
   return SXMC_OK;

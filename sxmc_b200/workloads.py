@@ -234,5 +234,27 @@ def bench_pdfz_shape(scale=1.0):
                    data=data, nsteps=100)
 
 
+PDFZ_GROUP_NSAMPLES = [1e3, 2e5, 1e4, 1e3, 1e3, 3e6, 5e5, 1e6, 8e4, 2e4] + [1e3] * 19
+
+
+def pdfz_group_shape(scale=1.0):
+    """The reference's second benchmark (bench/bench_sxmc.cpp:105-225): 29 PDFs of very
+    different sizes (10^3 ... 3x10^6 N(0,1) samples), 1-D, 1000 bins on [-3,3), one shift
+    systematic at 0, 100k clamped-Gaussian eval points, all evaluated together."""
+    rng = np.random.default_rng(434343)
+    signals = []
+    for j, n in enumerate(PDFZ_GROUP_NSAMPLES):
+        n = max(1, int(n * scale))
+        rows = np.stack([rng.normal(0, 1, n), np.zeros(n)], axis=1).astype(np.float32)
+        signals.append(SignalSpec(samples=rows, nexpected=1000.0, source=j))
+    ev = np.clip(rng.normal(0, 1, max(1, int(100_000 * min(1.0, scale * 10)))), -2.999, 2.999)
+    data = np.stack([ev, np.zeros_like(ev)], axis=1).astype(np.float32)
+    ns = len(signals)
+    return FitSpec(name="pdfz_group", lower=[-3.0], upper=[3.0], nbins=[1000],
+                   source_means=[1.0] * ns, source_sigmas=[0.0] * ns, source_fixed=[False] * ns,
+                   systematics=[SystSpec(type=SHIFT, obs=0, means=[0.0], sigmas=[0.01])],
+                   signals=signals, data=data, nsteps=100)
+
+
 WORKLOADS = {"A": config_A, "B": config_B, "C": config_C, "D": config_D,
-             "bench_pdfz": bench_pdfz_shape}
+             "bench_pdfz": bench_pdfz_shape, "pdfz_group": pdfz_group_shape}
