@@ -70,6 +70,9 @@ def parse_args():
                     help="CPU seconds the cpu_baseline / reference arm may spend stepping")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra workload-C / ensemble objects")
+    ap.add_argument("--shard-samples", action="store_true",
+                    help="N>1: ONE chain whose Monte-Carlo samples are cut over the GPUs, histograms "
+                         "summed with NCCL every step (strong scaling; BASELINE.json configs[3])")
     ap.add_argument("--experiments", type=int, default=296,
                     help="workload E: fake experiments per GPU (whole batches of 148)")
     ap.add_argument("--esteps", type=int, default=20000, help="workload E: MCMC steps per experiment")
@@ -251,12 +254,22 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     from sxmc_b200 import mcmc
     K, Wm = args.steps, args.warmup
     t_build0 = time.perf_counter()
-    hists, chain = mcmc.build_fit(fit)
+    comm = None
+    if getattr(args, "shard_samples", False) and torch.distributed.is_initialized():
+        from sxmc_b200 import sharding
+        world = torch.distributed.get_world_size()
+        fit_local = sharding.shard_fit_samples(fit, rank, world)
+        comm = sharding.Comm(device=local)
+        hists, chain = mcmc.build_fit(fit_local)
+        chain.set_comm(comm.handle)
+    else:
+        hists, chain = mcmc.build_fit(fit)
     for h in hists:
         h.Prepare()                      # sorted, tiled SoA layout (first-call Optimize analogue)
     torch.cuda.synchronize()
     build_s = time.perf_counter() - t_build0
-    chain.set_seed(20261104, rank)       # independent chain per rank (ensemble sharding)
+    # independent chain per rank (ensemble sharding) / the same chain on every rank (sample sharding)
+    chain.set_seed(20261104, 0 if comm is not None else rank)
 
     out = {"build_s": build_s}
     total = 2 * Wm + 2 * K
@@ -274,6 +287,7 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     sampler.start()
     l0 = chain.launches()
     step_ms, bin_ms, nll_ms = chain.advance_timed(K, L2_FLUSH_BYTES)
+    out["comm_ms"] = chain.last_comm_ms()
     out["gpu_launches"] = chain.launches() - l0
     barrier()
     out.update(step_ms=step_ms, bin_ms=bin_ms, nll_ms=nll_ms)
@@ -305,6 +319,10 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     chain.close()
     for h in hists:
         h.close()
+    if comm is not None:
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        comm.close()
     return out
 
 
@@ -399,14 +417,16 @@ def run_own_arm(args, rank, world, local):
     step_ms = allreduce_max(r["step_ms"])
     warm_ms = allreduce_max(r["warm_ms"])
     e2e_s = allreduce_max(r["e2e_s"])
-    value = world * K / (step_ms * 1e-3)
-    alg_bytes = algorithmic_bytes_per_step(fit)
+    sharded = args.shard_samples and world > 1
+    nchains = 1 if sharded else world
+    value = nchains * K / (step_ms * 1e-3)
+    alg_bytes = algorithmic_bytes_per_step(fit) // (world if sharded else 1)
     bin_avg_ms = r["bin_ms"] / K
     achieved = alg_bytes / (bin_avg_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": step_ms / K, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (seeded numpy, SURVEY 8 distributions)",
         "config": {"workload": WORKLOAD_TEXT[args.workload], "scale": args.scale,
                    "mc_samples_per_step": fit.total_samples(), "nevents": fit.nevents,
@@ -414,9 +434,12 @@ def run_own_arm(args, rank, world, local):
                    "l2": "flushed before every timed step (256 MiB memset outside the event "
                          "interval); the working set (%.1f MB) would otherwise be L2-resident"
                          % (alg_bytes / 1e6),
-                   "parallelism": "1 independent chain per GPU (ensemble sharding), no collective"},
+                   "parallelism": ("sample sharding: each GPU bins 1/%d of every signal's samples, uint32 "
+                                   "histograms summed with ncclAllReduce every step, one chain" % world)
+                   if sharded else "1 independent chain per GPU (ensemble sharding), no collective"},
         "samples_binned_per_s": value * fit.total_samples(),
-        "e2e": {"value": world * K / e2e_s, "unit": UNIT,
+        "allreduce_ms_per_step": r["comm_ms"] / K,
+        "e2e": {"value": nchains * K / e2e_s, "unit": UNIT,
                 "h2d_bytes_per_step": r["e2e_h2d"], "d2h_bytes_per_step": r["e2e_d2h"],
                 "what": "MCMC.__call__(host data, K steps, burn-in 0.1) -> host chain rows: "
                         "sxmc_chain_run + sxmc_chain_read"},
@@ -429,7 +452,7 @@ def run_own_arm(args, rank, world, local):
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "avg_launch_ms": bin_avg_ms, "share_of_step": r["bin_ms"] / r["step_ms"]},
         "kernels_ms_per_step": {"bin": bin_avg_ms, "lookup_nll_metropolis": r["nll_ms"] / K},
-        "chain_back_to_back": {"value": world * K / (warm_ms * 1e-3), "unit": UNIT,
+        "chain_back_to_back": {"value": nchains * K / (warm_ms * 1e-3), "unit": UNIT,
                                "ms_per_step": warm_ms / K,
                                "note": "production form: chain.advance(K), steps back to back (monotone / persistent kernel for small fits, CUDA graph otherwise)"},
         "accept_rate": r["accepted"] / float(2 * K + 2 * args.warmup),

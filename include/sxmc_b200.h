@@ -181,6 +181,9 @@ int sxmc_chain_end(sxmc_chain* c, long* nrows_out);
  * the timed intervals.  Outputs are sums over the nsteps steps, in ms. */
 int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
                              float* step_ms_sum, float* bin_ms_sum, float* nll_ms_sum);
+/* the part of bin_ms_sum of the last sxmc_chain_advance_timed spent between the end of the
+ * binning kernel and the end of the histogram all-reduce (sample-sharded chains; else ~0) */
+int sxmc_chain_last_comm_ms(sxmc_chain* c, float* ms_out);
 /* the ntuple rows: nparameters+1 floats each (src/nll_kernels.cpp:78-84) */
 int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows);
 int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out);

@@ -704,6 +704,7 @@ struct sxmc_chain {
   unsigned* mult_dev = nullptr;     // events per bin (grouped lookup), when every signal reads one dataset
   long long* nevents_dev = nullptr;
   int last_path = 0;                // 1 graph/stream, 2 persistent, 4 monotone
+  float last_comm_ms = 0;           // all-reduce time inside the last advance_timed (sum over its steps)
   unsigned long long* stamps_dev = nullptr;   // persistent kernel phase stamps (profiling hook)
   std::vector<cudaEvent_t> tev;
 };
@@ -748,9 +749,10 @@ static int chain_build_tables(sxmc_chain* c) {
   return SXMC_OK;
 }
 
-static int chain_bin(sxmc_chain* c, int b) {
+static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr) {
   SXMC_TRY(launch_bin(c->batch[b].launch, c->stream));
   c->launches += 1;
+  if (after_bin) SXMC_CUDA(cudaEventRecord(after_bin, c->stream));
   if (c->comm && c->comm->nranks > 1) {
     int rc = g_nccl.AllReduce(c->hist_buf[b], c->hist_buf[b], c->hist_words, NCCL_UINT32, NCCL_SUM,
                               c->comm->comm, c->stream);
@@ -1265,10 +1267,10 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
   }
   const unsigned CHUNK = 64;
   if (c->tev.empty()) {
-    c->tev.resize(3 * CHUNK);
+    c->tev.resize(4 * CHUNK);
     for (auto& e : c->tev) SXMC_CUDA(cudaEventCreate(&e));
   }
-  double t_step = 0, t_bin = 0, t_nll = 0;
+  double t_step = 0, t_bin = 0, t_nll = 0, t_comm = 0;
   unsigned left = nsteps;
   while (left > 0) {
     const unsigned n = std::min(left, CHUNK);
@@ -1277,7 +1279,8 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
       const int b = rebin ? (int)((i + 1) & 1) : 0;
       if (flush_bytes) SXMC_CUDA(cudaMemsetAsync(c->flush_buf, (int)(i & 0xff), flush_bytes, c->stream));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k], c->stream));
-      if (rebin) SXMC_TRY(chain_bin(c, b));
+      if (rebin) SXMC_TRY(chain_bin(c, b, c->tev[3 * CHUNK + k]));
+      else SXMC_CUDA(cudaEventRecord(c->tev[3 * CHUNK + k], c->stream));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 1], c->stream));
       SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 2], c->stream));
@@ -1289,6 +1292,9 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
       SXMC_CUDA(cudaEventElapsedTime(&a, c->tev[3 * k], c->tev[3 * k + 1]));
       SXMC_CUDA(cudaEventElapsedTime(&b2, c->tev[3 * k + 1], c->tev[3 * k + 2]));
       t_bin += a; t_nll += b2; t_step += a + b2;
+      float cm = 0;     // binning kernel end -> all-reduce end (0 without a communicator)
+      SXMC_CUDA(cudaEventElapsedTime(&cm, c->tev[3 * CHUNK + k], c->tev[3 * k + 1]));
+      t_comm += cm;
     }
     left -= n;
   }
@@ -1297,6 +1303,7 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
   if (step_ms_sum) *step_ms_sum = (float)t_step;
   if (bin_ms_sum) *bin_ms_sum = (float)t_bin;
   if (nll_ms_sum) *nll_ms_sum = (float)t_nll;
+  c->last_comm_ms = (float)t_comm;
   return SXMC_OK;
 }
 
@@ -1329,6 +1336,7 @@ int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out) { *accepted_out = (lo
 int sxmc_chain_loop_ms(sxmc_chain* c, float* ms_out) { *ms_out = c->loop_ms; return SXMC_OK; }
 int sxmc_chain_launches(sxmc_chain* c, long* launches_out) { *launches_out = c->launches; return SXMC_OK; }
 int sxmc_chain_last_path(sxmc_chain* c, int* path_out) { *path_out = c->last_path; return SXMC_OK; }
+int sxmc_chain_last_comm_ms(sxmc_chain* c, float* ms_out) { *ms_out = c->last_comm_ms; return SXMC_OK; }
 
 int sxmc_chain_read_trace(sxmc_chain* c, double* nll_trace_out, double* proposed_out, unsigned nsteps) {
   if (!c->nll_trace_dev || nsteps > c->trace_steps) { set_error("trace was not enabled for that many steps"); return SXMC_ESTATE; }

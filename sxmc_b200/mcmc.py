@@ -213,6 +213,11 @@ class MCMC:
         _check(lib().sxmc_chain_launches(self._c, C.byref(v)))
         return v.value
 
+    def last_comm_ms(self):
+        v = C.c_float(0)
+        _check(lib().sxmc_chain_last_comm_ms(self._c, C.byref(v)))
+        return v.value
+
     def last_path(self):
         """1 graph / stream launches, 2 persistent kernel, 4 monotone edge-search kernel"""
         v = C.c_int(0)
