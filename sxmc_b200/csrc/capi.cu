@@ -702,6 +702,7 @@ struct sxmc_chain {
   MonoPlan* mono_plan = nullptr;
   bool mono_checked = false;
   unsigned* mult_dev = nullptr;     // events per bin (grouped lookup), when every signal reads one dataset
+  bool mult_fits_table = false;     // ... and the (signal, bin) table fits the batch kernels' shared memory
   long long* nevents_dev = nullptr;
   int last_path = 0;                // 1 graph/stream, 2 persistent, 4 monotone
   float last_comm_ms = 0;           // all-reduce time inside the last advance_timed (sum over its steps)
@@ -778,6 +779,8 @@ static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut
   L.zero_ptr = zero_other ? c->hist_buf[1 - b] : nullptr;
   L.zero_words = zero_other ? c->hist_words : 0;
   L.grid = c->nll_grid;
+  L.mult = c->mult_dev;
+  L.mult_nbins = c->total_nbins;
   SXMC_TRY(launch_nll(L, c->stream));
   c->launches += 1;
   return SXMC_OK;
@@ -969,7 +972,8 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
   for (int j = 1; j < c->nsignals; ++j) shared = shared && c->pdfs[j]->dataset == c->pdfs[0]->dataset;
   cudaFree(c->mult_dev);
   c->mult_dev = nullptr;
-  if (shared && (size_t)c->nsignals * c->total_nbins <= (size_t)BATCH_PDF_TABLE) {
+  c->mult_fits_table = (size_t)c->nsignals * c->total_nbins <= (size_t)BATCH_PDF_TABLE;
+  if (shared) {
     SXMC_CUDA(cudaMalloc(&c->mult_dev, sizeof(unsigned) * (size_t)c->total_nbins));
     SXMC_TRY(launch_event_mult(c->pdfs[0]->read_bins_dev, (long long)c->nevents, c->total_nbins, c->mult_dev, c->stream));
   }
@@ -1140,7 +1144,8 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
       Q.st = c->st_dev; Q.sigs = c->sigs_dev[0]; Q.hist = c->hist_buf[0]; Q.hist_words = c->hist_words;
       Q.nevents = c->nevents_dev; Q.sync = c->sync_dev;
       Q.nchains = 1; Q.ns = c->nsignals; Q.np = c->nparameters; Q.nsources = c->nsources;
-      Q.nsteps = nsteps; Q.do_init = 0; Q.rebin = rebin ? 1 : 0; Q.mult = c->mult_dev; Q.mono = 1;
+      Q.nsteps = nsteps; Q.do_init = 0; Q.rebin = rebin ? 1 : 0;
+      Q.mult = c->mult_fits_table ? c->mult_dev : nullptr; Q.mono = 1;
       if (rebin) SXMC_CUDA(cudaMemsetAsync(c->hist_buf[0], 0, sizeof(unsigned) * c->hist_words, c->stream));
       else if (c->last_buf != 0) {   // fixed systematics: the lookups read the initial evaluation
         SXMC_CUDA(cudaMemcpyAsync(c->hist_buf[0], c->hist_buf[c->last_buf], sizeof(unsigned) * c->hist_words,

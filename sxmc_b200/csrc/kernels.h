@@ -78,6 +78,8 @@ struct NllLaunch {
   unsigned* zero_ptr;           // optional buffer to clear for the next step
   unsigned long long zero_words;
   int grid;                     // fixed for the life of a chain (deterministic summation order)
+  const unsigned* mult;         // optional events per bin [mult_nbins]: grouped lookup (all signals one dataset)
+  int mult_nbins;
 };
 int nll_grid_for(long long nevents);
 int launch_nll(const NllLaunch& L, cudaStream_t stream);

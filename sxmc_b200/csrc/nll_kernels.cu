@@ -18,7 +18,7 @@ __global__ void __launch_bounds__(NLL_THREADS)
 lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict__ norms, int ns,
                   int np, int nsources, long long ne, ChainState* st, double* partials,
                   unsigned* ticket, int mode, float* lut, unsigned* zero_ptr,
-                  unsigned long long zero_words) {
+                  unsigned long long zero_words, const unsigned* __restrict__ mult, int mult_nbins) {
   __shared__ double s_c[NLL_MAX_SIGNALS];
   __shared__ double s_bn[NLL_MAX_SIGNALS];
   __shared__ const unsigned* s_bins[NLL_MAX_SIGNALS];
@@ -68,6 +68,23 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   __syncthreads();
 
   double sum = 0;
+  if (mult && !lut) {
+    // Grouped lookup: every signal reads the same dataset, so the events of one bin share a
+    // likelihood and sum_i log(s_i) = sum_b m_b log(s_b), m_b = events in bin b (counted once when
+    // the data were set).  One division per (signal, occupied bin) instead of one per
+    // (signal, event); no gather.
+    for (long long b = gtid; b < mult_nbins; b += gstride) {
+      const unsigned m = mult[b];
+      if (!m) continue;
+      double s = 0;
+      for (int j = 0; j < ns; ++j) {
+        float v = (float)((double)s_bins[j][b] / s_bn[j]);            // pdfz.cpp:429-432
+        if (isnan(v)) v = 0.0f;                                       // nll_kernels.cpp:107
+        s = __dadd_rn(s, __dmul_rn(s_c[j], (double)v));
+      }
+      if (s > 0) sum += (double)m * log(s);
+    }
+  } else
   for (long long i = gtid; i < ne; i += gstride) {
     double s = 0;
     for (int j = 0; j < ns; ++j) {
@@ -123,7 +140,7 @@ int launch_nll(const NllLaunch& L, cudaStream_t stream) {
   lookup_nll_kernel<<<L.grid, NLL_THREADS, 0, stream>>>(L.sigs_dev, L.norms_dev, L.nsignals,
                                                         L.nparameters, L.nsources, L.nevents, L.state,
                                                         L.partials, L.ticket, L.mode, L.lut,
-                                                        L.zero_ptr, L.zero_words);
+                                                        L.zero_ptr, L.zero_words, L.mult, L.mult_nbins);
   SXMC_CUDA(cudaGetLastError());
   return SXMC_OK;
 }
