@@ -73,6 +73,9 @@ def parse_args():
     ap.add_argument("--shard-samples", action="store_true",
                     help="N>1: ONE chain whose Monte-Carlo samples are cut over the GPUs, histograms "
                          "summed with NCCL every step (strong scaling; BASELINE.json configs[3])")
+    ap.add_argument("--p2p", action="store_true",
+                    help="with --shard-samples: exchange the histograms with the peer-memory kernel "
+                         "(p2p_kernels.cu) instead of ncclAllReduce")
     ap.add_argument("--experiments", type=int, default=296,
                     help="workload E: fake experiments per GPU (whole batches of 148)")
     ap.add_argument("--esteps", type=int, default=20000, help="workload E: MCMC steps per experiment")
@@ -259,9 +262,13 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
         from sxmc_b200 import sharding
         world = torch.distributed.get_world_size()
         fit_local = sharding.shard_fit_samples(fit, rank, world)
-        comm = sharding.Comm(device=local)
         hists, chain = mcmc.build_fit(fit_local)
-        chain.set_comm(comm.handle)
+        if getattr(args, "p2p", False):
+            comm = "p2p"
+            sharding.connect_p2p(chain, rank, world)
+        else:
+            comm = sharding.Comm(device=local)
+            chain.set_comm(comm.handle)
     else:
         hists, chain = mcmc.build_fit(fit)
     for h in hists:
@@ -322,7 +329,8 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     if comm is not None:
         torch.cuda.synchronize()
         torch.distributed.barrier()
-        comm.close()
+        if comm != "p2p":
+            comm.close()
     return out
 
 
@@ -435,7 +443,9 @@ def run_own_arm(args, rank, world, local):
                          "interval); the working set (%.1f MB) would otherwise be L2-resident"
                          % (alg_bytes / 1e6),
                    "parallelism": ("sample sharding: each GPU bins 1/%d of every signal's samples, uint32 "
-                                   "histograms summed with ncclAllReduce every step, one chain" % world)
+                                   "histograms summed with %s every step, one chain"
+                                   % (world, "one peer-memory kernel (NVLink P2P loads)" if args.p2p
+                                      else "ncclAllReduce"))
                    if sharded else "1 independent chain per GPU (ensemble sharding), no collective"},
         "samples_binned_per_s": value * fit.total_samples(),
         "allreduce_ms_per_step": r["comm_ms"] / K,

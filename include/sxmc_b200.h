@@ -299,6 +299,16 @@ int sxmc_comm_destroy(sxmc_comm* comm);
 /* in-place uint32 sum over ranks of a device array (used by tests and by the chain) */
 int sxmc_comm_allreduce_u32(sxmc_comm* comm, unsigned* dev, size_t count);
 
+/* Sample sharding over NVLink peer memory instead of NCCL: each rank exports a window holding
+ * its partial histograms (a 64-byte cudaIpcMemHandle_t), the ranks exchange the handles by any
+ * means and connect; from then on the per-step exchange is ONE kernel that publishes a flag to
+ * every peer, waits for theirs and sums the N partials with 128-bit peer loads
+ * (p2p_kernels.cu).  All ranks must issue the same sequence of evaluations.  One box, <= 8 ranks. */
+int sxmc_chain_p2p_export(sxmc_chain* c, void* handle64_out);
+int sxmc_chain_p2p_connect(sxmc_chain* c, const void* handles, int nranks, int rank);
+/* exchanges completed so far; aborted != 0 after a peer failed to show up within ~2 s */
+int sxmc_chain_p2p_status(sxmc_chain* c, unsigned* exchanges_out, int* aborted_out);
+
 #ifdef __cplusplus
 }
 #endif

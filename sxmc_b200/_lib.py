@@ -127,6 +127,9 @@ SYMBOLS = {
     "sxmc_batch_loop_ms": (C.c_int, [c_vp, c_fp]),
     "sxmc_batch_last_path": (C.c_int, [c_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "sxmc_batch_phase_stamps": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_uint64)]),
+    "sxmc_chain_p2p_export": (C.c_int, [c_vp, c_vp]),
+    "sxmc_chain_p2p_connect": (C.c_int, [c_vp, c_vp, C.c_int, C.c_int]),
+    "sxmc_chain_p2p_status": (C.c_int, [c_vp, C.POINTER(C.c_uint), C.POINTER(C.c_int)]),
     "sxmc_comm_unique_id": (C.c_int, [c_vp]),
     "sxmc_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "sxmc_comm_destroy": (C.c_int, [c_vp]),

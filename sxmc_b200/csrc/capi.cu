@@ -667,7 +667,16 @@ struct sxmc_chain {
   cudaStream_t stream = nullptr;
   ChainState* st_dev = nullptr;
   ChainState* st_host = nullptr;      // pinned
-  unsigned* hist_buf[2] = {nullptr, nullptr};   // [ns*total_nbins bins][ns norms]
+  unsigned* hist_buf[2] = {nullptr, nullptr};   // [ns*total_nbins bins][ns norms]: what the lookup reads
+  unsigned* part_buf[2] = {nullptr, nullptr};   // what the binning kernel writes: == hist_buf, or this rank's
+                                                // partials inside its peer window (sample sharding over P2P)
+  // peer-memory all-reduce (p2p_kernels.cu)
+  unsigned* p2p_window = nullptr;               // [2][p2p_pitch] partials + [P2P_MAX_RANKS] flags, cudaIpc-exported
+  size_t p2p_pitch = 0;
+  void* p2p_peer[P2P_MAX_RANKS] = {nullptr};    // opened peer windows (own slot = p2p_window)
+  int p2p_nranks = 0, p2p_rank = 0;
+  unsigned* p2p_state = nullptr;                // [0] seq, [1] ticket, [2] abort
+  unsigned* p2p_state_host = nullptr;
   size_t hist_words = 0;
   Batch batch[2];
   NllSignal* sigs_dev[2] = {nullptr, nullptr};
@@ -723,10 +732,12 @@ static int chain_build_tables(sxmc_chain* c) {
     SXMC_TRY(c->batch[b].reserve(ns));
     unsigned* bins = c->hist_buf[b];
     unsigned* norms = c->hist_buf[b] + (size_t)ns * c->total_nbins;
+    unsigned* pbins = c->part_buf[b];
+    unsigned* pnorms = c->part_buf[b] + (size_t)ns * c->total_nbins;
     std::vector<NllSignal> sg(ns);
     for (int j = 0; j < ns; ++j) {
       sxmc_hist* h = c->pdfs[j];
-      SXMC_TRY(fill_job(h, c->batch[b].host[j], bins + (size_t)j * c->total_nbins, norms + j,
+      SXMC_TRY(fill_job(h, c->batch[b].host[j], pbins + (size_t)j * c->total_nbins, pnorms + j,
                         c->st_dev->proposed + c->nsources, 1));
       sg[j].bins = bins + (size_t)j * c->total_nbins;
       sg[j].norm = norms + j;
@@ -754,7 +765,20 @@ static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr) {
   SXMC_TRY(launch_bin(c->batch[b].launch, c->stream));
   c->launches += 1;
   if (after_bin) SXMC_CUDA(cudaEventRecord(after_bin, c->stream));
-  if (c->comm && c->comm->nranks > 1) {
+  if (c->p2p_nranks > 1) {
+    P2PParams W;
+    memset(&W, 0, sizeof W);
+    for (int p = 0; p < c->p2p_nranks; ++p) {
+      W.part[p] = (const unsigned*)c->p2p_peer[p];
+      W.flags[p] = (unsigned*)c->p2p_peer[p] + 2 * c->p2p_pitch;
+    }
+    W.sum = c->hist_buf[b];
+    W.seq = c->p2p_state; W.ticket = c->p2p_state + 1; W.abort_flag = c->p2p_state + 2;
+    W.words = c->hist_words; W.pitch = c->p2p_pitch; W.parity = b;
+    W.nranks = c->p2p_nranks; W.rank = c->p2p_rank;
+    SXMC_TRY(launch_hist_allreduce_p2p(W, c->stream));
+    c->launches += 1;
+  } else if (c->comm && c->comm->nranks > 1) {
     int rc = g_nccl.AllReduce(c->hist_buf[b], c->hist_buf[b], c->hist_words, NCCL_UINT32, NCCL_SUM,
                               c->comm->comm, c->stream);
     if (rc) return nccl_fail(rc, "ncclAllReduce");
@@ -776,7 +800,7 @@ static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut
   L.ticket = c->ticket;
   L.mode = mode;
   L.lut = lut;
-  L.zero_ptr = zero_other ? c->hist_buf[1 - b] : nullptr;
+  L.zero_ptr = zero_other ? c->part_buf[1 - b] : nullptr;
   L.zero_words = zero_other ? c->hist_words : 0;
   L.grid = c->nll_grid;
   L.mult = c->mult_dev;
@@ -886,6 +910,7 @@ int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out) {
   if (e == cudaSuccess) e = cudaMallocHost(&c->st_host, sizeof(ChainState));
   for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
     e = cudaMalloc(&c->hist_buf[b], sizeof(unsigned) * c->hist_words);
+    c->part_buf[b] = c->hist_buf[b];
     if (e == cudaSuccess) e = cudaMalloc(&c->sigs_dev[b], sizeof(NllSignal) * c->nsignals);
   }
   if (e == cudaSuccess) e = cudaMalloc(&c->partials, sizeof(double) * 148 * 8);
@@ -908,6 +933,10 @@ int sxmc_chain_destroy(sxmc_chain* c) {
   cudaFree(c->flush_buf);
   cudaFree(c->bcast_dev); cudaFree(c->sync_dev); cudaFree(c->stamps_dev);
   cudaFree(c->mult_dev); cudaFree(c->nevents_dev);
+  for (int p = 0; p < c->p2p_nranks; ++p)
+    if (p != c->p2p_rank && c->p2p_peer[p]) cudaIpcCloseMemHandle(c->p2p_peer[p]);
+  cudaFree(c->p2p_window); cudaFree(c->p2p_state);
+  if (c->p2p_state_host) cudaFreeHost(c->p2p_state_host);
   delete c->mono_plan;
   if (c->sync_host) cudaFreeHost(c->sync_host);
   for (auto& e : c->tev) cudaEventDestroy(e);
@@ -1052,6 +1081,17 @@ static int chain_pull_state(sxmc_chain* c) {
   return SXMC_OK;
 }
 
+// after a synchronisation: did a peer fail to show up in a peer-memory exchange?
+static int chain_p2p_check(sxmc_chain* c) {
+  if (c->p2p_nranks <= 1) return SXMC_OK;
+  SXMC_CUDA(cudaMemcpy(c->p2p_state_host, c->p2p_state, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost));
+  if (c->p2p_state_host[2]) {
+    set_error("peer-memory histogram exchange timed out waiting for another rank");
+    return SXMC_ESTATE;
+  }
+  return SXMC_OK;
+}
+
 // one MCMC step enqueued on the chain's stream: [bin -> (allreduce)] -> lookup+nll+decide+propose
 static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b) {
   if (rebin) SXMC_TRY(chain_bin(c, b));
@@ -1090,13 +1130,16 @@ int sxmc_chain_begin(sxmc_chain* c, const float* data, size_t data_nfloats, unsi
   c->steps_planned = nsteps;
 
   // initial evaluation at the means (src/mcmc.cpp:233-252): always bins, whatever is fixed
-  SXMC_CUDA(cudaMemsetAsync(c->hist_buf[0], 0, sizeof(unsigned) * c->hist_words, c->stream));
-  SXMC_CUDA(cudaMemsetAsync(c->hist_buf[1], 0, sizeof(unsigned) * c->hist_words, c->stream));
+  for (int b = 0; b < 2; ++b) {
+    SXMC_CUDA(cudaMemsetAsync(c->hist_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
+    if (c->part_buf[b] != c->hist_buf[b])
+      SXMC_CUDA(cudaMemsetAsync(c->part_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
+  }
   SXMC_TRY(chain_bin(c, 0));
   SXMC_TRY(chain_nll(c, 0, NLL_MODE_INIT, false, nullptr));
   c->last_buf = 0;
   SXMC_CUDA(cudaStreamSynchronize(c->stream));
-  return SXMC_OK;
+  return chain_p2p_check(c);
 }
 
 // Advance the chain by nsteps (the body of the loop at src/mcmc.cpp:261-378), device-resident.
@@ -1107,7 +1150,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
     return SXMC_ESTATE;
   }
   const bool rebin = c->nsystematics > 0 && !c->systematics_fixed;   // src/mcmc.cpp:264
-  const bool has_comm = c->comm && c->comm->nranks > 1;
+  const bool has_comm = (c->comm && c->comm->nranks > 1) || c->p2p_nranks > 1;
   const unsigned GRAPH_STEPS = 16;   // even: the histogram double-buffer parity is preserved
   unsigned left = nsteps;
   // Small fits: the whole segment in one cooperative launch (chain_kernels.cu).  Chosen when a
@@ -1249,7 +1292,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
   SXMC_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
   c->loop_ms += ms;
   c->last_path = 1;
-  return SXMC_OK;
+  return chain_p2p_check(c);
 }
 
 // Same steps as sxmc_chain_advance, issued as plain stream launches with a CUDA event around
@@ -1309,7 +1352,7 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
   if (bin_ms_sum) *bin_ms_sum = (float)t_bin;
   if (nll_ms_sum) *nll_ms_sum = (float)t_nll;
   c->last_comm_ms = (float)t_comm;
-  return SXMC_OK;
+  return chain_p2p_check(c);
 }
 
 int sxmc_chain_end(sxmc_chain* c, long* nrows_out) {
@@ -1362,7 +1405,7 @@ int sxmc_chain_nll_at(sxmc_chain* c, const double* pars, int rebin, double* nll_
   const int b = c->last_buf;
   cudaEvent_t e0 = c->ev0, e1 = c->ev1;
   if (rebin) {
-    SXMC_CUDA(cudaMemsetAsync(c->hist_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
+    SXMC_CUDA(cudaMemsetAsync(c->part_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
     if (g_timing) SXMC_CUDA(cudaEventRecord(e0, c->stream));
     SXMC_TRY(chain_bin(c, b));
     if (g_timing) {
@@ -2043,6 +2086,62 @@ int sxmc_batch_phase_stamps(sxmc_batch* b, int enable, unsigned long long* out14
   if (out148x8 && b->stamps_dev)   // + 16 words of per-chain clock deltas of one warp (monotone kernel)
     SXMC_CUDA(cudaMemcpy(out148x8, b->stamps_dev, sizeof(unsigned long long) * (148 * 8 + 16), cudaMemcpyDeviceToHost));
   if (!enable && b->stamps_dev) { cudaFree(b->stamps_dev); b->stamps_dev = nullptr; }
+  return SXMC_OK;
+}
+
+}  // extern "C"
+
+
+// =========================================================================================
+// Sample sharding over NVLink peer memory: the chain's partial histograms live in a window the
+// other ranks open with CUDA IPC; the per-step exchange is hist_allreduce_p2p_kernel.
+// =========================================================================================
+extern "C" {
+
+int sxmc_chain_p2p_export(sxmc_chain* c, void* handle64_out) {
+  if (!c || !handle64_out) SXMC_INVAL("sxmc_chain_p2p_export: NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  if (!c->p2p_window) {
+    c->p2p_pitch = (c->hist_words + 31) & ~(size_t)31;           // 128-byte aligned parities
+    const size_t words = 2 * c->p2p_pitch + P2P_MAX_RANKS;
+    SXMC_CUDA(cudaMalloc(&c->p2p_window, sizeof(unsigned) * words));
+    SXMC_CUDA(cudaMemset(c->p2p_window, 0, sizeof(unsigned) * words));
+    SXMC_CUDA(cudaMalloc(&c->p2p_state, sizeof(unsigned) * 4));
+    SXMC_CUDA(cudaMemset(c->p2p_state, 0, sizeof(unsigned) * 4));
+    SXMC_CUDA(cudaMallocHost(&c->p2p_state_host, sizeof(unsigned) * 4));
+  }
+  cudaIpcMemHandle_t h;
+  SXMC_CUDA(cudaIpcGetMemHandle(&h, c->p2p_window));
+  memcpy(handle64_out, &h, 64);
+  return SXMC_OK;
+}
+
+int sxmc_chain_p2p_connect(sxmc_chain* c, const void* handles, int nranks, int rank) {
+  if (!c || !handles) SXMC_INVAL("sxmc_chain_p2p_connect: NULL argument");
+  if (nranks < 1 || nranks > P2P_MAX_RANKS || rank < 0 || rank >= nranks)
+    SXMC_INVAL("sxmc_chain_p2p_connect: 1..8 ranks of one box");
+  if (!c->p2p_window) { set_error("sxmc_chain_p2p_connect: call sxmc_chain_p2p_export first"); return SXMC_ESTATE; }
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  chain_drop_graph(c);
+  for (int p = 0; p < nranks; ++p) {
+    if (p == rank) { c->p2p_peer[p] = c->p2p_window; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + 64 * (size_t)p, 64);
+    SXMC_CUDA(cudaIpcOpenMemHandle(&c->p2p_peer[p], h, cudaIpcMemLazyEnablePeerAccess));
+  }
+  c->p2p_nranks = nranks;
+  c->p2p_rank = rank;
+  c->part_buf[0] = c->p2p_window;
+  c->part_buf[1] = c->p2p_window + c->p2p_pitch;
+  if (c->have_data) SXMC_TRY(chain_build_tables(c));
+  return SXMC_OK;
+}
+
+int sxmc_chain_p2p_status(sxmc_chain* c, unsigned* exchanges_out, int* aborted_out) {
+  if (!c || !c->p2p_state) { if (exchanges_out) *exchanges_out = 0; if (aborted_out) *aborted_out = 0; return SXMC_OK; }
+  SXMC_CUDA(cudaMemcpy(c->p2p_state_host, c->p2p_state, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost));
+  if (exchanges_out) *exchanges_out = c->p2p_state_host[0];
+  if (aborted_out) *aborted_out = (int)c->p2p_state_host[2];
   return SXMC_OK;
 }
 

@@ -161,6 +161,21 @@ struct MonoParams {
   int njobs;
 };
 
+// Arguments of the peer-memory histogram all-reduce (p2p_kernels.cu), by value.
+constexpr int P2P_MAX_RANKS = 8;
+struct P2PParams {
+  const unsigned* part[P2P_MAX_RANKS];   // every rank's partial-histogram window (own one included)
+  unsigned* flags[P2P_MAX_RANKS];        // every rank's flag array [P2P_MAX_RANKS]: flags[p][r] = last step rank r published to p
+  unsigned* sum;                         // this rank's complete histogram (private)
+  unsigned* seq;                         // this rank's step counter (private, advanced by the kernel)
+  unsigned* ticket;
+  unsigned* abort_flag;
+  unsigned long long words;              // histogram words
+  unsigned long long pitch;              // words between the two parities inside a window
+  int parity;
+  int nranks, rank;
+};
+
 // One signal as seen by the lookup + event-likelihood kernel.
 struct NllSignal {
   const unsigned* bins;       // histogram of this step

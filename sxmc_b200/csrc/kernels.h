@@ -111,6 +111,9 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
 int launch_chain_batch_mono(const MonoPlan& plan, const BatchParams& Q, cudaStream_t stream);
 int column_has_nan_or_neginf(const float* col_dev, unsigned long long n, bool* out, cudaStream_t stream);
 
+// ---- p2p_kernels.cu ----
+int launch_hist_allreduce_p2p(const P2PParams& W, cudaStream_t stream);
+
 // ---- ensemble_kernels.cu ----
 int launch_event_mult(const int* read_bins_dev, long long nevents, int tnb, unsigned* mult_dev, cudaStream_t stream);
 int launch_cum(const unsigned* bins_dev, int nb, unsigned* cum_dev, cudaStream_t stream);

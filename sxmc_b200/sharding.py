@@ -111,3 +111,25 @@ class Comm:
         if self._c:
             lib().sxmc_comm_destroy(self._c)
             self._c = c_vp()
+
+
+def connect_p2p(chain, rank=None, world=None):
+    """Sample sharding over NVLink peer memory (``sxmc_chain_p2p_*``): export this rank's
+    histogram window, all-gather the 64-byte IPC handles through torch.distributed, open the
+    peers'.  Call on every rank, after ``chain.set_data`` or before the first run."""
+    import torch.distributed as dist
+    rank = dist.get_rank() if rank is None else int(rank)
+    world = dist.get_world_size() if world is None else int(world)
+    h = (C.c_ubyte * 64)()
+    check(lib().sxmc_chain_p2p_export(chain._c, C.cast(h, c_vp)))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, bytes(h))
+    blob = (C.c_ubyte * (64 * world)).from_buffer_copy(b"".join(gathered))
+    check(lib().sxmc_chain_p2p_connect(chain._c, C.cast(blob, c_vp), world, rank))
+    dist.barrier()
+
+
+def p2p_status(chain):
+    n, a = C.c_uint(0), C.c_int(0)
+    check(lib().sxmc_chain_p2p_status(chain._c, C.byref(n), C.byref(a)))
+    return n.value, bool(a.value)

@@ -63,6 +63,20 @@ def nccl_sample_sharded(outdir):
     torch.cuda.synchronize()
     dist.barrier()
     comm.close()
+
+    # the same over NVLink peer memory: one exchange kernel per step instead of ncclAllReduce
+    hists, chain = mcmc.build_fit(part)
+    chain.set_seed(99, 0)
+    sharding.connect_p2p(chain, rank, world)
+    ls = chain(fit.data, nsteps, 0.1)
+    nex, aborted = sharding.p2p_status(chain)
+    out.update(p2p_rows=ls.get_samples().copy(), p2p_bins=chain.bins(), p2p_norms=chain.norms(),
+               p2p_accepted=chain.accepted(), p2p_exchanges=nex, p2p_aborted=aborted)
+    torch.cuda.synchronize()
+    dist.barrier()
+    chain.close()
+    for h in hists:
+        h.close()
     np.savez(os.path.join(outdir, "sharded_rank%d.npz" % rank), **out)
     dist.destroy_process_group()
 
