@@ -76,6 +76,8 @@ def parse_args():
     ap.add_argument("--p2p", action="store_true",
                     help="with --shard-samples: exchange the histograms with the peer-memory kernel "
                          "(p2p_kernels.cu) instead of ncclAllReduce")
+    ap.add_argument("--p2p-form", type=int, default=0,
+                    help="with --p2p: 0 automatic (reduce-scatter + all-gather above 2 ranks), 1 one-shot, 2 two-shot")
     ap.add_argument("--experiments", type=int, default=296,
                     help="workload E: fake experiments per GPU (whole batches of 148)")
     ap.add_argument("--esteps", type=int, default=20000, help="workload E: MCMC steps per experiment")
@@ -265,6 +267,8 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
         hists, chain = mcmc.build_fit(fit_local)
         if getattr(args, "p2p", False):
             comm = "p2p"
+            from sxmc_b200 import pdfz as _pdfz
+            _pdfz.set_bin_tuning(p2p_form=getattr(args, "p2p_form", 0))
             sharding.connect_p2p(chain, rank, world)
         else:
             comm = sharding.Comm(device=local)
@@ -293,8 +297,13 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     barrier()
     sampler.start()
     l0 = chain.launches()
+    if comm == "p2p":
+        clk0 = sharding.p2p_clocks(chain)
     step_ms, bin_ms, nll_ms = chain.advance_timed(K, L2_FLUSH_BYTES)
     out["comm_ms"] = chain.last_comm_ms()
+    if comm == "p2p":
+        clk1 = sharding.p2p_clocks(chain)
+        out["p2p_us"] = [round((b - a) / K * 1e-3, 3) for a, b in zip(clk0, clk1)]
     out["gpu_launches"] = chain.launches() - l0
     barrier()
     out.update(step_ms=step_ms, bin_ms=bin_ms, nll_ms=nll_ms)
@@ -303,8 +312,13 @@ def measure_fit(fit, args, local, rank, sampler, do_e2e=True):
     chain.advance(Wm)
     barrier()
     ms0 = chain.loop_ms()
+    if comm == "p2p":
+        clk0 = sharding.p2p_clocks(chain)
     chain.advance(K)
     out["warm_ms"] = chain.loop_ms() - ms0
+    if comm == "p2p":
+        clk1 = sharding.p2p_clocks(chain)
+        out["p2p_us_warm"] = [round((b - a) / K * 1e-3, 3) for a, b in zip(clk0, clk1)]
     barrier()
     ls = chain.end()
     out["accepted"] = chain.accepted()
@@ -422,6 +436,12 @@ def run_own_arm(args, rank, world, local):
     fit = make_fit(args.workload, args.scale)
     K = args.steps
     r = measure_fit(fit, args, local, rank, sampler)
+    p2p_phases = None
+    if "p2p_us" in r:
+        box = [None] * world
+        torch.distributed.all_gather_object(box, (r["p2p_us"], r.get("p2p_us_warm")))
+        p2p_phases = {"what": "per rank [wait for every peer's partial, sum, close], device globaltimer",
+                      "cold": [b[0] for b in box], "back_to_back": [b[1] for b in box]}
     step_ms = allreduce_max(r["step_ms"])
     warm_ms = allreduce_max(r["warm_ms"])
     e2e_s = allreduce_max(r["e2e_s"])
@@ -449,6 +469,7 @@ def run_own_arm(args, rank, world, local):
                    if sharded else "1 independent chain per GPU (ensemble sharding), no collective"},
         "samples_binned_per_s": value * fit.total_samples(),
         "allreduce_ms_per_step": r["comm_ms"] / K,
+        "p2p_kernel_us_per_step": p2p_phases,
         "e2e": {"value": nchains * K / e2e_s, "unit": UNIT,
                 "h2d_bytes_per_step": r["e2e_h2d"], "d2h_bytes_per_step": r["e2e_d2h"],
                 "what": "MCMC.__call__(host data, K steps, burn-in 0.1) -> host chain rows: "

@@ -112,7 +112,8 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * blocks_per_sm <= 0 keeps the default;  kernel_select: 0 = automatic, bit 0 = force the
  * generic (interpreting) kernel, bit 1 = force run-time systematic dispatch in the fast
  * kernel (no compile-time program), bit 2 = the chain batch never takes its monotone endpoint
- * path -- used by the parity tests to cover every path. */
+ * path, bits 3-4 = form of the peer-memory all-reduce (0 automatic: two-shot above two ranks,
+ * 1 one-shot, 2 two-shot) -- used by the parity tests and measurements to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
@@ -308,6 +309,10 @@ int sxmc_chain_p2p_export(sxmc_chain* c, void* handle64_out);
 int sxmc_chain_p2p_connect(sxmc_chain* c, const void* handles, int nranks, int rank);
 /* exchanges completed so far; aborted != 0 after a peer failed to show up within ~2 s */
 int sxmc_chain_p2p_status(sxmc_chain* c, unsigned* exchanges_out, int* aborted_out);
+/* profiling hook: nanoseconds (device globaltimer), summed over all exchanges so far, the
+ * exchange kernel spent [0] publishing its flag and waiting for every peer's partial, [1]
+ * summing (until the last block is done), [2] closing the step (two-shot: second flag round) */
+int sxmc_chain_p2p_clocks(sxmc_chain* c, double* ns_out3);
 
 #ifdef __cplusplus
 }

@@ -130,6 +130,7 @@ SYMBOLS = {
     "sxmc_chain_p2p_export": (C.c_int, [c_vp, c_vp]),
     "sxmc_chain_p2p_connect": (C.c_int, [c_vp, c_vp, C.c_int, C.c_int]),
     "sxmc_chain_p2p_status": (C.c_int, [c_vp, C.POINTER(C.c_uint), C.POINTER(C.c_int)]),
+    "sxmc_chain_p2p_clocks": (C.c_int, [c_vp, C.POINTER(C.c_double)]),
     "sxmc_comm_unique_id": (C.c_int, [c_vp]),
     "sxmc_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "sxmc_comm_destroy": (C.c_int, [c_vp]),

@@ -29,6 +29,7 @@ static int g_smem_hist_max_bins = 8192;
 static int g_blocks_per_sm = 0;
 static int g_force_generic = 0;
 static int g_force_dynamic = 0;
+static int g_p2p_form = 0;       // peer-memory all-reduce: 0 automatic (two-shot above 2 ranks), 1 one-shot, 2 two-shot
 static int g_no_mono = 0;        // chain batch: never take the monotone endpoint path (tests)
 static long long g_persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent   // fast kernel with run-time systematic dispatch only
 static int g_timing = 0;
@@ -382,6 +383,7 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_force_generic = force_generic & 1;
   g_force_dynamic = (force_generic >> 1) & 1;
   g_no_mono = (force_generic >> 2) & 1;
+  g_p2p_form = (force_generic >> 3) & 3;
   return SXMC_OK;
 }
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
@@ -671,7 +673,8 @@ struct sxmc_chain {
   unsigned* part_buf[2] = {nullptr, nullptr};   // what the binning kernel writes: == hist_buf, or this rank's
                                                 // partials inside its peer window (sample sharding over P2P)
   // peer-memory all-reduce (p2p_kernels.cu)
-  unsigned* p2p_window = nullptr;               // [2][p2p_pitch] partials + [P2P_MAX_RANKS] flags, cudaIpc-exported
+  unsigned* p2p_window = nullptr;               // [2][p2p_pitch] partials + [2][p2p_pitch] sums + [2][P2P_MAX_RANKS] flags, cudaIpc-exported
+  unsigned* hist_own[2] = {nullptr, nullptr};   // the cudaMalloc'd hist_buf (hist_buf points into the window once connected)
   size_t p2p_pitch = 0;
   void* p2p_peer[P2P_MAX_RANKS] = {nullptr};    // opened peer windows (own slot = p2p_window)
   int p2p_nranks = 0, p2p_rank = 0;
@@ -770,9 +773,11 @@ static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr) {
     memset(&W, 0, sizeof W);
     for (int p = 0; p < c->p2p_nranks; ++p) {
       W.part[p] = (const unsigned*)c->p2p_peer[p];
-      W.flags[p] = (unsigned*)c->p2p_peer[p] + 2 * c->p2p_pitch;
+      W.flags[p] = (unsigned*)c->p2p_peer[p] + 4 * c->p2p_pitch;
     }
     W.sum = c->hist_buf[b];
+    W.sum_offset = (2 + (size_t)b) * c->p2p_pitch;
+    W.twoshot = g_p2p_form ? (g_p2p_form == 2) : (c->p2p_nranks > 2);
     W.seq = c->p2p_state; W.ticket = c->p2p_state + 1; W.abort_flag = c->p2p_state + 2;
     W.words = c->hist_words; W.pitch = c->p2p_pitch; W.parity = b;
     W.nranks = c->p2p_nranks; W.rank = c->p2p_rank;
@@ -911,6 +916,7 @@ int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out) {
   for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
     e = cudaMalloc(&c->hist_buf[b], sizeof(unsigned) * c->hist_words);
     c->part_buf[b] = c->hist_buf[b];
+    c->hist_own[b] = c->hist_buf[b];
     if (e == cudaSuccess) e = cudaMalloc(&c->sigs_dev[b], sizeof(NllSignal) * c->nsignals);
   }
   if (e == cudaSuccess) e = cudaMalloc(&c->partials, sizeof(double) * 148 * 8);
@@ -942,7 +948,7 @@ int sxmc_chain_destroy(sxmc_chain* c) {
   for (auto& e : c->tev) cudaEventDestroy(e);
   cudaFree(c->st_dev);
   if (c->st_host) cudaFreeHost(c->st_host);
-  for (int b = 0; b < 2; ++b) { cudaFree(c->hist_buf[b]); cudaFree(c->sigs_dev[b]); c->batch[b].release(); }
+  for (int b = 0; b < 2; ++b) { cudaFree(c->hist_own[b]); cudaFree(c->sigs_dev[b]); c->batch[b].release(); }
   cudaFree(c->partials); cudaFree(c->ticket); cudaFree(c->lut_dev); cudaFree(c->rows_dev);
   cudaFree(c->nll_trace_dev); cudaFree(c->prop_trace_dev); cudaFree(c->tape_n_dev); cudaFree(c->tape_u_dev);
   if (c->ev0) cudaEventDestroy(c->ev0);
@@ -2103,12 +2109,12 @@ int sxmc_chain_p2p_export(sxmc_chain* c, void* handle64_out) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
   if (!c->p2p_window) {
     c->p2p_pitch = (c->hist_words + 31) & ~(size_t)31;           // 128-byte aligned parities
-    const size_t words = 2 * c->p2p_pitch + P2P_MAX_RANKS;
+    const size_t words = 4 * c->p2p_pitch + 2 * P2P_MAX_RANKS;
     SXMC_CUDA(cudaMalloc(&c->p2p_window, sizeof(unsigned) * words));
     SXMC_CUDA(cudaMemset(c->p2p_window, 0, sizeof(unsigned) * words));
-    SXMC_CUDA(cudaMalloc(&c->p2p_state, sizeof(unsigned) * 4));
-    SXMC_CUDA(cudaMemset(c->p2p_state, 0, sizeof(unsigned) * 4));
-    SXMC_CUDA(cudaMallocHost(&c->p2p_state_host, sizeof(unsigned) * 4));
+    SXMC_CUDA(cudaMalloc(&c->p2p_state, sizeof(unsigned) * 16));      // + 4 x u64 phase clocks
+    SXMC_CUDA(cudaMemset(c->p2p_state, 0, sizeof(unsigned) * 16));
+    SXMC_CUDA(cudaMallocHost(&c->p2p_state_host, sizeof(unsigned) * 16));
   }
   cudaIpcMemHandle_t h;
   SXMC_CUDA(cudaIpcGetMemHandle(&h, c->p2p_window));
@@ -2133,6 +2139,8 @@ int sxmc_chain_p2p_connect(sxmc_chain* c, const void* handles, int nranks, int r
   c->p2p_rank = rank;
   c->part_buf[0] = c->p2p_window;
   c->part_buf[1] = c->p2p_window + c->p2p_pitch;
+  c->hist_buf[0] = c->p2p_window + 2 * c->p2p_pitch;      // peers store their slices of the sum here
+  c->hist_buf[1] = c->p2p_window + 3 * c->p2p_pitch;
   if (c->have_data) SXMC_TRY(chain_build_tables(c));
   return SXMC_OK;
 }
@@ -2142,6 +2150,17 @@ int sxmc_chain_p2p_status(sxmc_chain* c, unsigned* exchanges_out, int* aborted_o
   SXMC_CUDA(cudaMemcpy(c->p2p_state_host, c->p2p_state, sizeof(unsigned) * 4, cudaMemcpyDeviceToHost));
   if (exchanges_out) *exchanges_out = c->p2p_state_host[0];
   if (aborted_out) *aborted_out = (int)c->p2p_state_host[2];
+  return SXMC_OK;
+}
+
+int sxmc_chain_p2p_clocks(sxmc_chain* c, double* ns_out3) {
+  if (!c || !ns_out3) SXMC_INVAL("sxmc_chain_p2p_clocks: NULL argument");
+  ns_out3[0] = ns_out3[1] = ns_out3[2] = 0;
+  if (!c->p2p_state) return SXMC_OK;
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  SXMC_CUDA(cudaMemcpy(c->p2p_state_host, c->p2p_state, sizeof(unsigned) * 16, cudaMemcpyDeviceToHost));
+  const unsigned long long* clk = reinterpret_cast<const unsigned long long*>(c->p2p_state_host + 4);
+  for (int i = 0; i < 3; ++i) ns_out3[i] = (double)clk[1 + i];
   return SXMC_OK;
 }
 

@@ -165,8 +165,10 @@ struct MonoParams {
 constexpr int P2P_MAX_RANKS = 8;
 struct P2PParams {
   const unsigned* part[P2P_MAX_RANKS];   // every rank's partial-histogram window (own one included)
-  unsigned* flags[P2P_MAX_RANKS];        // every rank's flag array [P2P_MAX_RANKS]: flags[p][r] = last step rank r published to p
-  unsigned* sum;                         // this rank's complete histogram (private)
+  unsigned* flags[P2P_MAX_RANKS];        // every rank's flag array [2][P2P_MAX_RANKS]: flags[p][r] = last step rank r
+                                         // published to p ("partial complete"); [p][8 + r] = "my slice of the sum is written"
+  unsigned* sum;                         // this rank's complete histogram (one-shot form)
+  unsigned long long sum_offset;         // two-shot form: words from a window's start to the sum of this parity
   unsigned* seq;                         // this rank's step counter (private, advanced by the kernel)
   unsigned* ticket;
   unsigned* abort_flag;
@@ -174,6 +176,7 @@ struct P2PParams {
   unsigned long long pitch;              // words between the two parities inside a window
   int parity;
   int nranks, rank;
+  int twoshot;                           // reduce-scatter + all-gather (nranks > 2)
 };
 
 // One signal as seen by the lookup + event-likelihood kernel.

@@ -8,9 +8,12 @@
 //   2. waits until every peer has published the same (acquire loads, bounded spin),
 //   3. sums the N partials with 128-bit peer loads into the rank's private, complete histogram.
 // One synchronisation, (N-1) x histogram bytes of NVLink reads per rank (D: 3 MB per peer), no
-// intermediate copies: at these sizes the exchange is latency-bound, and one flag round trip
-// beats the two or more a ring or tree needs.  Integer sums in a fixed rank order, so every
-// rank holds bit-identical histograms.
+// intermediate copies.  That is the form for two ranks; for more, reading every peer's whole
+// partial costs (N-1) x 3 MB per rank (8 ranks: 68 us per step measured), so the kernel
+// switches to reduce-scatter + all-gather inside the same launch: each rank sums 1/N of the
+// words and stores that slice into every rank's sum buffer (which therefore lives in the
+// window too), then a second flag round says "slice in place".  Integer sums, so every rank
+// holds bit-identical histograms in either form.
 //
 // Buffer reuse is safe without further handshakes: a peer overwrites the partial of parity b
 // only two steps later, and it cannot pass its own step s+1 kernel before this rank has
@@ -30,55 +33,110 @@ __device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(256)
-hist_allreduce_p2p_kernel(const __grid_constant__ P2PParams W) {
-  __shared__ int s_ok;
-  const unsigned seq = *W.seq + 1u;              // the step being exchanged (same on every block)
-  if (threadIdx.x == 0) {
-    int ok = 1;
-    if (blockIdx.x == 0) {
-      __threadfence_system();                    // the binning kernel's writes are ordered before the flags
-      for (int p = 0; p < W.nranks; ++p) st_release_sys_u32(W.flags[p] + W.rank, seq);
-    }
-    const long long t0 = clock64();
-    for (int p = 0; p < W.nranks && ok; ++p) {
-      unsigned n = 0;
-      while ((int)(ld_acquire_sys_u32(W.flags[W.rank] + p) - seq) < 0) {
-        if ((++n & 63u) == 0) {
-          if (*(volatile unsigned*)W.abort_flag) { ok = 0; break; }
-          if (clock64() - t0 > PK_TIMEOUT_CYCLES) { atomicExch(W.abort_flag, 1u); ok = 0; break; }
-        }
+// Spin until every peer's flag in this rank's own flag row `base` has reached `seq`.
+__device__ __forceinline__ int wait_peers(const P2PParams& W, const unsigned* base, unsigned seq) {
+  const long long t0 = clock64();
+  for (int p = 0; p < W.nranks; ++p) {
+    unsigned n = 0;
+    while ((int)(ld_acquire_sys_u32(base + p) - seq) < 0) {
+      if ((++n & 63u) == 0) {
+        if (*(volatile unsigned*)W.abort_flag) return 0;
+        if (clock64() - t0 > PK_TIMEOUT_CYCLES) { atomicExch(W.abort_flag, 1u); return 0; }
       }
     }
-    s_ok = ok;
+  }
+  return 1;
+}
+
+__global__ void __launch_bounds__(256)
+hist_allreduce_p2p_kernel(const __grid_constant__ P2PParams W) {
+  __shared__ int s_ok, s_last;
+  const unsigned seq = *W.seq + 1u;              // the step being exchanged (same on every block)
+  unsigned long long* const clk = reinterpret_cast<unsigned long long*>(W.seq + 4);   // [0] scratch, [1..3] sums (ns)
+  unsigned long long t0 = 0;
+  // the binning kernel finished before this launch started (stream order), so its partial is
+  // complete in this rank's memory: tell every peer, one thread per peer so the system-scope
+  // release stores travel in parallel
+  if (blockIdx.x == 0 && threadIdx.x < W.nranks) {
+    if (threadIdx.x == 0) t0 = globaltimer_ns();
+    __threadfence_system();
+    st_release_sys_u32(W.flags[threadIdx.x] + W.rank, seq);
+  }
+  if (threadIdx.x == 0) {
+    s_ok = wait_peers(W, W.flags[W.rank], seq);
+    if (blockIdx.x == 0) {
+      const unsigned long long t1 = globaltimer_ns();
+      clk[0] = t1;
+      clk[1] += t1 - t0;
+    }
   }
   __syncthreads();
-  if (s_ok) {
+  const unsigned long long gtid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  const unsigned long long gstride = (unsigned long long)gridDim.x * blockDim.x;
+  const size_t poff = (size_t)W.parity * W.pitch;
+  if (s_ok && !W.twoshot) {
     const unsigned long long nvec = W.words / 4;
-    const unsigned long long gtid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-    const unsigned long long gstride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long v = gtid; v < nvec; v += gstride) {
       uint4 acc = make_uint4(0u, 0u, 0u, 0u);
       for (int p = 0; p < W.nranks; ++p) {
-        const uint4 x = __ldcv(reinterpret_cast<const uint4*>(W.part[p] + (size_t)W.parity * W.pitch) + v);
+        const uint4 x = __ldcv(reinterpret_cast<const uint4*>(W.part[p] + poff) + v);
         acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
       }
       reinterpret_cast<uint4*>(W.sum)[v] = acc;
     }
     for (unsigned long long w = nvec * 4 + gtid; w < W.words; w += gstride) {
       unsigned acc = 0;
-      for (int p = 0; p < W.nranks; ++p) acc += __ldcv(W.part[p] + (size_t)W.parity * W.pitch + w);
+      for (int p = 0; p < W.nranks; ++p) acc += __ldcv(W.part[p] + poff + w);
       W.sum[w] = acc;
     }
+  } else if (s_ok) {
+    // reduce-scatter + all-gather: this rank sums its 1/N slice of the (128-byte padded) window
+    // and stores the result into every rank's sum buffer: 2 (N-1)/N x histogram bytes of NVLink
+    // traffic per rank instead of (N-1) x.
+    const unsigned long long nvec = W.pitch / 4;
+    const unsigned long long v0 = nvec * (unsigned)W.rank / (unsigned)W.nranks;
+    const unsigned long long v1 = nvec * (unsigned)(W.rank + 1) / (unsigned)W.nranks;
+    for (unsigned long long v = v0 + gtid; v < v1; v += gstride) {
+      uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+      for (int p = 0; p < P2P_MAX_RANKS; ++p)
+        if (p < W.nranks) {
+          const uint4 x = __ldcv(reinterpret_cast<const uint4*>(W.part[p] + poff) + v);
+          acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+        }
+#pragma unroll
+      for (int p = 0; p < P2P_MAX_RANKS; ++p)
+        if (p < W.nranks)
+          reinterpret_cast<uint4*>(const_cast<unsigned*>(W.part[p]) + W.sum_offset)[v] = acc;
+    }
+    __threadfence_system();                      // this thread's peer stores are visible before the block reports
   }
-  // the last block to finish advances the sequence number for the next step's launch
+  // the last block to finish closes the step: (two-shot) tell every peer this rank's slice is
+  // in place and wait for theirs, then advance the sequence number for the next launch
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
-    if (atomicAdd(W.ticket, 1u) == gridDim.x - 1) {
-      *W.ticket = 0u;
-      *W.seq = seq;
+    s_last = atomicAdd(W.ticket, 1u) == gridDim.x - 1;
+    if (s_last) __threadfence();
+  }
+  __syncthreads();
+  if (!s_last) return;
+  unsigned long long t2 = 0;
+  if (threadIdx.x == 0) {
+    t2 = globaltimer_ns();
+    clk[2] += t2 - *(volatile unsigned long long*)clk;
+  }
+  if (W.twoshot && s_ok) {
+    if (threadIdx.x < W.nranks) {
+      __threadfence_system();
+      st_release_sys_u32(W.flags[threadIdx.x] + P2P_MAX_RANKS + W.rank, seq);
     }
+    if (threadIdx.x == 0) wait_peers(W, W.flags[W.rank] + P2P_MAX_RANKS, seq);
+  }
+  if (threadIdx.x == 0) {
+    clk[3] += globaltimer_ns() - t2;
+    *W.ticket = 0u;
+    *W.seq = seq;
   }
 }
 

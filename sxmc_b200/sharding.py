@@ -133,3 +133,10 @@ def p2p_status(chain):
     n, a = C.c_uint(0), C.c_int(0)
     check(lib().sxmc_chain_p2p_status(chain._c, C.byref(n), C.byref(a)))
     return n.value, bool(a.value)
+
+
+def p2p_clocks(chain):
+    """(wait, sum, close) nanoseconds the exchange kernel has spent so far, summed over exchanges."""
+    out = (C.c_double * 3)()
+    check(lib().sxmc_chain_p2p_clocks(chain._c, out))
+    return tuple(out)

@@ -77,6 +77,23 @@ def nccl_sample_sharded(outdir):
     chain.close()
     for h in hists:
         h.close()
+
+    # ... and its reduce-scatter + all-gather form (what more than two ranks use), forced here
+    from sxmc_b200 import pdfz
+    pdfz.set_bin_tuning(p2p_form=2)
+    hists, chain = mcmc.build_fit(part)
+    chain.set_seed(99, 0)
+    sharding.connect_p2p(chain, rank, world)
+    ls = chain(fit.data, nsteps, 0.1)
+    nex, aborted = sharding.p2p_status(chain)
+    out.update(p2p2_rows=ls.get_samples().copy(), p2p2_bins=chain.bins(), p2p2_norms=chain.norms(),
+               p2p2_accepted=chain.accepted(), p2p2_exchanges=nex, p2p2_aborted=aborted)
+    torch.cuda.synchronize()
+    dist.barrier()
+    chain.close()
+    for h in hists:
+        h.close()
+    pdfz.set_bin_tuning(p2p_form=0)
     np.savez(os.path.join(outdir, "sharded_rank%d.npz" % rank), **out)
     dist.destroy_process_group()
 

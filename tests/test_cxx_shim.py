@@ -1,0 +1,122 @@
+"""The C++ class API of the reference (pdfz::Eval/EvalHist, hemi::Array, Signal, MCMC,
+LikelihoodSpace; cxx/include/sxmc/*.h) written over the C ABI: a test runner in C++
+(cxx/tests/test_class_api.cpp) drives it the way the reference's gtest suite does
+(test/test_pdfz*.cpp), on the same golden constants, and runs one fit whose chain must equal
+the ctypes mirror's chain row for row (same library, same Philox seed)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from tests import golden_vectors as G
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RUNNER = os.path.join(ROOT, "cxx", "tests", "test_class_api")
+SHIM = os.path.join(ROOT, "sxmc_b200", "libsxmc_cxx.so")
+
+
+def _fmt(v):
+    return " ".join("nan" if (x is None or (isinstance(x, float) and np.isnan(x))) else repr(float(x)) for x in v)
+
+
+def write_cases(path):
+    """golden_vectors.CASES / CTOR_ERRORS in the runner's record format."""
+    with open(path, "w") as f:
+        for name, samples, geom, evalp, syst, value, norm, expect in G.CASES:
+            nobs = len(geom["nbins"])
+            stype, sobs, sextra = syst if syst is not None else (-1, 0, 0)
+            f.write("case %s %d %d %d\n%s\n%s %s %s\n%d\n%s\n%d %d %d %r %d\n%s\n" % (
+                name, samples.shape[0], samples.shape[1], nobs, _fmt(samples.ravel()),
+                _fmt(geom["lower"]), _fmt(geom["upper"]), " ".join(str(int(b)) for b in geom["nbins"]),
+                evalp.shape[0], _fmt(evalp.ravel()), stype, sobs, sextra, float(value), norm,
+                _fmt(expect + [None] * (evalp.shape[0] - len(expect)))))
+        for name, kw, msg in G.CTOR_ERRORS:
+            nfields, nobs = kw.get("nfields", 1), kw.get("nobs", 1)
+            lower, upper, nbins = kw.get("lower", [0.0]), kw.get("upper", [1.0]), kw.get("nbins", [2])
+            f.write("error %s 7 %d %d %d %d %d %s %s\n" % (name, nfields, nobs, len(lower), len(upper), len(nbins),
+                                                          " ".join(str(b) for b in nbins), msg))
+
+
+def write_fit(fit, outdir, nsteps, seed):
+    """FitSpec -> fit.txt + raw float32 files, the runner's input."""
+    nfields = fit.signals[0].samples.shape[1]
+    lines = ["%d %d" % (fit.nobs, nfields)]
+    for i in range(fit.nobs):
+        lines.append("%r %r %d" % (float(fit.lower[i]), float(fit.upper[i]), int(fit.nbins[i])))
+    lines.append(str(fit.nsources))
+    for i in range(fit.nsources):
+        lines.append("%r %r %d" % (float(fit.source_means[i]), float(fit.source_sigmas[i]), int(fit.source_fixed[i])))
+    lines.append(str(len(fit.systematics)))
+    for y in fit.systematics:
+        lines.append("%d %d %d %d %d %s %s %s" % (y.type, y.obs, y.extra, y.npars, int(y.fixed), _fmt(y.means[:y.npars]),
+                                                 _fmt(y.sigmas[:y.npars]), " ".join(str(i) for i in y.pidx)))
+    lines.append(str(fit.nsignals))
+    for j, sig in enumerate(fit.signals):
+        assert sig.systematics == list(range(len(fit.systematics)))
+        name = "samples_%d.f32" % j
+        np.ascontiguousarray(sig.samples, dtype=np.float32).tofile(os.path.join(outdir, name))
+        lines.append("%r %d %d %d %s" % (float(sig.nexpected), sig.source, sig.n_mc, sig.samples.shape[0], name))
+    fit.data.tofile(os.path.join(outdir, "data.f32"))
+    lines.append("%d data.f32" % fit.data.size)
+    lines.append("%d 0.1 %d" % (nsteps, seed))
+    path = os.path.join(outdir, "fit.txt")
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path
+
+
+def test_shim_library_and_runner_are_built():
+    """CPU check: the class-API library links against the C ABI and loads; the runner refuses to
+    run without a device (no CPU fallback anywhere above the C ABI either)."""
+    assert os.path.exists(SHIM), "run `make -C cxx` (python __graft_entry__.py does)"
+    ctypes.CDLL(os.path.join(ROOT, "sxmc_b200", "libsxmc_b200.so"), mode=ctypes.RTLD_GLOBAL)
+    ctypes.CDLL(SHIM)
+    assert os.access(RUNNER, os.X_OK)
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([RUNNER, "x", "y", "z"], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 3 and "no CPU fallback" in r.stderr
+
+
+def test_case_files_round_trip(tmp_path):
+    write_cases(tmp_path / "cases.txt")
+    text = (tmp_path / "cases.txt").read_text()
+    assert text.count("case ") == len(G.CASES) and text.count("error ") == len(G.CTOR_ERRORS)
+
+
+@pytest.mark.gpu
+def test_class_api_runner_matches_golden_vectors_and_ctypes_chain(tmp_path):
+    from sxmc_b200 import mcmc, workloads as W
+    fit = W.config_C(0.002)
+    nsteps, seed = 1500, 4242
+    write_cases(tmp_path / "cases.txt")
+    fit_txt = write_fit(fit, str(tmp_path), nsteps, seed)
+    r = subprocess.run([RUNNER, str(tmp_path / "cases.txt"), fit_txt, str(tmp_path)], capture_output=True,
+                       text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert " 0 failures" in r.stdout
+
+    # the same fit through the ctypes mirror: identical rows, acceptance count, efficiencies
+    hists, chain = mcmc.build_fit(fit)
+    chain.set_seed(seed, 0)
+    ls = chain(fit.data, nsteps, 0.1)
+    rows = ls.get_samples()
+    got = np.fromfile(tmp_path / "rows.bin", dtype=np.float32).reshape(-1, fit.nparameters + 1)
+    assert got.shape == rows.shape and got.tobytes() == rows.tobytes()
+    head = (tmp_path / "fit_out.txt").read_text().split("\n")
+    nrows, accepted, _ = head[0].split()
+    assert int(nrows) == rows.shape[0] and int(accepted) == chain.accepted()
+    eff = np.asarray([float(x) for x in head[1:1 + fit.nsignals]])
+    pars = fit.parameter_means()
+    chain.nll(pars)
+    want = chain.norms() / np.asarray([s.n_mc for s in fit.signals], dtype=np.float64)
+    assert np.array_equal(eff, want)
+    # the contour intervals bracket the point estimate
+    for line in head[1 + fit.nsignals:1 + fit.nsignals + fit.nparameters]:
+        _, pt, lo, hi = line.split()
+        assert float(lo) <= float(pt) <= float(hi)
+    chain.close()
+    for h in hists:
+        h.close()

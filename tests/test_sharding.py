@@ -89,8 +89,10 @@ def test_nccl_sample_sharded_chain_equals_single_gpu_chain(tmp_path):
     assert z0["accepted"] == z0["single_accepted"] == z1["accepted"]
     assert z0["rows"].shape[0] > 0
     # the peer-memory exchange gives the same chain, on both ranks
+    # (p2p_: one-shot form, p2p2_: reduce-scatter + all-gather form)
     for z in (z0, z1):
-        for k in ("bins", "norms", "rows"):
-            assert np.array_equal(z["p2p_" + k], z0["single_" + k]), k
-        assert z["p2p_accepted"] == z0["single_accepted"]
-        assert not z["p2p_aborted"] and z["p2p_exchanges"] == 301     # initial evaluation + 300 steps
+        for pre in ("p2p_", "p2p2_"):
+            for k in ("bins", "norms", "rows"):
+                assert np.array_equal(z[pre + k], z0["single_" + k]), pre + k
+            assert z[pre + "accepted"] == z0["single_accepted"]
+            assert not z[pre + "aborted"] and z[pre + "exchanges"] == 301     # initial evaluation + 300 steps
