@@ -109,13 +109,15 @@ hist_allreduce_p2p_kernel(const __grid_constant__ P2PParams W) {
         if (p < W.nranks)
           reinterpret_cast<uint4*>(const_cast<unsigned*>(W.part[p]) + W.sum_offset)[v] = acc;
     }
-    __threadfence_system();                      // this thread's peer stores are visible before the block reports
   }
   // the last block to finish closes the step: (two-shot) tell every peer this rank's slice is
   // in place and wait for theirs, then advance the sequence number for the next launch
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence();
+    // barrier, then ONE cumulative fence per block (the grid-sync idiom): the block's peer
+    // stores are ordered before its ticket, hence before the flags the last block publishes.
+    // (A system fence in every storing thread cost ~10 us per exchange.)
+    if (W.twoshot) __threadfence_system(); else __threadfence();
     s_last = atomicAdd(W.ticket, 1u) == gridDim.x - 1;
     if (s_last) __threadfence();
   }

@@ -371,13 +371,16 @@ def build_fit(fit, sort=True, batch=0):
             else:
                 h.AddSystematic(pdfz.ResolutionScaleSystematic(y.obs, y.extra, y.pidx))
         hists.append(h)
-    sources = [Source("s%d" % i, i, fit.source_means[i], fit.source_sigmas[i], fit.source_fixed[i])
+    nm = getattr(fit, "names", None) or {}      # config.FitConfig.to_fitspec carries the configured names
+    name = lambda kind, fmt, i: nm[kind][i] if kind in nm else fmt % i
+    sources = [Source(name("sources", "s%d", i), i, fit.source_means[i], fit.source_sigmas[i], fit.source_fixed[i])
                for i in range(fit.nsources)]
-    systs = [Systematic("y%d" % i, y.npars, list(y.means), list(y.sigmas), y.fixed)
+    systs = [Systematic(name("systematics", "y%d", i), y.npars, list(y.means), list(y.sigmas), y.fixed)
              for i, y in enumerate(fit.systematics)]
-    signals = [Signal("sig%d" % j, hists[j], sig.nexpected, sig.n_mc, sources[sig.source])
+    signals = [Signal(name("signals", "sig%d", j), hists[j], sig.nexpected, sig.n_mc, sources[sig.source])
                for j, sig in enumerate(fit.signals)]
-    observables = [Observable("o%d" % i, float(fit.lower[i]), float(fit.upper[i])) for i in range(fit.nobs)]
+    observables = [Observable(name("observables", "o%d", i), float(fit.lower[i]), float(fit.upper[i]))
+                   for i in range(fit.nobs)]
     if batch:
         return hists, MCMCBatch(sources, signals, systs, observables, batch)
     mc = MCMC(sources, signals, systs, observables)
