@@ -5,6 +5,11 @@
 #include "nll_device.cuh"
 #include "grid_sync.cuh"
 
+// threads per CTA of the including kernel (every thread takes part in the lookup + tail)
+#ifndef BATCH_THREADS
+#define BATCH_THREADS FAST_THREADS
+#endif
+
 namespace sxmc {
 
 constexpr int BK_MAX_SIGNALS = 128;
@@ -17,7 +22,7 @@ struct BatchShared {
   const int* rb[BK_MAX_SIGNALS];
   unsigned nmc[BK_MAX_SIGNALS];
   short sid[BK_MAX_SIGNALS];
-  double warp[FAST_THREADS / 32];
+  double warp[BATCH_THREADS / 32];
   double term[BK_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
   FinState F;
   int ok;
@@ -28,7 +33,7 @@ struct BatchShared {
 // once per launch: the owned chain's state and signal tables into shared memory
 __device__ __forceinline__ void batch_owner_init(BatchShared& S, const BatchParams& Q, int mine, int tid) {
   if (mine < 0) return;
-  prefetch_state(S.F, Q.st + mine, Q.np, tid, FAST_THREADS);
+  prefetch_state(S.F, Q.st + mine, Q.np, tid, BATCH_THREADS);
   if (tid < Q.ns) {
     const NllSignal sg = Q.sigs[(size_t)mine * Q.ns + tid];
     S.nexp[tid] = sg.nexpected;
@@ -56,7 +61,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     S.bn[tid] = __dmul_rn((double)norm, S.binvol[tid]);                    // pdfz.cpp:417
     S.term[tid] = __dmul_rn(rate, (double)norm) / (double)S.nmc[tid];      // nll_kernels.cpp:167-171
   }
-  for (int i = tid; i < np; i += FAST_THREADS) {       // Gaussian constraints (nll_kernels.cpp:176-185)
+  for (int i = tid; i < np; i += BATCH_THREADS) {       // Gaussian constraints (nll_kernels.cpp:176-185)
     const double sg = F.sigmas[i];
     double t = 0;
     if (sg > 0) {
@@ -73,7 +78,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     // same likelihood: sum_i log(s_i) = sum_b m_b log(s_b), m_b = events of this chain in bin b
     // (counted once when the data were set).  eval_pdf's division runs once per (signal, bin)
     // instead of once per (signal, event), and the values live in shared memory.
-    for (int q = tid; q < ns * tnb; q += FAST_THREADS) {
+    for (int q = tid; q < ns * tnb; q += BATCH_THREADS) {
       const int j = q / tnb;
       float v = (float)((double)__ldcg(my_hist + q) / S.bn[j]);              // pdfz.cpp:429-432
       if (isnan(v)) v = 0.0f;                                                  // nll_kernels.cpp:107
@@ -81,7 +86,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     }
     __syncthreads();
     const unsigned* mult = Q.mult + (size_t)mine * tnb;
-    for (int b = tid; b < tnb; b += FAST_THREADS) {
+    for (int b = tid; b < tnb; b += BATCH_THREADS) {
       const unsigned m = mult[b];
       if (!m) continue;
       double acc = 0;
@@ -89,7 +94,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
       if (acc > 0) sum += (double)m * log(acc);
     }
   } else
-  for (long long i = tid; i < my_ne; i += FAST_THREADS) {
+  for (long long i = tid; i < my_ne; i += BATCH_THREADS) {
     double acc = 0;
     for (int j = 0; j < ns; ++j) {
       const int rb = S.rb[j][i];
@@ -102,10 +107,10 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     }
     if (acc > 0) sum += log(acc);
   }
-  const double total = block_sum<FAST_THREADS>(sum, S.warp);   // ends past a CTA barrier: lookups done
+  const double total = block_sum<BATCH_THREADS>(sum, S.warp);   // ends past a CTA barrier: lookups done
   if (tid == 0) S.warp[0] = total;
   if (clear)     // rebuilt from zero by the next super-step's bin phase (the last one is kept)
-    for (unsigned long long w = tid; w < Q.hist_words; w += FAST_THREADS) my_hist[w] = 0u;
+    for (unsigned long long w = tid; w < Q.hist_words; w += BATCH_THREADS) my_hist[w] = 0u;
   __syncthreads();
   if (tid < 32) finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid);
   __syncthreads();

@@ -10,7 +10,7 @@
 // For one chain, a warp evaluates the two ends of the range and then each lane bisects for one
 // bin edge: ~log2(n) evaluations per EDGE instead of one per SAMPLE, every evaluation being the
 // reference's arithmetic on an actual sample, so the counts are bit-identical to the
-// sample-by-sample pass.  The 16 warps of a CTA work on 16 different chains at once.
+// sample-by-sample pass.  The warps of a CTA (32) work on as many different chains at once.
 // The host cuts the ranges so that every CTA sees about the same number of edges (sparse tails
 // get few samples, the dense core is limited by shared-memory capacity) -- plan_chain_batch_mono.
 //
@@ -21,6 +21,16 @@
 #include "bin_device.cuh"
 #include "nll_device.cuh"
 #include "grid_sync.cuh"
+// Threads per CTA.  The bin phase is a chain of dependent shared-memory loads and FP64
+// evaluations per warp, so the warps in flight set its speed: 32 warps (64 registers each, no spills)
+// against the 16 of the streaming kernels (E: 184 -> 210 -> 236 experiments/s at 16 / 24 / 32 warps).
+#ifndef SXMC_MONO_THREADS
+#define SXMC_MONO_THREADS 1024
+#endif
+#define BATCH_THREADS SXMC_MONO_THREADS
+#ifndef SXMC_MONO_DBG_CTA
+#define SXMC_MONO_DBG_CTA 70   // the CTA whose per-chain clocks tools/prof_batch.py prints
+#endif
 #include "batch_device.cuh"
 
 #include <algorithm>
@@ -28,6 +38,9 @@
 #include <vector>
 
 namespace sxmc {
+
+constexpr int MONO_THREADS = SXMC_MONO_THREADS;
+constexpr int MONO_WARPS = MONO_THREADS / 32;
 
 // code of a transformed sample: -1 below the domain (or NaN), -2 at/above the upper edge, else
 // the bin index (which can be total_nbins for x' within an ulp of the edge: counted in the norm
@@ -59,12 +72,22 @@ __device__ __forceinline__ int mono_rank(int code, int tnb) {
   return code == -1 ? 0 : (code == -2 ? tnb + 2 : code + 1);
 }
 
+// rank of an untransformed value (guesses only; never decides a count)
+constexpr int MONO_TAB = 128;
+__device__ __forceinline__ int nominal_rank(float xf, const Geo& geo, int tnb) {
+  const double x = (double)xf;
+  if (!(x >= geo.lo[0])) return 0;
+  if (!(x < geo.hi[0])) return tnb + 2;
+  return min((int)((x - geo.lo[0]) * geo.sc[0]), tnb) + 1;
+}
+
 template <int NOPS, unsigned CODES>
-__global__ void __launch_bounds__(FAST_THREADS, 1)
+__global__ void __launch_bounds__(MONO_THREADS, 1)
 chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_constant__ BatchParams Q) {
   extern __shared__ __align__(16) float s_x[];       // this CTA's sorted samples
   __shared__ BatchShared S;
   __shared__ double s_par[BATCH_MAX_CHAINS][FAST_MAX_OPS];   // every chain's systematic coefficients
+  __shared__ int s_tab[MONO_TAB];
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -81,10 +104,27 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
   const MonoJob& job = M.job[job_j];
   {
     const unsigned long long s0 = M.s0[blockIdx.x];
-    for (int p = tid; p < n; p += FAST_THREADS) s_x[p] = __ldg(job.col + tiled_offset(s0 + p));
+    for (int p = tid; p < n; p += MONO_THREADS) s_x[p] = __ldg(job.col + tiled_offset(s0 + p));
   }
   const int mine = blockIdx.x < (unsigned)nch ? (int)blockIdx.x : -1;
   batch_owner_init(S, Q, mine, tid);
+  __syncthreads();
+  // Nominal edge table: s_tab[k] = first position whose rank WITHOUT systematics reaches
+  // r0_nom + k.  A lane's threshold falls into one nominal bin, so its float bisection starts
+  // from that bin's samples instead of the whole range: fewer steps, and the lanes no longer
+  // probe positions a power-of-two stride apart (for n near k * 4096 those shared one bank:
+  // the CTA with n = 28671 took twice as long over its guesses as its neighbours).
+  const int r0_nom = n > 0 ? nominal_rank(s_x[0], geo, tnb) : 0;
+  const int r1_nom = n > 0 ? nominal_rank(s_x[n - 1], geo, tnb) : 0;
+  const int ntab = (r1_nom - r0_nom + 2 <= MONO_TAB) ? r1_nom - r0_nom + 2 : 0;    // 0: span too wide, no table
+  for (int k = tid; k < ntab; k += MONO_THREADS) {
+    int a0 = 0, a1 = n;
+    while (a0 < a1) {
+      const int mid = (a0 + a1) >> 1;
+      if (nominal_rank(s_x[mid], geo, tnb) < r0_nom + k) a0 = mid + 1; else a1 = mid;
+    }
+    s_tab[k] = a0;
+  }
   __syncthreads();
 
   const int nsyst = job.nsyst;
@@ -102,20 +142,20 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
     const bool bin_now = Q.rebin || mode == NLL_MODE_INIT;
     BKM_STAMP(0);
 
-    // ---- bin: warp w takes chains w, w + 16, ... ---------------------------------------------
+    // ---- bin: warp w takes chains w, w + MONO_WARPS, ... ---------------------------------------------
     if (bin_now) {
       if (n > 0) {
         // all chains' coefficients in one round of loads (a warp would otherwise pay an L2 round
         // trip per chain)
-        for (int q = tid; q < nch * FAST_MAX_OPS; q += FAST_THREADS) {
+        for (int q = tid; q < nch * FAST_MAX_OPS; q += MONO_THREADS) {
           const int e = q / FAST_MAX_OPS, k = q % FAST_MAX_OPS;
           double par = 0.0;
           if (k < nsyst && job.npars[k]) par = __ldcg(&Q.st[e].proposed[nsources + job.pidx[k]]);
           s_par[e][k] = par;
         }
         __syncthreads();
-        for (int e = warp; e < nch; e += FAST_WARPS) {
-          const bool dbg = Q.stamps && s == 20u && blockIdx.x == 70 && tid == 0 && e == 0;
+        for (int e = warp; e < nch; e += MONO_WARPS) {
+          const bool dbg = Q.stamps && s == 20u && blockIdx.x == SXMC_MONO_DBG_CTA && tid == 0 && e == 0;
           long long tq0 = 0, tq1 = 0, tq2 = 0, tq3 = 0;
           if (dbg) tq0 = clock64();
           double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
@@ -172,6 +212,11 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
               int p0 = n >> 1;
               if (thr == thr) {
                 int a0 = 0, a1 = n;                        // first sample >= thr (floats only)
+                if (ntab) {
+                  const int kk = min(max(nominal_rank(thr, geo, tnb) - r0_nom, 0), ntab - 1);
+                  a0 = s_tab[kk];
+                  a1 = kk + 1 < ntab ? s_tab[kk + 1] : n;
+                }
                 while (a0 < a1) {
                   const int mid = (a0 + a1) >> 1;
                   if (s_x[mid] < thr) a0 = mid + 1; else a1 = mid;
@@ -408,11 +453,11 @@ int launch_chain_batch_mono(const MonoPlan& plan, const BatchParams& Q0, cudaStr
   const size_t smem = std::max<size_t>(plan.smem_bytes, 128);
   SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
-  SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fk, FAST_THREADS, smem));
+  SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fk, MONO_THREADS, smem));
   if (occ < 1) { set_error("monotone chain batch kernel does not fit on an SM"); return SXMC_ESTATE; }
   BatchParams Q = Q0;
   void* args[2] = {(void*)&plan.params, (void*)&Q};
-  SXMC_CUDA(cudaLaunchCooperativeKernel((const void*)fk, dim3((unsigned)plan.grid), dim3(FAST_THREADS), args, smem,
+  SXMC_CUDA(cudaLaunchCooperativeKernel((const void*)fk, dim3((unsigned)plan.grid), dim3(MONO_THREADS), args, smem,
                                         stream));
   return SXMC_OK;
 }
