@@ -73,12 +73,13 @@ __device__ __forceinline__ int mono_rank(int code, int tnb) {
 }
 
 // rank of an untransformed value (guesses only; never decides a count)
-constexpr int MONO_TAB = 128;
-__device__ __forceinline__ int nominal_rank(float xf, const Geo& geo, int tnb) {
+// `fine` sub-divisions per bin: rank 0 below the domain, then fine ranks per bin, then above.
+constexpr int MONO_TAB = 512;
+__device__ __forceinline__ int nominal_rank(float xf, const Geo& geo, int tnb, int fine) {
   const double x = (double)xf;
   if (!(x >= geo.lo[0])) return 0;
-  if (!(x < geo.hi[0])) return tnb + 2;
-  return min((int)((x - geo.lo[0]) * geo.sc[0]), tnb) + 1;
+  if (!(x < geo.hi[0])) return (tnb + 1) * fine + 1;
+  return min((int)((x - geo.lo[0]) * (geo.sc[0] * fine)), (tnb + 1) * fine - 1) + 1;
 }
 
 template <int NOPS, unsigned CODES>
@@ -110,24 +111,29 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
   batch_owner_init(S, Q, mine, tid);
   __syncthreads();
   // Nominal edge table: s_tab[k] = first position whose rank WITHOUT systematics reaches
-  // r0_nom + k.  A lane's threshold falls into one nominal bin, so its float bisection starts
-  // from that bin's samples instead of the whole range: fewer steps, and the lanes no longer
+  // r0_nom + k, on a grid of up to 16 sub-divisions per bin.  A lane's threshold falls into one
+  // cell, so its float bisection starts from that cell's samples instead of the whole range: fewer steps, and the lanes no longer
   // probe positions a power-of-two stride apart (for n near k * 4096 those shared one bank:
   // the CTA with n = 28671 took twice as long over its guesses as its neighbours).
-  const int r0_nom = n > 0 ? nominal_rank(s_x[0], geo, tnb) : 0;
-  const int r1_nom = n > 0 ? nominal_rank(s_x[n - 1], geo, tnb) : 0;
-  const int ntab = (r1_nom - r0_nom + 2 <= MONO_TAB) ? r1_nom - r0_nom + 2 : 0;    // 0: span too wide, no table
+  int fine = 16, r0_nom = 0, ntab = 0;
+  for (; fine >= 1 && n > 0; fine >>= 1) {          // the finest table that fits
+    r0_nom = nominal_rank(s_x[0], geo, tnb, fine);
+    const int span = nominal_rank(s_x[n - 1], geo, tnb, fine) - r0_nom + 2;
+    if (span <= MONO_TAB) { ntab = span; break; }
+  }
+  if (fine < 1) fine = 1;                             // ntab == 0: span too wide, no table
   for (int k = tid; k < ntab; k += MONO_THREADS) {
     int a0 = 0, a1 = n;
     while (a0 < a1) {
       const int mid = (a0 + a1) >> 1;
-      if (nominal_rank(s_x[mid], geo, tnb) < r0_nom + k) a0 = mid + 1; else a1 = mid;
+      if (nominal_rank(s_x[mid], geo, tnb, fine) < r0_nom + k) a0 = mid + 1; else a1 = mid;
     }
     s_tab[k] = a0;
   }
   __syncthreads();
 
   const int nsyst = job.nsyst;
+  const double inv_sc = 1.0 / geo.sc[0];
   int op_code[FAST_MAX_OPS];
 #pragma unroll
   for (int k = 0; k < FAST_MAX_OPS; ++k) op_code[k] = k < nsyst ? job.code[k] : 0;
@@ -178,6 +184,7 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
               else if (type == SXMC_SYST_CTSCALE) { aff_a *= op_onep[k]; aff_b = 1.0 + (aff_b - 1.0) * op_onep[k]; }
             }
           }
+          const double inv_a = 1.0 / aff_a;
           auto rank_at = [&](int p) {
             return mono_rank(mono_code<NOPS, CODES>(s_x[p], op_code, op_c0, op_onep, nsyst, geo), tnb);
           };
@@ -207,13 +214,13 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
             if (active) {
               auto pred = [&](int p) { return (rank_at(p) - t) * dir >= 0; };
               const int rb = dir > 0 ? t : t + 1;          // rank whose lower boundary is crossed
-              const double bv = rb <= tnb + 1 ? geo.lo[0] + (double)(rb - 1) / geo.sc[0] : geo.hi[0];
-              const float thr = (float)((bv - aff_b) / aff_a);
+              const double bv = rb <= tnb + 1 ? geo.lo[0] + (double)(rb - 1) * inv_sc : geo.hi[0];
+              const float thr = (float)((bv - aff_b) * inv_a);      // reciprocals: two FP64 divisions per edge were a third of the guess
               int p0 = n >> 1;
               if (thr == thr) {
                 int a0 = 0, a1 = n;                        // first sample >= thr (floats only)
                 if (ntab) {
-                  const int kk = min(max(nominal_rank(thr, geo, tnb) - r0_nom, 0), ntab - 1);
+                  const int kk = min(max(nominal_rank(thr, geo, tnb, fine) - r0_nom, 0), ntab - 1);
                   a0 = s_tab[kk];
                   a1 = kk + 1 < ntab ? s_tab[kk + 1] : n;
                 }
