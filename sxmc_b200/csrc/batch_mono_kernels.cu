@@ -7,10 +7,11 @@
 // so over samples SORTED by x the bin index is a monotone step function, and a histogram is
 // fully described by the positions at which the index changes.  Every CTA keeps a contiguous
 // range of the sorted samples in shared memory (plain float array, loaded once per launch).
-// For one chain, a warp evaluates the two ends of the range and then each lane bisects for one
-// bin edge: ~log2(n) evaluations per EDGE instead of one per SAMPLE, every evaluation being the
-// reference's arithmetic on an actual sample, so the counts are bit-identical to the
-// sample-by-sample pass.  The warps of a CTA (32) work on as many different chains at once.
+// For one chain, the two ends of the range give the ranks it spans, and every bin edge in
+// between is found by one thread: a float guess, then a few evaluations of the reference's
+// exact arithmetic on actual samples -- per EDGE instead of per SAMPLE, so the counts are
+// bit-identical to the sample-by-sample pass.  The (chain, edge) pairs of all chains form one
+// flat list shared by the CTA's 1024 threads.
 // The host cuts the ranges so that every CTA sees about the same number of edges (sparse tails
 // get few samples, the dense core is limited by shared-memory capacity) -- plan_chain_batch_mono.
 //
@@ -28,9 +29,6 @@
 #define SXMC_MONO_THREADS 1024
 #endif
 #define BATCH_THREADS SXMC_MONO_THREADS
-#ifndef SXMC_MONO_DBG_CTA
-#define SXMC_MONO_DBG_CTA 70   // the CTA whose per-chain clocks tools/prof_batch.py prints
-#endif
 #include "batch_device.cuh"
 
 #include <algorithm>
@@ -82,13 +80,26 @@ __device__ __forceinline__ int nominal_rank(float xf, const Geo& geo, int tnb, i
   return min((int)((x - geo.lo[0]) * (geo.sc[0] * fine)), (tnb + 1) * fine - 1) + 1;
 }
 
+// Per-launch scratch in front of the samples in dynamic shared memory.
+struct MonoShared {
+  double par[BATCH_MAX_CHAINS][FAST_MAX_OPS];   // every chain's systematic coefficients
+  double inv_a[BATCH_MAX_CHAINS];               // the chain's program as an affine map x' = a x + b:
+  double aff_b[BATCH_MAX_CHAINS];               //   1 / a and b (guesses only; never decide a count)
+  int rf[BATCH_MAX_CHAINS];                     // rank of the range's first / last sample under the chain
+  int rl[BATCH_MAX_CHAINS];
+  int off[BATCH_MAX_CHAINS + 1];                // exclusive scan of the chains' edge counts
+  int wsum[8];
+  int tab[MONO_TAB];                            // nominal edge table
+};
+constexpr size_t MONO_SHARED_BYTES = (sizeof(MonoShared) + 127) & ~(size_t)127;
+
 template <int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(MONO_THREADS, 1)
 chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_constant__ BatchParams Q) {
-  extern __shared__ __align__(16) float s_x[];       // this CTA's sorted samples
+  extern __shared__ __align__(128) unsigned char s_dyn[];
+  MonoShared& X = *reinterpret_cast<MonoShared*>(s_dyn);
+  float* const s_x = reinterpret_cast<float*>(s_dyn + MONO_SHARED_BYTES);   // this CTA's sorted samples
   __shared__ BatchShared S;
-  __shared__ double s_par[BATCH_MAX_CHAINS][FAST_MAX_OPS];   // every chain's systematic coefficients
-  __shared__ int s_tab[MONO_TAB];
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -110,11 +121,12 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
   const int mine = blockIdx.x < (unsigned)nch ? (int)blockIdx.x : -1;
   batch_owner_init(S, Q, mine, tid);
   __syncthreads();
-  // Nominal edge table: s_tab[k] = first position whose rank WITHOUT systematics reaches
+  // Nominal edge table: tab[k] = first position whose rank WITHOUT systematics reaches
   // r0_nom + k, on a grid of up to 16 sub-divisions per bin.  A lane's threshold falls into one
-  // cell, so its float bisection starts from that cell's samples instead of the whole range: fewer steps, and the lanes no longer
-  // probe positions a power-of-two stride apart (for n near k * 4096 those shared one bank:
-  // the CTA with n = 28671 took twice as long over its guesses as its neighbours).
+  // cell, so its float bisection starts from that cell's samples instead of the whole range:
+  // fewer steps, and the lanes no longer probe positions a power-of-two stride apart (for n near
+  // k * 4096 those shared one bank: the CTA with n = 28671 took twice as long over its guesses
+  // as its neighbours).
   int fine = 16, r0_nom = 0, ntab = 0;
   for (; fine >= 1 && n > 0; fine >>= 1) {          // the finest table that fits
     r0_nom = nominal_rank(s_x[0], geo, tnb, fine);
@@ -128,7 +140,7 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
       const int mid = (a0 + a1) >> 1;
       if (nominal_rank(s_x[mid], geo, tnb, fine) < r0_nom + k) a0 = mid + 1; else a1 = mid;
     }
-    s_tab[k] = a0;
+    X.tab[k] = a0;
   }
   __syncthreads();
 
@@ -139,6 +151,18 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
   for (int k = 0; k < FAST_MAX_OPS; ++k) op_code[k] = k < nsyst ? job.code[k] : 0;
   const unsigned total_super = Q.nsteps + (Q.do_init ? 1u : 0u);
 
+  // chain e's program constants, as bin_samples forms them (src/pdfz.cpp:310-314)
+  auto load_ops = [&](int e, double (&op_c0)[FAST_MAX_OPS], double (&op_onep)[FAST_MAX_OPS]) {
+#pragma unroll
+    for (int k = 0; k < FAST_MAX_OPS; ++k) {
+      op_c0[k] = 0.0; op_onep[k] = 1.0;
+      if (k < nsyst) {
+        op_c0[k] = __dadd_rn(0.0, __dmul_rn(X.par[e][k], 1.0));
+        op_onep[k] = __dadd_rn(1.0, op_c0[k]);
+      }
+    }
+  };
+
 #define BKM_STAMP(slot)                                                              \
   do {                                                                               \
     if (Q.stamps && tid == 0 && s == 20u) Q.stamps[blockIdx.x * 8 + (slot)] = globaltimer_ns(); \
@@ -148,142 +172,162 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
     const bool bin_now = Q.rebin || mode == NLL_MODE_INIT;
     BKM_STAMP(0);
 
-    // ---- bin: warp w takes chains w, w + MONO_WARPS, ... ---------------------------------------------
+    // ---- bin ----------------------------------------------------------------------------------
+    // A chain's histogram over this range is the set of positions where its rank steps.  The
+    // (chain, edge) pairs of ALL chains form one flat list that the 1024 threads share, one
+    // pair per thread per pass -- no lane idles because a chain has fewer than 32 edges here.
+    // Edge at position p between the run of rank r and the run of rank r': +p to r, -p to r'
+    // (unsigned wrap-around: the sums are exact once every edge has been added).
     if (bin_now) {
       if (n > 0) {
-        // all chains' coefficients in one round of loads (a warp would otherwise pay an L2 round
-        // trip per chain)
+        // (1) all chains' coefficients in one round of loads
         for (int q = tid; q < nch * FAST_MAX_OPS; q += MONO_THREADS) {
           const int e = q / FAST_MAX_OPS, k = q % FAST_MAX_OPS;
           double par = 0.0;
           if (k < nsyst && job.npars[k]) par = __ldcg(&Q.st[e].proposed[nsources + job.pidx[k]]);
-          s_par[e][k] = par;
+          X.par[e][k] = par;
         }
         __syncthreads();
-        for (int e = warp; e < nch; e += MONO_WARPS) {
-          const bool dbg = Q.stamps && s == 20u && blockIdx.x == SXMC_MONO_DBG_CTA && tid == 0 && e == 0;
-          long long tq0 = 0, tq1 = 0, tq2 = 0, tq3 = 0;
-          if (dbg) tq0 = clock64();
+        // (2) every chain's rank at the two ends of the range, and its affine map
+        for (int q = tid; q < 2 * nch; q += MONO_THREADS) {
+          const int e = q >> 1;
           double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
+          load_ops(e, op_c0, op_onep);
+          const int r = mono_rank(mono_code<NOPS, CODES>(s_x[(q & 1) ? n - 1 : 0], op_code, op_c0, op_onep, nsyst, geo), tnb);
+          if (q & 1) {
+            X.rl[e] = r;
+          } else {
+            X.rf[e] = r;
+            double aff_a = 1.0, aff_b = 0.0;
 #pragma unroll
-          for (int k = 0; k < FAST_MAX_OPS; ++k) {
-            op_c0[k] = 0.0; op_onep[k] = 1.0;
-            if (k < nsyst) {
-              op_c0[k] = __dadd_rn(0.0, __dmul_rn(s_par[e][k], 1.0));      // src/pdfz.cpp:310-314
-              op_onep[k] = __dadd_rn(1.0, op_c0[k]);
+            for (int k = 0; k < FAST_MAX_OPS; ++k) {
+              if (k < nsyst) {
+                const int type = op_code[k] & 15;
+                if (type == SXMC_SYST_SHIFT) aff_b += op_c0[k];
+                else if (type == SXMC_SYST_SCALE) { aff_a *= op_onep[k]; aff_b *= op_onep[k]; }
+                else if (type == SXMC_SYST_CTSCALE) { aff_a *= op_onep[k]; aff_b = 1.0 + (aff_b - 1.0) * op_onep[k]; }
+              }
+            }
+            X.inv_a[e] = 1.0 / aff_a;
+            X.aff_b[e] = aff_b;
+          }
+        }
+        __syncthreads();
+        // (3) edge counts, their exclusive scan, and the run that is still open at the end of
+        // the range (rank rl, ends at n)
+        int ne = 0, incl = 0;
+        if (tid < 160) {
+          if (tid < nch) {
+            const int rl = X.rl[tid];
+            ne = abs(rl - X.rf[tid]);
+            if (rl >= 1 && rl <= tnb + 1) {
+              unsigned* const hist = Q.hist + (size_t)tid * Q.hist_words;
+              atomicAdd(hist + (size_t)ns * tnb + job_j, (unsigned)n);
+              if (rl <= tnb) atomicAdd(hist + (size_t)job_j * tnb + (rl - 1), (unsigned)n);
             }
           }
-          // the program as an affine map (guesses only; never decides a count)
-          double aff_a = 1.0, aff_b = 0.0;
+          incl = ne;
 #pragma unroll
-          for (int k = 0; k < FAST_MAX_OPS; ++k) {
-            if (k < nsyst) {
-              const int type = op_code[k] & 15;
-              if (type == SXMC_SYST_SHIFT) aff_b += op_c0[k];
-              else if (type == SXMC_SYST_SCALE) { aff_a *= op_onep[k]; aff_b *= op_onep[k]; }
-              else if (type == SXMC_SYST_CTSCALE) { aff_a *= op_onep[k]; aff_b = 1.0 + (aff_b - 1.0) * op_onep[k]; }
-            }
+          for (int d = 1; d < 32; d <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
           }
-          const double inv_a = 1.0 / aff_a;
+          if (lane == 31) X.wsum[warp] = incl;
+        }
+        __syncthreads();
+        if (tid < 160) {
+          int base = 0;
+          for (int w = 0; w < warp; ++w) base += X.wsum[w];
+          if (tid <= nch) X.off[tid] = base + incl - ne;
+        }
+        __syncthreads();
+        const int total_edges = X.off[nch];
+        // (4) one (chain, edge) pair per thread per pass
+        for (int g = tid; g < total_edges; g += MONO_THREADS) {
+          int e = 0;
+          {
+            int a = 0, b = nch - 1;                  // largest e with off[e] <= g
+            while (a < b) {
+              const int mid = (a + b + 1) >> 1;
+              if (X.off[mid] <= g) a = mid; else b = mid - 1;
+            }
+            e = a;
+          }
+          const int k = g - X.off[e];
+          double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
+          load_ops(e, op_c0, op_onep);
           auto rank_at = [&](int p) {
             return mono_rank(mono_code<NOPS, CODES>(s_x[p], op_code, op_c0, op_onep, nsyst, geo), tnb);
           };
-          unsigned* const hist = Q.hist + (size_t)e * Q.hist_words + (size_t)job_j * tnb;
-          unsigned norm = 0;
-          auto add = [&](int rank, unsigned k) {      // k samples whose code has this rank
-            if (k && rank >= 1 && rank <= tnb + 1) {
-              norm += k;
-              if (rank <= tnb) atomicAdd(hist + (rank - 1), k);
+          const int r_first = X.rf[e];
+          const int dir = X.rl[e] >= r_first ? 1 : -1;
+          const int t = r_first + dir * (k + 1);
+          // first position whose rank has reached t (exists: the last sample has rank rl).
+          // A guess comes from inverting the affine map in plain floating point and a float-only
+          // bisection of the samples; the answer is then settled with the exact arithmetic:
+          // gallop away from the guess, bisect what is left (usually two evaluations in all).
+          int lo = 0, hi = n - 1;
+          auto pred = [&](int p) { return (rank_at(p) - t) * dir >= 0; };
+          const int rb = dir > 0 ? t : t + 1;          // rank whose lower boundary is crossed
+          const double bv = rb <= tnb + 1 ? geo.lo[0] + (double)(rb - 1) * inv_sc : geo.hi[0];
+          const float thr = (float)((bv - X.aff_b[e]) * X.inv_a[e]);
+          int p0 = n >> 1;
+          if (thr == thr) {
+            int a0 = 0, a1 = n;                        // first sample >= thr (floats only)
+            if (ntab) {
+              const int kk = min(max(nominal_rank(thr, geo, tnb, fine) - r0_nom, 0), ntab - 1);
+              a0 = X.tab[kk];
+              a1 = kk + 1 < ntab ? X.tab[kk + 1] : n;
             }
-          };
-          const int r_first = rank_at(0), r_last = rank_at(n - 1);
-          const int dir = r_last >= r_first ? 1 : -1;
-          const int nedges = (r_last - r_first) * dir;
-          if (dbg) tq1 = clock64();
-          int prev = 0;                               // start of the run that is still open
-          for (int e0 = 0; e0 < nedges; e0 += 32) {
-            const int k = e0 + lane;
-            const bool active = k < nedges;
-            const int t = r_first + dir * (k + 1);
-            // first position whose rank has reached t (exists: the last sample has rank r_last).
-            // A guess comes from inverting the affine map x' = aff_a x + aff_b in plain floating
-            // point and a float-only bisection of the samples; the answer is then settled with
-            // the exact arithmetic: gallop away from the guess, bisect what is left (usually two
-            // evaluations in all).
-            int lo = 0, hi = n - 1;
-            if (active) {
-              auto pred = [&](int p) { return (rank_at(p) - t) * dir >= 0; };
-              const int rb = dir > 0 ? t : t + 1;          // rank whose lower boundary is crossed
-              const double bv = rb <= tnb + 1 ? geo.lo[0] + (double)(rb - 1) * inv_sc : geo.hi[0];
-              const float thr = (float)((bv - aff_b) * inv_a);      // reciprocals: two FP64 divisions per edge were a third of the guess
-              int p0 = n >> 1;
-              if (thr == thr) {
-                int a0 = 0, a1 = n;                        // first sample >= thr (floats only)
-                if (ntab) {
-                  const int kk = min(max(nominal_rank(thr, geo, tnb, fine) - r0_nom, 0), ntab - 1);
-                  a0 = s_tab[kk];
-                  a1 = kk + 1 < ntab ? s_tab[kk + 1] : n;
-                }
-                while (a0 < a1) {
-                  const int mid = (a0 + a1) >> 1;
-                  if (s_x[mid] < thr) a0 = mid + 1; else a1 = mid;
-                }
-                p0 = min(a0, n - 1);
-              }
-              if (dbg) tq2 = clock64();
-              // the guess and its two neighbours, evaluated together (the answer is almost
-              // always one of them)
-              const int pm = max(p0 - 1, 0), pp = min(p0 + 1, n - 1);
-              const bool f_m = pred(pm), f_0 = pred(p0), f_p = pred(pp);
-              if (f_0) {
-                hi = p0;
-                if (p0 == 0) {
-                  lo = 0;
-                } else if (!f_m) {
-                  lo = p0;
-                } else {
-                  hi = pm;
-                  int step = 1;
-                  while (hi > 0) {
-                    const int q = max(hi - step, 0);
-                    if (pred(q)) { hi = q; step <<= 1; } else { lo = q + 1; break; }
-                  }
-                  if (hi == 0) lo = 0;
-                }
-              } else if (f_p) {
-                lo = hi = pp;
-              } else {
-                lo = pp + 1;
-                int step = 1;
-                while (lo < hi) {
-                  const int q = min(lo + step - 1, hi);
-                  if (pred(q)) { hi = q; break; }
-                  lo = q + 1;
-                  step <<= 1;
-                }
-              }
-              while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if (pred(mid)) hi = mid; else lo = mid + 1;
-              }
+            while (a0 < a1) {
+              const int mid = (a0 + a1) >> 1;
+              if (s_x[mid] < thr) a0 = mid + 1; else a1 = mid;
             }
-            const int pos = active ? lo : n;
-            const int up = __shfl_up_sync(0xffffffffu, pos, 1);
-            const int start = lane == 0 ? prev : up;
-            if (active) add(t - dir, (unsigned)(pos - start));
-            const int lastk = min(31, nedges - 1 - e0);
-            prev = __shfl_sync(0xffffffffu, pos, lastk);
+            p0 = min(a0, n - 1);
           }
-          if (dbg) tq3 = clock64();
-          if (lane == 0) add(r_last, (unsigned)(n - prev));
-          const unsigned wn = __reduce_add_sync(0xffffffffu, norm);
-          if (lane == 0 && wn) atomicAdd(Q.hist + (size_t)e * Q.hist_words + (size_t)ns * tnb + job_j, wn);
-          if (dbg) {
-            unsigned long long* d = Q.stamps + 148 * 8;
-            d[0] = (unsigned long long)(tq1 - tq0); d[1] = (unsigned long long)(tq2 - tq1);
-            d[2] = (unsigned long long)(tq3 - tq2); d[3] = (unsigned long long)(clock64() - tq3);
-            d[4] = (unsigned long long)nedges; d[5] = (unsigned long long)n;
+          // the guess and its two neighbours, evaluated together (the answer is almost always
+          // one of them)
+          const int pm = max(p0 - 1, 0), pp = min(p0 + 1, n - 1);
+          const bool f_m = pred(pm), f_0 = pred(p0), f_p = pred(pp);
+          if (f_0) {
+            hi = p0;
+            if (p0 == 0) {
+              lo = 0;
+            } else if (!f_m) {
+              lo = p0;
+            } else {
+              hi = pm;
+              int step = 1;
+              while (hi > 0) {
+                const int q = max(hi - step, 0);
+                if (pred(q)) { hi = q; step <<= 1; } else { lo = q + 1; break; }
+              }
+              if (hi == 0) lo = 0;
+            }
+          } else if (f_p) {
+            lo = hi = pp;
+          } else {
+            lo = pp + 1;
+            int step = 1;
+            while (lo < hi) {
+              const int q = min(lo + step - 1, hi);
+              if (pred(q)) { hi = q; break; }
+              lo = q + 1;
+              step <<= 1;
+            }
           }
+          while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (pred(mid)) hi = mid; else lo = mid + 1;
+          }
+          // the run of rank t - dir ends at lo, the run of rank t starts there
+          unsigned* const hist = Q.hist + (size_t)e * Q.hist_words;
+          const unsigned pos = (unsigned)lo;
+          const int ra = t - dir;
+          const bool in_a = ra >= 1 && ra <= tnb + 1, in_t = t >= 1 && t <= tnb + 1;
+          if (in_a && ra <= tnb) atomicAdd(hist + (size_t)job_j * tnb + (ra - 1), pos);
+          if (in_t && t <= tnb) atomicAdd(hist + (size_t)job_j * tnb + (t - 1), 0u - pos);
+          if (in_a != in_t) atomicAdd(hist + (size_t)ns * tnb + job_j, in_a ? pos : 0u - pos);
         }
       }
       BKM_STAMP(1);
@@ -319,7 +363,7 @@ static const MonoEntry g_mono_table[] = {
     {1, OPC(SXMC_SYST_SCALE, 0, 0), chain_batch_mono_kernel<1, OPC(SXMC_SYST_SCALE, 0, 0)>},
 };
 
-constexpr size_t MONO_STATIC_RESERVE = 52 * 1024;   // BatchShared + slack
+constexpr size_t MONO_STATIC_RESERVE = 56 * 1024;   // BatchShared (static) + MonoShared (dynamic) + slack
 constexpr size_t MONO_CAP_SAMPLES = (227 * 1024 - MONO_STATIC_RESERVE) / sizeof(float);
 
 // nominal (no systematics) rank of a sample, on the host: only used to balance the ranges
@@ -445,7 +489,7 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
     }
   }
   plan->grid = sms;
-  plan->smem_bytes = ((size_t)max_n * sizeof(float) + 127) & ~(size_t)127;
+  plan->smem_bytes = MONO_SHARED_BYTES + (((size_t)max_n * sizeof(float) + 127) & ~(size_t)127);
   plan->max_edges = max_edges;
   plan->prog_nops = L.prog_nops;
   plan->prog_codes = L.prog_codes;

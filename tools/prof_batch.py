@@ -28,14 +28,15 @@ def main():
     raw = np.zeros(148 * 8 + 16, dtype=np.uint64)
     _lib.check(L.sxmc_batch_phase_stamps(mb._b, 1, raw.ctypes.data_as(C.POINTER(C.c_uint64))))
     t = raw[:148 * 8].reshape(148, 8).astype(np.int64)
-    print("  one chain in one warp (CTA 70) [clk]: setup+ends %d, guess %d, exact+add %d, tail %d; edges %d, n %d" % tuple(int(v) for v in raw[148 * 8:148 * 8 + 6]))
     base = t[:, 0].min()
     rel = (t[:, :6] - base) / 1e3
     per = 1e3 * mb.loop_ms() / (a.steps + 1)
     print("workload %s, %d chains: %.1f us/super-step = %.3f us/chain-step (path, max edges = %s)" %
           (a.workload, a.chains, per, per / a.chains, mb.last_path()))
-    names = ["start", "bin done", "barrier1 out", "lookup done", "tail done", "barrier2 out"]
+    names = ["start", "bin done", "barrier1 out", None, "tail done", "barrier2 out"]
     for k, n in enumerate(names):
+        if n is None:
+            continue
         print("  %-13s min/mean/max %8.2f %8.2f %8.2f us" % (n, rel[:, k].min(), rel[:, k].mean(), rel[:, k].max()))
     d = rel[:, 1] - rel[:, 0]
     print("  bin phase per CTA: min/mean/max %.2f %.2f %.2f us -> %.3f us per chain (mean)" %
