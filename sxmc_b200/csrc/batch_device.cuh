@@ -49,7 +49,8 @@ __device__ __forceinline__ void batch_owner_init(BatchShared& S, const BatchPara
 // reduce (src/pdfz.cpp:411-436, src/nll_kernels.cpp:89-146), then finish_step; the histogram is
 // cleared for the next super-step's bin phase.  All threads of the CTA call it.
 __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchParams& Q, int mine, int mode,
-                                                  int tnb, int tid, bool clear) {
+                                                  int tnb, int tid, bool clear,
+                                                  unsigned long long* stamp = nullptr) {
   const int ns = Q.ns, np = Q.np;
   unsigned* const my_hist = Q.hist + (size_t)mine * Q.hist_words;
   FinState& F = S.F;
@@ -85,6 +86,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
       S.pdf[q] = v;
     }
     __syncthreads();
+    if (stamp && tid == 0) stamp[3] = globaltimer_ns();
     const unsigned* mult = Q.mult + (size_t)mine * tnb;
     for (int b = tid; b < tnb; b += BATCH_THREADS) {
       const unsigned m = mult[b];
@@ -109,9 +111,11 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
   }
   const double total = block_sum<BATCH_THREADS>(sum, S.warp);   // ends past a CTA barrier: lookups done
   if (tid == 0) S.warp[0] = total;
+  if (stamp && tid == 0) stamp[6] = globaltimer_ns();
   if (clear)     // rebuilt from zero by the next super-step's bin phase (the last one is kept)
     for (unsigned long long w = tid; w < Q.hist_words; w += BATCH_THREADS) my_hist[w] = 0u;
   __syncthreads();
+  if (stamp && tid == 0) stamp[7] = globaltimer_ns();
   if (tid < 32) finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid);
   __syncthreads();
 }

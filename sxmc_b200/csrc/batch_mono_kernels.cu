@@ -338,7 +338,9 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
     }
 
     // ---- lookup + event likelihood + tail of the chain this CTA owns ---------------------------
-    if (mine >= 0) batch_lookup_tail(S, Q, mine, mode, tnb, tid, Q.rebin && s + 1 < total_super);
+    if (mine >= 0)
+      batch_lookup_tail(S, Q, mine, mode, tnb, tid, Q.rebin && s + 1 < total_super,
+                        (Q.stamps && s == 20u) ? Q.stamps + blockIdx.x * 8 : nullptr);
     BKM_STAMP(4);
     if (Q.rebin && s + 1 < total_super) {      // proposals published, histograms cleared
       cta_arrive(bar);

@@ -29,13 +29,15 @@ def main():
     _lib.check(L.sxmc_batch_phase_stamps(mb._b, 1, raw.ctypes.data_as(C.POINTER(C.c_uint64))))
     t = raw[:148 * 8].reshape(148, 8).astype(np.int64)
     base = t[:, 0].min()
-    rel = (t[:, :6] - base) / 1e3
+    rel = (t[:, :8] - base) / 1e3
     per = 1e3 * mb.loop_ms() / (a.steps + 1)
     print("workload %s, %d chains: %.1f us/super-step = %.3f us/chain-step (path, max edges = %s)" %
           (a.workload, a.chains, per, per / a.chains, mb.last_path()))
-    names = ["start", "bin done", "barrier1 out", None, "tail done", "barrier2 out"]
+    names = ["start", "bin done", "barrier1 out", "pdf table", "tail done", "barrier2 out", "event sum", "hist cleared"]
     for k, n in enumerate(names):
-        if n is None:
+        if k in (3, 6, 7):
+            own = rel[:a.chains, k]        # only CTAs that own a chain stamp these
+            print("  %-13s min/mean/max %8.2f %8.2f %8.2f us" % (n, own.min(), own.mean(), own.max()))
             continue
         print("  %-13s min/mean/max %8.2f %8.2f %8.2f us" % (n, rel[:, k].min(), rel[:, k].mean(), rel[:, k].max()))
     d = rel[:, 1] - rel[:, 0]
