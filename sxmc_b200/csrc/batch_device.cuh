@@ -27,6 +27,8 @@ struct BatchShared {
   FinState F;
   int ok;
   long long ne;
+  double pre_z[SXMC_MAX_PARAMETERS];   // the step's normals / uniform, drawn ahead of the serial tail
+  double pre_u;
   float pdf[BATCH_PDF_TABLE];      // PDF values of every (signal, bin) at the proposed point (grouped lookup)
 };
 
@@ -50,10 +52,14 @@ __device__ __forceinline__ void batch_owner_init(BatchShared& S, const BatchPara
 // cleared for the next super-step's bin phase.  All threads of the CTA call it.
 __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchParams& Q, int mine, int mode,
                                                   int tnb, int tid, bool clear,
-                                                  unsigned long long* stamp = nullptr) {
+                                                  unsigned long long* stamp = nullptr,
+                                                  bool have_m0 = false, unsigned m0 = 0u) {
   const int ns = Q.ns, np = Q.np;
   unsigned* const my_hist = Q.hist + (size_t)mine * Q.hist_words;
   FinState& F = S.F;
+  // the last warp draws the step's random numbers while the others look up the events
+  const bool pre_rng = pre_rng_applies(F, mode);
+  if (pre_rng && tid >= BATCH_THREADS - 32) pre_rng_draw(F, np, tid & 31, S.pre_z, &S.pre_u);
   if (tid < ns) {
     const unsigned norm = __ldcg(my_hist + (size_t)ns * tnb + tid);
     const float eff = (float)(1.0 * norm / S.nmc[tid]);                    // nll_kernels.cpp:105
@@ -89,7 +95,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     if (stamp && tid == 0) stamp[3] = globaltimer_ns();
     const unsigned* mult = Q.mult + (size_t)mine * tnb;
     for (int b = tid; b < tnb; b += BATCH_THREADS) {
-      const unsigned m = mult[b];
+      const unsigned m = (have_m0 && b == tid) ? m0 : mult[b];   // m0: the caller's register copy of mult[tid]
       if (!m) continue;
       double acc = 0;
       for (int j = 0; j < ns; ++j) acc = __dadd_rn(acc, __dmul_rn(S.c[j], (double)S.pdf[j * tnb + b]));
@@ -116,7 +122,10 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     for (unsigned long long w = tid; w < Q.hist_words; w += BATCH_THREADS) my_hist[w] = 0u;
   __syncthreads();
   if (stamp && tid == 0) stamp[7] = globaltimer_ns();
-  if (tid < 32) finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid);
+  if (tid < 32)
+    finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid,
+                pre_rng ? S.pre_z : nullptr, pre_rng ? &S.pre_u : nullptr,
+                (stamp && mine == 0) ? reinterpret_cast<long long*>(stamp + BATCH_MAX_CHAINS * 8) : nullptr);
   __syncthreads();
 }
 

@@ -163,6 +163,10 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
     }
   };
 
+  // the owned chain's event multiplicities do not change during a launch: bin `tid`'s in a register
+  const bool have_m0 = mine >= 0 && Q.mult != nullptr && tid < tnb;
+  const unsigned m0 = have_m0 ? __ldg(Q.mult + (size_t)mine * tnb + tid) : 0u;
+
 #define BKM_STAMP(slot)                                                              \
   do {                                                                               \
     if (Q.stamps && tid == 0 && s == 20u) Q.stamps[blockIdx.x * 8 + (slot)] = globaltimer_ns(); \
@@ -340,7 +344,7 @@ chain_batch_mono_kernel(const __grid_constant__ MonoParams M, const __grid_const
     // ---- lookup + event likelihood + tail of the chain this CTA owns ---------------------------
     if (mine >= 0)
       batch_lookup_tail(S, Q, mine, mode, tnb, tid, Q.rebin && s + 1 < total_super,
-                        (Q.stamps && s == 20u) ? Q.stamps + blockIdx.x * 8 : nullptr);
+                        (Q.stamps && s == 20u) ? Q.stamps + blockIdx.x * 8 : nullptr, have_m0, m0);
     BKM_STAMP(4);
     if (Q.rebin && s + 1 < total_super) {      // proposals published, histograms cleared
       cta_arrive(bar);

@@ -222,6 +222,10 @@ struct ChainState {
   double* nll_trace;                      // optional [nsteps]
   double* prop_trace;                     // optional [nsteps][nparameters]
   double last_nll, last_event_sum;        // results of an evaluate-only pass
+  // lookup_nll_kernel: the step's random numbers, drawn by block 0 while the other blocks look
+  // up events, read by whichever block finishes last (Philox is stateless: counter = step)
+  double pre_z[SXMC_MAX_PARAMETERS];
+  double pre_u;
 };
 
 // ---- fake-data generator (ensemble_kernels.cu) ---------------------------------------------

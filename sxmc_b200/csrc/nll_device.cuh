@@ -121,6 +121,21 @@ __device__ __forceinline__ double fin_normal(const FinState& F, unsigned step, u
   return sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
 }
 
+// The random numbers of the step F.step is about to take (one warp; lane-strided over the
+// parameters), so that a warp with nothing else to do can draw them off the serial tail.
+// Not applicable with tapes (consumed in order) or outside NLL_MODE_STEP.
+__device__ __forceinline__ bool pre_rng_applies(const FinState& F, int mode) {
+  return mode == NLL_MODE_STEP && !F.tape_normals && !F.tape_uniforms;
+}
+__device__ __forceinline__ void pre_rng_draw(const FinState& F, int np, int lane, double* z, double* u) {
+  for (int k = lane; k < np; k += 32)
+    z[k] = F.jump_width[k] > 0 ? fin_normal(F, F.step, (unsigned)k, 1u) : 0.0;
+  if (lane == 31) {
+    const uint4 r = fin_random(F, F.step, 0u, 2u);
+    *u = u01(r.x, r.y);
+  }
+}
+
 // pre_z (optional): the step's normals, computed ahead of time by an idle warp
 static __device__ void propose(FinState& F, ChainState* st, int np, unsigned step_for_rng, unsigned purpose,
                         int lane, const double* pre_z = nullptr) {
@@ -155,7 +170,10 @@ static __device__ void propose(FinState& F, ChainState* st, int np, unsigned ste
 // s_term: nsignals normalisation terms + nparameters constraint terms, filled beforehand.
 static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, int nsources, double ev_new,
                             int mode, const double* s_term, int lane,
-                            const double* pre_z = nullptr, const double* pre_u = nullptr) {
+                            const double* pre_z = nullptr, const double* pre_u = nullptr,
+                            long long* clk = nullptr) {
+#define FIN_CLK(i) do { if (clk && lane == 0) clk[i] = clock64(); } while (0)
+  FIN_CLK(0);
   // --- burn-in re-tune of the jump widths (src/mcmc.cpp:274-311), before this step's decision
   const unsigned step = F.step;
   bool reset_stats = false;
@@ -200,6 +218,7 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
     }
   }
   nll = __shfl_sync(0xffffffffu, nll, 0);
+  FIN_CLK(1);
 
   if (mode == NLL_MODE_EVAL_ONLY) {
     if (lane == 0) { st->last_nll = nll; st->last_event_sum = ev; }
@@ -234,6 +253,7 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
     if (accept) { F.current_nll = nll; st->current_nll = nll; F.accepted += 1; st->accepted = F.accepted; }
   }
   accept = __shfl_sync(0xffffffffu, accept, 0);
+  FIN_CLK(2);
   const double cur_nll = __shfl_sync(0xffffffffu, F.current_nll, 0);
   const bool store = row < F.row_cap;
   float* out = F.rows + row * (np + 1);
@@ -262,7 +282,10 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
     st->step = F.step;
   }
   __syncwarp();
+  FIN_CLK(3);
   propose(F, st, np, step, 1u, lane, pre_z);
+  FIN_CLK(4);
+#undef FIN_CLK
 }
 
 }  // namespace sxmc

@@ -28,6 +28,8 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   __shared__ double s_term[NLL_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
   __shared__ int s_last;
   __shared__ FinState F;
+  __shared__ double s_z[SXMC_MAX_PARAMETERS];
+  __shared__ double s_u;
 
   const int tid = threadIdx.x;
   const long long gtid = blockIdx.x * (long long)NLL_THREADS + tid;
@@ -42,6 +44,11 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   // clear the histogram buffer the NEXT step bins into (double-buffered; nobody reads it now)
   for (unsigned long long w = gtid; w < zero_words; w += gstride) zero_ptr[w] = 0u;
   __syncthreads();
+
+  // block 0's last warp draws the step's random numbers while everybody looks up events; the
+  // block that finishes last picks them up (ordered by block 0's ticket, as its partial sum is)
+  const bool pre_rng = pre_rng_applies(F, mode);
+  if (pre_rng && blockIdx.x == 0 && tid >= NLL_THREADS - 32) pre_rng_draw(F, np, tid & 31, st->pre_z, &st->pre_u);
 
   if (tid < ns) {
     const int j = tid;
@@ -121,8 +128,14 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   for (int b = tid; b < (int)gridDim.x; b += NLL_THREADS) acc += __ldcg(partials + b);
   const double total = block_sum<NLL_THREADS>(acc, s_warp);
   if (tid == 0) { s_warp[0] = total; *ticket = 0u; }
+  if (pre_rng) {
+    for (int k = tid; k < np; k += NLL_THREADS) s_z[k] = __ldcg(st->pre_z + k);
+    if (tid == 0) s_u = __ldcg(&st->pre_u);
+  }
   __syncthreads();
-  if (tid < 32) finish_step(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid);
+  if (tid < 32)
+    finish_step(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid, pre_rng ? s_z : nullptr,
+                pre_rng ? &s_u : nullptr);
 }
 
 int nll_grid_for(long long nevents) {

@@ -28,6 +28,9 @@ def main():
     raw = np.zeros(148 * 8 + 16, dtype=np.uint64)
     _lib.check(L.sxmc_batch_phase_stamps(mb._b, 1, raw.ctypes.data_as(C.POINTER(C.c_uint64))))
     t = raw[:148 * 8].reshape(148, 8).astype(np.int64)
+    c = raw[148 * 8:148 * 8 + 5].astype(np.int64)
+    print("  finish_step of chain 0 [clk]: nll total %d, decide %d, row + stats %d, propose %d" %
+          tuple(int(c[i + 1] - c[i]) for i in range(4)))
     base = t[:, 0].min()
     rel = (t[:, :8] - base) / 1e3
     per = 1e3 * mb.loop_ms() / (a.steps + 1)
