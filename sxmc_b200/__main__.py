@@ -6,7 +6,7 @@ Differences forced by the missing ROOT: sample files are .npz/.npy/.csv/.f32 tab
 (``sxmc_b200.config.read_float_table``); each experiment's likelihood space is written as
 ``<output_path>/<output_prefix>_<i>.npy`` (float32 rows, one column per parameter plus
 "likelihood") with the column names in ``<output_prefix>_columns.json`` instead of a TNtuple in
-a .root file; no plots; only the contour error estimator.
+a .root file; no plots; the projection estimator is a host restatement (ensemble.projection_interval).
 
 Under ``torch.distributed.run`` (one process per GPU) experiment ``i`` runs on rank
 ``i mod N`` and rank 0 prints the gathered limits."""
@@ -45,9 +45,6 @@ def main(argv=None):
     fc = config.FitConfig(argv[1])
     if rank == 0:
         fc.print()
-    if fc.error_type != "contour":
-        raise config.ConfigError("error_type '%s' needs ROOT's histogram fit; only 'contour' is available"
-                                 % fc.error_type)
     if fc.samples:
         raise config.ConfigError("fit.samples (re-reading a saved .root likelihood space) needs ROOT")
 
@@ -62,6 +59,11 @@ def main(argv=None):
                               seed=fc.seed, rank=rank, world=world, keep_chains=True)
         limits = r["limits"]
         columns = fit.names["sources"] + ["%s_%d" % (y.name, j) for y in fc.systematics for j in range(y.npars)]
+        if fc.error_type == "projection":          # ERROR_PROJECTION: host estimator on the chain rows
+            limits = []
+            for rows in r["chains"]:
+                best = ensemble.projection_intervals(rows, columns + ["likelihood"], fc.confidence)
+                limits.append(best[fc.signal_name].upper if fc.signal_name in best else float("nan"))
         for i, rows, n in zip(r["experiments"], r["chains"], r["observed"]):
             print("Experiment %d / %d: %d fake events, %d chain rows, limit %g"
                   % (i + 1, fc.nexperiments, int(np.sum(n)), rows.shape[0], limits[r["experiments"].index(i)]))
@@ -77,6 +79,8 @@ def main(argv=None):
             ls = chain(data, fc.nsteps, fc.burnin_fraction, fc.debug_mode)
             best_fit, lmin = ensemble.contour_intervals(chain, fc.confidence)
             columns = chain.parameter_names[:-1]
+            if fc.error_type == "projection":
+                best_fit = ensemble.projection_intervals(ls.get_samples(), chain.parameter_names, fc.confidence)
             print("-- Best fit --")
             for name in columns:
                 iv = best_fit[name]

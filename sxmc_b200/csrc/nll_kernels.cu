@@ -14,7 +14,8 @@ constexpr int NLL_THREADS = 256;
 constexpr int NLL_MAX_SIGNALS = 128;
 
 // =========================================================================================
-__global__ void __launch_bounds__(NLL_THREADS)
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
 lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict__ norms, int ns,
                   int np, int nsources, long long ne, ChainState* st, double* partials,
                   unsigned* ticket, int mode, float* lut, unsigned* zero_ptr,
@@ -24,7 +25,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   __shared__ const unsigned* s_bins[NLL_MAX_SIGNALS];
   __shared__ const int* s_rb[NLL_MAX_SIGNALS];
   __shared__ int s_nb[NLL_MAX_SIGNALS];
-  __shared__ double s_warp[NLL_THREADS / 32];
+  __shared__ double s_warp[THREADS / 32];
   __shared__ double s_term[NLL_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
   __shared__ int s_last;
   __shared__ FinState F;
@@ -32,10 +33,10 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   __shared__ double s_u;
 
   const int tid = threadIdx.x;
-  const long long gtid = blockIdx.x * (long long)NLL_THREADS + tid;
-  const long long gstride = (long long)gridDim.x * NLL_THREADS;
+  const long long gtid = blockIdx.x * (long long)THREADS + tid;
+  const long long gstride = (long long)gridDim.x * THREADS;
 
-  prefetch_state(F, st, np, tid, NLL_THREADS);
+  prefetch_state(F, st, np, tid, THREADS);
   // per-signal tables; norms[j] is addressed directly so that it does not wait for sigs[j]
   NllSignal my_sig;
   unsigned my_norm = 0;
@@ -48,7 +49,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   // block 0's last warp draws the step's random numbers while everybody looks up events; the
   // block that finishes last picks them up (ordered by block 0's ticket, as its partial sum is)
   const bool pre_rng = pre_rng_applies(F, mode);
-  if (pre_rng && blockIdx.x == 0 && tid >= NLL_THREADS - 32) pre_rng_draw(F, np, tid & 31, st->pre_z, &st->pre_u);
+  if (pre_rng && blockIdx.x == 0 && tid >= THREADS - 32) pre_rng_draw(F, np, tid & 31, st->pre_z, &st->pre_u);
 
   if (tid < ns) {
     const int j = tid;
@@ -63,7 +64,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     s_term[j] = __dmul_rn(rate, (double)my_norm) / (double)my_sig.n_mc;
   }
   // Gaussian constraints (nll_kernels.cpp:176-185)
-  for (int i = tid; i < np; i += NLL_THREADS) {
+  for (int i = tid; i < np; i += THREADS) {
     const double sg = F.sigmas[i];
     double t = 0;
     if (sg > 0) {
@@ -112,25 +113,35 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     }
     if (s > 0) sum += log(s);
   }
-  const double bsum = block_sum<NLL_THREADS>(sum, s_warp);
-  if (tid == 0) {
-    partials[blockIdx.x] = bsum;
-    __threadfence();
-    const unsigned t = atomicAdd(ticket, 1u);
-    s_last = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!s_last) return;
+  const double bsum = block_sum<THREADS>(sum, s_warp);
+  if (gridDim.x == 1) {
+    // small fit, one block (launch_nll): no partials, no ticket round trip, no second reduction
+    if (tid == 0) s_warp[0] = bsum;
+    __syncthreads();                 // also orders the last warp's pre_z / pre_u stores before the loads below
+    if (pre_rng) {
+      for (int k = tid; k < np; k += THREADS) s_z[k] = __ldcg(st->pre_z + k);
+      if (tid == 0) s_u = __ldcg(&st->pre_u);
+    }
+  } else {
+    if (tid == 0) {
+      partials[blockIdx.x] = bsum;
+      __threadfence();
+      const unsigned t = atomicAdd(ticket, 1u);
+      s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
 
-  // ---- last block: total the partials in a fixed order, then finish the step -------------
-  __threadfence();
-  double acc = 0;
-  for (int b = tid; b < (int)gridDim.x; b += NLL_THREADS) acc += __ldcg(partials + b);
-  const double total = block_sum<NLL_THREADS>(acc, s_warp);
-  if (tid == 0) { s_warp[0] = total; *ticket = 0u; }
-  if (pre_rng) {
-    for (int k = tid; k < np; k += NLL_THREADS) s_z[k] = __ldcg(st->pre_z + k);
-    if (tid == 0) s_u = __ldcg(&st->pre_u);
+    // ---- last block: total the partials in a fixed order, then finish the step -------------
+    __threadfence();
+    double acc = 0;
+    for (int b = tid; b < (int)gridDim.x; b += THREADS) acc += __ldcg(partials + b);
+    const double total = block_sum<THREADS>(acc, s_warp);
+    if (tid == 0) { s_warp[0] = total; *ticket = 0u; }
+    if (pre_rng) {
+      for (int k = tid; k < np; k += THREADS) s_z[k] = __ldcg(st->pre_z + k);
+      if (tid == 0) s_u = __ldcg(&st->pre_u);
+    }
   }
   __syncthreads();
   if (tid < 32)
@@ -150,10 +161,18 @@ int launch_nll(const NllLaunch& L, cudaStream_t stream) {
     set_error("more than 128 signals in one fit are not supported by the NLL kernel");
     return SXMC_EINVAL;
   }
-  lookup_nll_kernel<<<L.grid, NLL_THREADS, 0, stream>>>(L.sigs_dev, L.norms_dev, L.nsignals,
-                                                        L.nparameters, L.nsources, L.nevents, L.state,
-                                                        L.partials, L.ticket, L.mode, L.lut,
-                                                        L.zero_ptr, L.zero_words, L.mult, L.mult_nbins);
+  // Grouped lookup over a few thousand bins: one block does it all, which drops the partial-sum
+  // hand-over (store, fence, ticket, last block's reload: ~3 us of dependent round trips) from a
+  // kernel that is latency from end to end.  1024 threads: one bin per thread for workload B.
+  if (L.mult && !L.lut && L.mult_nbins <= 4096 && L.zero_words <= 65536) {
+    lookup_nll_kernel<1024><<<1, 1024, 0, stream>>>(L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources,
+                                                    L.nevents, L.state, L.partials, L.ticket, L.mode, L.lut,
+                                                    L.zero_ptr, L.zero_words, L.mult, L.mult_nbins);
+  } else {
+    lookup_nll_kernel<NLL_THREADS><<<L.grid, NLL_THREADS, 0, stream>>>(
+        L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources, L.nevents, L.state, L.partials, L.ticket,
+        L.mode, L.lut, L.zero_ptr, L.zero_words, L.mult, L.mult_nbins);
+  }
   SXMC_CUDA(cudaGetLastError());
   return SXMC_OK;
 }

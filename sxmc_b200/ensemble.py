@@ -12,6 +12,7 @@ Experiments are independent: with ``world`` ranks, experiment ``i`` runs on rank
 with Philox stream id ``i`` (the reference's single gRandom stream is replaced by one
 counter-based stream per experiment, so the result does not depend on the number of GPUs)."""
 import ctypes as C
+import math
 import time
 from dataclasses import dataclass
 from statistics import NormalDist
@@ -147,6 +148,103 @@ def rows_contour(rows, cl):
     finally:
         lib().sxmc_buf_free(dev)
     return lo, up, pt, float(lmin.value), int(nc.value)
+
+
+def _root_axis_limits(xmin, xmax, nbins=100):
+    """Histogram axis the way TTree::Draw("x>>h") picks it: THLimitsFinder::Optimize rounds the
+    bin width up to 1, 2 or 5 x 10^k and the edges to multiples of it (restated from the published
+    CERNLIB/ROOT algorithm; ROOT is not on this image, so this is unpinned)."""
+    al, ah = float(xmin), float(xmax)
+    if al == ah:
+        ah = al + 1.0
+    awidth = (ah - al) / nbins
+    jlog = int(math.floor(math.log10(awidth)))
+    sigfig = awidth * 10.0 ** (-jlog)
+    if sigfig <= 1:
+        sig = 1.0
+    elif sigfig <= 2:
+        sig = 2.0
+    elif sigfig <= 5:
+        sig = 5.0
+    else:
+        sig, jlog = 1.0, jlog + 1
+    bwid = sig * 10.0 ** jlog
+    lwid = math.floor(al / bwid)
+    kwid = math.floor(ah / bwid + 1.00001)
+    return bwid * lwid, bwid * kwid, int(kwid - lwid)
+
+
+def projection_interval(values, cl, nbins=100):
+    """sxmc::errors::Projection::get_interval (src/error_estimators/projection.cpp:14-77) on one
+    column of the chain.  Host code: the 1-D projection (`LikelihoodSpace::get_projection`,
+    src/likelihood.cpp:76-85 = TTree::Draw into an auto-binned TH1F), a chi-square Gaussian fit of
+    its bins (TH1::Fit("gaus"): bins with content, error sqrt(n)) for the mode, then the
+    reference's bin walk: one-sided limit when less than cl/2 of the probability lies at or
+    below the mode's bin, else cl/2 to each side.  The walk is the reference's arithmetic; the axis
+    finder and the fit restate ROOT (unpinned)."""
+    from scipy.optimize import least_squares
+    v = np.asarray(values, dtype=np.float32).astype(np.float64)
+    if v.size == 0:
+        raise ValueError("projection_interval: empty chain")
+    lo, hi, nb = _root_axis_limits(v.min(), v.max(), nbins)
+    width = (hi - lo) / nb
+    idx = np.floor((v - lo) / width).astype(np.int64)
+    content = np.zeros(nb + 2)                         # [0] underflow, [1..nb], [nb+1] overflow
+    np.add.at(content, np.clip(idx + 1, 0, nb + 1), 1.0)
+    centers = lo + (np.arange(nb) + 0.5) * width
+    y = content[1:nb + 1]
+    use = y > 0
+    mean = float(np.average(centers, weights=np.maximum(y, 0))) if y.sum() > 0 else float(v.mean())
+    rms = float(np.sqrt(np.average((centers - mean) ** 2, weights=y))) if y.sum() > 0 else 0.0
+    mu = mean
+    if use.sum() >= 3 and rms > 0:
+        def resid(p):
+            return (p[0] * np.exp(-0.5 * ((centers[use] - p[1]) / p[2]) ** 2) - y[use]) / np.sqrt(y[use])
+        fit = least_squares(resid, [float(y.max()), mean, rms])
+        mu = float(fit.x[1])
+    total = content.sum()                              # Integral(0, -1) includes under/overflow
+
+    def integral(a, b):
+        return content[max(a, 0):min(b, nb + 1) + 1].sum() if b >= a else 0.0
+
+    def find_bin(x):
+        return 0 if x < lo else (nb + 1 if x >= hi else int((x - lo) / width) + 1)
+
+    low_edge = lambda i: lo + (i - 1) * width
+    out = Interval(cl=float(np.float32(cl)))
+    imax = find_bin(mu)
+    out.point_estimate = mu
+    if imax < 1:
+        imax = 1
+        out.point_estimate = low_edge(1)
+    ilo, ihi = 1, 0
+    if integral(0, imax) / total < cl / 2:
+        out.one_sided = True
+        for i in range(nb + 1):
+            if integral(0, i) / total >= cl:
+                ihi = i
+                break
+    else:
+        out.one_sided = False
+        for i in range(imax, 0, -1):
+            if integral(i, imax) / total >= cl / 2:
+                ilo = i
+                break
+        for i in range(imax + 1, nb + 1):
+            if integral(imax + 1, i) / total >= cl / 2:
+                ihi = i
+                break
+    out.coverage = float(integral(ilo, ihi) / total)
+    out.lower = float(low_edge(ilo))
+    out.upper = float(low_edge(ihi) + width)
+    return out
+
+
+def projection_intervals(rows, names, cl):
+    """{parameter: Interval} with ERROR_PROJECTION (LikelihoodSpace::extract_best_fit,
+    src/likelihood.cpp:104-137) from host rows [n, nparameters+1]."""
+    rows = np.asarray(rows)
+    return {name: projection_interval(rows[:, k], cl) for k, name in enumerate(names[:-1])}
 
 
 def _fit_objects(fit, hists):

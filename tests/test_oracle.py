@@ -138,3 +138,23 @@ def test_port_matches_committed_ref_fixtures():
         assert l.tobytes() == z[name + "_lut"].tobytes()
         v, e = port.nll(fit, l, pars, n)
         assert v == float(z[name + "_nll"]) and e == float(z[name + "_evsum"])
+
+
+def test_projection_estimator_walk_on_known_shapes():
+    """sxmc::errors::Projection (src/error_estimators/projection.cpp:14-77), host restatement:
+    a Gaussian column gives a central interval with about cl coverage around the mean; a column
+    piled up at zero (a rate with no signal) gives a one-sided limit at the cl quantile."""
+    from sxmc_b200 import ensemble
+    rng = np.random.default_rng(3)
+    g = rng.normal(5.0, 0.5, 200000).astype(np.float32)
+    iv = ensemble.projection_interval(g, 0.683)
+    assert not iv.one_sided and abs(iv.point_estimate - 5.0) < 0.01
+    assert 0.683 <= iv.coverage < 0.75                      # whole bins: at least cl
+    assert abs(iv.lower - 4.5) < 0.06 and abs(iv.upper - 5.5) < 0.06
+    e = rng.exponential(1.0, 200000).astype(np.float32)     # mode at the lower edge
+    iv = ensemble.projection_interval(e, 0.9)
+    assert iv.one_sided and abs(iv.upper - np.quantile(e, 0.9)) < 0.15 and iv.coverage >= 0.9
+    lo, hi, nb = ensemble._root_axis_limits(0.0, 9.7, 100)
+    assert (lo, nb) == (0.0, 98) and abs(hi - 9.8) < 1e-12  # width 0.097 -> 0.1
+    out = ensemble.projection_intervals(np.stack([g, e, g], axis=1), ["a", "b", "likelihood"], 0.683)
+    assert set(out) == {"a", "b"}
