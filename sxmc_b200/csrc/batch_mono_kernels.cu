@@ -427,7 +427,40 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
     set_error("chain batch: the samples do not fit in shared memory (not a small fit)");
     return SXMC_ESTATE;
   }
-  // CTAs per job: its capacity minimum, the rest in proportion to the bin edges it spans
+  // greedy cut of job j for an edge budget E: the ranges needed (optionally listed as pos, count)
+  auto cut = [&](int j, int E, std::vector<unsigned>* out) {
+    const unsigned n = (unsigned)nsamples[j];
+    int count = 0;
+    unsigned pos = 0;
+    while (pos < n) {
+      // rank at pos = largest t with edge[t] <= pos
+      const int r = (int)(std::upper_bound(edge[j].begin(), edge[j].end(), pos) - edge[j].begin()) - 1;
+      const int lim = std::min(nranks, r + E);
+      unsigned next = edge[j][lim];
+      if (next <= pos) next = n;
+      next = std::min<unsigned>(next, pos + (unsigned)MONO_CAP_SAMPLES);
+      next = std::min(next, n);
+      if (out) { out->push_back(pos); out->push_back(next - pos); }
+      pos = next;
+      ++count;
+    }
+    return count;
+  };
+  // smallest edge budget with which job j fits into c CTAs (nranks + 1: it does not fit at all)
+  auto budget = [&](int j, int c) {
+    if (!nsamples[j]) return 0;
+    if (c < (int)need[j]) return nranks + 1;
+    int lo = 1, hi = nranks;
+    while (lo < hi) {
+      const int mid = (lo + hi) / 2;
+      if (cut(j, mid, nullptr) <= c) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+  };
+  // CTAs per job: its capacity minimum, the rest in proportion to the bin edges it spans; then
+  // CTAs move from the job with the smallest edge budget to the one with the largest while that
+  // lowers the largest (capacity-limited ranges in a dense core hold few edges, so a job's
+  // budget is not simply span / CTAs: the super-step waits for the slowest CTA)
   std::vector<int> ctas(nj);
   int used = 0;
   for (int j = 0; j < nj; ++j) { ctas[j] = (int)need[j]; used += ctas[j]; }
@@ -442,6 +475,29 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
     if (best < 0) break;
     ctas[best] += 1;
     used += 1;
+  }
+  std::vector<int> bud(nj);
+  for (int j = 0; j < nj; ++j) bud[j] = budget(j, ctas[j]);
+  for (int round = 0; round < 4 * sms; ++round) {
+    int jmax = -1, jmin = -1;
+    for (int j = 0; j < nj; ++j) {
+      if (!nsamples[j]) continue;
+      if (jmax < 0 || bud[j] > bud[jmax]) jmax = j;
+    }
+    int best_after = jmax < 0 ? 0 : bud[jmax];
+    int give_bud = 0, take_bud = 0;
+    if (jmax < 0) break;
+    const int after_take = budget(jmax, ctas[jmax] + 1);
+    for (int j = 0; j < nj; ++j) {
+      if (j == jmax || !nsamples[j] || ctas[j] <= (int)need[j] || ctas[j] <= 1) continue;
+      const int after_give = budget(j, ctas[j] - 1);
+      int worst = std::max(after_take, after_give);
+      for (int q = 0; q < nj; ++q) if (q != j && q != jmax && nsamples[q]) worst = std::max(worst, bud[q]);
+      if (worst < best_after) { best_after = worst; jmin = j; give_bud = after_give; take_bud = after_take; }
+    }
+    if (jmin < 0) break;
+    ctas[jmin] -= 1; bud[jmin] = give_bud;
+    ctas[jmax] += 1; bud[jmax] = take_bud;
   }
   MonoParams& M = plan->params;
   memset(&M, 0, sizeof M);
@@ -462,31 +518,9 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
     }
     const unsigned n = (unsigned)nsamples[j];
     if (!n) continue;
-    // greedy cut for a given edge budget E: ranges needed
-    auto cut = [&](int E, std::vector<unsigned>* out) {
-      int count = 0;
-      unsigned pos = 0;
-      while (pos < n) {
-        // rank at pos = largest t with edge[t] <= pos
-        const int r = (int)(std::upper_bound(edge[j].begin(), edge[j].end(), pos) - edge[j].begin()) - 1;
-        const int lim = std::min(nranks, r + E);
-        unsigned next = edge[j][lim];
-        if (next <= pos) next = n;
-        next = std::min<unsigned>(next, pos + (unsigned)MONO_CAP_SAMPLES);
-        next = std::min(next, n);
-        if (out) { out->push_back(pos); out->push_back(next - pos); }
-        pos = next;
-        ++count;
-      }
-      return count;
-    };
-    int lo = 1, hi = nranks;
-    while (lo < hi) {
-      const int mid = (lo + hi) / 2;
-      if (cut(mid, nullptr) <= ctas[j]) hi = mid; else lo = mid + 1;
-    }
+    const int lo = bud[j];
     std::vector<unsigned> ranges;
-    const int got = cut(lo, &ranges);
+    const int got = cut(j, lo, &ranges);
     if (got > ctas[j]) { set_error("monotone chain batch: partition failed"); return SXMC_ESTATE; }
     max_edges = std::max(max_edges, lo);
     for (int q = 0; q < ctas[j]; ++q, ++cta) {
