@@ -567,5 +567,16 @@ def main():
         torch.distributed.destroy_process_group()
 
 
+def _only_json_on_stdout():
+    """Libraries under us print to stdout now and then (NCCL's version banner, the reference's
+    progress lines in the CPU arm).  The contract is ONE JSON line there: everything written to
+    fd 1 while the run lasts goes to stderr, and print() is pointed at the real stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real
+
+
 if __name__ == "__main__":
+    _only_json_on_stdout()
     main()
