@@ -60,6 +60,16 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
   // the last warp draws the step's random numbers while the others look up the events
   const bool pre_rng = pre_rng_applies(F, mode);
   if (pre_rng && tid >= BATCH_THREADS - 32) pre_rng_draw(F, np, tid & 31, S.pre_z, &S.pre_u);
+  // Small grouped fits (one bin per thread, a handful of signals): the bin's counts go straight
+  // to registers, and the loads are issued before the norm-dependent stage instead of after it
+  // (one L2 round trip and the shared-memory table less on a path that is latency end to end).
+  constexpr int DIRECT_NS = 4;
+  const bool direct = Q.mult != nullptr && tnb <= BATCH_THREADS && ns <= DIRECT_NS;
+  unsigned hreg[DIRECT_NS];
+  if (direct && tid < tnb) {
+#pragma unroll
+    for (int j = 0; j < DIRECT_NS; ++j) hreg[j] = j < ns ? __ldcg(my_hist + (size_t)j * tnb + tid) : 0u;
+  }
   if (tid < ns) {
     const unsigned norm = __ldcg(my_hist + (size_t)ns * tnb + tid);
     const float eff = (float)(1.0 * norm / S.nmc[tid]);                    // nll_kernels.cpp:105
@@ -80,7 +90,24 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
   __syncthreads();
   const long long my_ne = S.ne;
   double sum = 0;
-  if (Q.mult) {
+  if (direct) {
+    if (tid < tnb) {
+      const unsigned m = have_m0 ? m0 : Q.mult[(size_t)mine * tnb + tid];
+      if (m) {
+        double acc = 0;
+#pragma unroll
+        for (int j = 0; j < DIRECT_NS; ++j) {
+          if (j < ns) {
+            float v = (float)((double)hreg[j] / S.bn[j]);                       // pdfz.cpp:429-432
+            if (isnan(v)) v = 0.0f;                                              // nll_kernels.cpp:107
+            acc = __dadd_rn(acc, __dmul_rn(S.c[j], (double)v));
+          }
+        }
+        if (acc > 0) sum += (double)m * log(acc);
+      }
+    }
+    if (stamp && tid == 0) stamp[3] = globaltimer_ns();
+  } else if (Q.mult) {
     // Grouped lookup.  Every signal reads the same dataset, so events in the same bin have the
     // same likelihood: sum_i log(s_i) = sum_b m_b log(s_b), m_b = events of this chain in bin b
     // (counted once when the data were set).  eval_pdf's division runs once per (signal, bin)
