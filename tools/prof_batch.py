@@ -13,11 +13,14 @@ def main():
     ap.add_argument("--chains", type=int, default=148)
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--reverse", action="store_true", help="signals in reverse order (does a slow CTA follow its samples?)")
     a = ap.parse_args()
     from sxmc_b200 import _lib, mcmc, workloads
     L = _lib.lib()
     _lib.check(L.sxmc_init(0))
     fit = workloads.WORKLOADS[a.workload](a.scale)
+    if a.reverse:
+        fit.signals.reverse()
     hists, mb = mcmc.build_fit(fit, batch=a.chains)
     for k in range(a.chains):
         mb.set_seed(k, 5, k)
