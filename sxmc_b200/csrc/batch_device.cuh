@@ -149,8 +149,8 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     for (unsigned long long w = tid; w < Q.hist_words; w += BATCH_THREADS) my_hist[w] = 0u;
   __syncthreads();
   if (stamp && tid == 0) stamp[7] = globaltimer_ns();
-  if (tid < 32)
-    finish_step(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid,
+  if (tid < 64)
+    finish_step2(F, Q.st + mine, np, ns, Q.nsources, S.warp[0], mode, S.term, tid & 31, tid >> 5,
                 pre_rng ? S.pre_z : nullptr, pre_rng ? &S.pre_u : nullptr,
                 (stamp && mine == 0) ? reinterpret_cast<long long*>(stamp + BATCH_MAX_CHAINS * 8) : nullptr);
   __syncthreads();

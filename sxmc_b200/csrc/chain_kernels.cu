@@ -195,8 +195,8 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
       }
       __syncthreads();
       PK_STAMP(5);
-      if (tid < 32)
-        finish_step(F, Q.st, np, ns, nsources, s_warp[0], NLL_MODE_STEP, s_term, tid,
+      if (tid < 64)
+        finish_step2(F, Q.st, np, ns, nsources, s_warp[0], NLL_MODE_STEP, s_term, tid & 31, tid >> 5,
                     pre_rng ? s_z : nullptr, pre_rng ? &s_u : nullptr);
       __syncthreads();
       PK_STAMP(6);

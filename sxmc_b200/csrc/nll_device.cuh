@@ -64,6 +64,7 @@ struct FinState {
   float* rows;
   double* nll_trace;
   double* prop_trace;
+  int accept_flag;          // finish_step2: the decision, handed from warp 0 to warp 1
 };
 
 __device__ __forceinline__ void prefetch_state(FinState& F, const ChainState* st, int np, int tid,
@@ -285,6 +286,147 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
   FIN_CLK(3);
   propose(F, st, np, step, 1u, lane, pre_z);
   FIN_CLK(4);
+#undef FIN_CLK
+}
+
+// The same step finished by TWO warps (threads 0..63 of the CTA call it with wid = warp index):
+// the tail is a single warp's chain of dependent instructions (~900 of them, ~7 cycles each), and
+// after the decision its two halves are independent -- warp 0 draws the next proposal while
+// warp 1 appends the row and updates the running sums.  Both read what they need of
+// current/proposed into registers, meet at a 64-thread barrier, then write.  Falls back to
+// finish_step (warp 0 alone) outside NLL_MODE_STEP and for more than 32 parameters.
+__device__ __forceinline__ void fin_bar64() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
+
+static __device__ void finish_step2(FinState& F, ChainState* st, int np, int ns, int nsources, double ev_new,
+                                    int mode, const double* s_term, int lane, int wid,
+                                    const double* pre_z = nullptr, const double* pre_u = nullptr,
+                                    long long* clk = nullptr) {
+  if (np > 32 || mode != NLL_MODE_STEP) {
+    if (wid == 0) finish_step(F, st, np, ns, nsources, ev_new, mode, s_term, lane, pre_z, pre_u, clk);
+    return;
+  }
+#define FIN_CLK(i) do { if (clk && wid == 0 && lane == 0) clk[i] = clock64(); } while (0)
+  FIN_CLK(0);
+  const unsigned step = F.step;
+  const bool retune = step == F.burnin_steps || step == 2 * F.burnin_steps;
+  const bool reset_stats = retune && !F.debug_mode;
+  if (wid == 0) {
+    // --- burn-in re-tune of the jump widths (src/mcmc.cpp:274-311), before this step's decision
+    if (retune) {
+      const double n = F.stat_n;
+      if (lane < np && !F.fixed[lane]) {
+        double rms = 0;
+        if (n > 0) {
+          const double m = F.stat_sx[lane] / n;
+          rms = sqrt(fabs(__dadd_rn(F.stat_sxx[lane] / n, -__dmul_rn(m, m))));
+        }
+        const double fit_width = rms > 0 ? rms : (double)F.jump_width[lane];
+        F.jump_width[lane] = (float)__dmul_rn((double)F.scale_factor, fit_width);
+        st->jump_width[lane] = F.jump_width[lane];
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      // --- nll_total_device (src/nll_kernels.cpp:150-188), terms summed in the reference's order
+      if (!isnan(ev_new)) { F.event_total = ev_new; st->event_total = ev_new; }   // :113-115
+      const double ev = F.event_total;
+      double nll;
+      double sum = -ev;
+      if (isnan(sum)) {
+        nll = 1e18;
+      } else {
+        for (int i = 0; i < ns; ++i) sum = __dadd_rn(sum, s_term[i]);
+        bool bad = false;
+        for (int i = 0; i < np; ++i) {
+          if (i < nsources && F.proposed[i] < 0) { bad = true; break; }
+          if (F.sigmas[i] > 0) sum = __dadd_rn(sum, s_term[ns + i]);
+        }
+        nll = bad ? 1e18 : sum;
+      }
+      FIN_CLK(1);
+      // --- jump_decider_device (src/nll_kernels.cpp:57-86)
+      st->proposed_nll = nll;
+      if (F.nll_trace) F.nll_trace[step] = nll;
+      double u;
+      if (F.tape_uniforms) {
+        u = F.i_uniform < F.n_uniforms ? F.tape_uniforms[F.i_uniform] : 0.5;
+        F.i_uniform += 1;
+        st->i_uniform = F.i_uniform;
+      } else if (pre_u) {
+        u = *pre_u;
+      } else {
+        const uint4 r = fin_random(F, step, 0u, 2u);
+        u = u01(r.x, r.y);
+      }
+      const double nc = F.current_nll;
+      const int accept = (F.debug_mode || (nll < nc || u <= exp(nc - nll))) ? 1 : 0;
+      if (accept) { F.current_nll = nll; st->current_nll = nll; F.accepted += 1; st->accepted = F.accepted; }
+      F.accept_flag = accept;
+      FIN_CLK(2);
+    }
+  }
+  fin_bar64();                                   // the decision is visible to both warps
+  const int accept = F.accept_flag;
+  const int k = lane;
+  if (wid == 0) {
+    // --- pick_new_vector_device (src/nll_kernels.cpp:31-53) from the point the chain is at now
+    const bool floating = k < np && F.jump_width[k] > 0;
+    const unsigned m = __ballot_sync(0xffffffffu, floating);
+    double v = 0;
+    if (k < np) {
+      v = accept ? F.proposed[k] : F.current[k];
+      if (floating) {
+        double z;
+        if (F.tape_normals) {
+          const unsigned long long ti = F.i_normal + __popc(m & ((1u << lane) - 1));
+          z = ti < F.n_normals ? F.tape_normals[ti] : 0.0;
+        } else {
+          z = pre_z ? pre_z[k] : fin_normal(F, step, (unsigned)k, 1u);
+        }
+        v = __dadd_rn(v, __dmul_rn((double)F.jump_width[k], z));
+      }
+    }
+    fin_bar64();                                 // warp 1 has read the old proposal
+    if (k < np) { F.proposed[k] = v; st->proposed[k] = v; }
+    if (lane == 0 && F.tape_normals) { F.i_normal += __popc(m); st->i_normal = F.i_normal; }
+    FIN_CLK(3);
+    FIN_CLK(4);
+  } else {
+    // --- the ntuple row and the running sums of the burn-in RMS (src/nll_kernels.cpp:78-84)
+    const double stat_n0 = reset_stats ? 0.0 : F.stat_n;
+    const long long row = reset_stats ? 0 : F.nrows;
+    const double cur_nll = F.current_nll;
+    const bool store = row < F.row_cap;
+    float* out = F.rows + row * (np + 1);
+    double oldp = 0, cur = 0, sx0 = 0, sxx0 = 0;
+    if (k < np) {
+      oldp = F.proposed[k];
+      cur = accept ? oldp : F.current[k];
+      sx0 = reset_stats ? 0.0 : F.stat_sx[k];
+      sxx0 = reset_stats ? 0.0 : F.stat_sxx[k];
+    }
+    fin_bar64();                                 // warp 0 has read current / proposed
+    if (k < np) {
+      if (F.prop_trace) F.prop_trace[(unsigned long long)step * np + k] = oldp;
+      if (accept) { F.current[k] = cur; st->current[k] = cur; }
+      const float xf = (float)cur;
+      if (store) out[k] = xf;
+      const double x = (double)xf;
+      F.stat_sx[k] = __dadd_rn(sx0, x);
+      F.stat_sxx[k] = __dadd_rn(sxx0, __dmul_rn(x, x));
+      st->stat_sx[k] = F.stat_sx[k];
+      st->stat_sxx[k] = F.stat_sxx[k];
+    }
+    if (lane == 0) {
+      if (store) out[np] = (float)cur_nll;
+      F.nrows = row + 1;
+      F.stat_n = stat_n0 + 1;
+      F.step = step + 1;
+      st->nrows = F.nrows;
+      st->stat_n = F.stat_n;
+      st->step = F.step;
+    }
+  }
 #undef FIN_CLK
 }
 

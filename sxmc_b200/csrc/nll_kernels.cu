@@ -144,8 +144,8 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     }
   }
   __syncthreads();
-  if (tid < 32)
-    finish_step(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid, pre_rng ? s_z : nullptr,
+  if (tid < 64)
+    finish_step2(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid & 31, tid >> 5, pre_rng ? s_z : nullptr,
                 pre_rng ? &s_u : nullptr);
 }
 
