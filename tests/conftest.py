@@ -18,11 +18,12 @@ def pytest_configure(config):
     lib = os.path.join(ROOT, "sxmc_b200", "libsxmc_b200.so")
     shim = os.path.join(ROOT, "sxmc_b200", "libsxmc_cxx.so")
     runner = os.path.join(ROOT, "cxx", "tests", "test_class_api")
+    sxmc_bin = os.path.join(ROOT, "cxx", "bin", "sxmc")
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(lib) and os.path.exists(nvcc):
         subprocess.run(["make", "-j4", "-C", os.path.join(ROOT, "sxmc_b200", "csrc")], check=False,
                        stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
-    if os.path.exists(lib) and not (os.path.exists(shim) and os.path.exists(runner)) and shutil.which("g++"):
+    if os.path.exists(lib) and not (os.path.exists(shim) and os.path.exists(runner) and os.path.exists(sxmc_bin)) and shutil.which("g++"):
         subprocess.run(["make", "-C", os.path.join(ROOT, "cxx")], check=False, stdout=subprocess.DEVNULL,
                        stderr=subprocess.DEVNULL)
 

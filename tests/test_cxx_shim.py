@@ -120,3 +120,53 @@ def test_class_api_runner_matches_golden_vectors_and_ctypes_chain(tmp_path):
     chain.close()
     for h in hists:
         h.close()
+
+
+SXMC_BIN = os.path.join(ROOT, "cxx", "bin", "sxmc")
+
+
+def test_cxx_command_line_usage_and_no_cpu_fallback():
+    """cxx/bin/sxmc keeps the reference's argument convention (src/sxmc.cpp:176-182) and refuses to
+    run without a device."""
+    assert os.access(SXMC_BIN, os.X_OK), "run `make -C cxx`"
+    r = subprocess.run([SXMC_BIN], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "fit_configuration.json output_path" in r.stderr
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([SXMC_BIN, "x.json", "/tmp/sxmc_no_gpu_out"], capture_output=True, text=True, timeout=60)
+        assert r.returncode == 3 and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cxx_command_line_equals_python_command_line(tmp_path):
+    """The same JSON configuration and .npy sample tables through the C++ main (FitConfig, Signal,
+    make_fake_dataset, MCMC, LikelihoodSpace in cxx/) and through `python -m sxmc_b200`: every
+    experiment's likelihood space bit for bit, the same limits."""
+    import sys
+    from tests.test_config import CONFIG
+    rng = np.random.default_rng(5)
+    for name, n, mu in (("signal1", 20000, 8.0), ("signal2", 40000, 11.0)):
+        e = rng.normal(mu, 1.5, n).astype(np.float32)
+        table = np.stack([(12 * rng.random(n) ** (1 / 3)).astype(np.float32),
+                          (e - rng.normal(0, 0.3, n)).astype(np.float32), e, np.zeros(n, np.float32)], axis=1)
+        np.save(tmp_path / (name + ".npy"), np.ascontiguousarray(table))
+        (tmp_path / (name + ".npy.fields")).write_text("radius\nmc_energy\nenergy\nunused\n")
+    cfg = tmp_path / "fit.json"
+    cfg.write_text(CONFIG.replace(".npz", ".npy"))
+    rc = subprocess.run([SXMC_BIN, str(cfg), str(tmp_path / "out_cxx")], capture_output=True, text=True, timeout=900)
+    assert rc.returncode == 0, rc.stdout[-3000:] + rc.stderr[-3000:]
+    rp = subprocess.run([sys.executable, "-m", "sxmc_b200", str(cfg), str(tmp_path / "out_py")], cwd=ROOT,
+                        capture_output=True, text=True, timeout=900)
+    assert rp.returncode == 0, rp.stdout[-3000:] + rp.stderr[-3000:]
+    for i in range(3):
+        a = np.load(tmp_path / "out_cxx" / ("example_%d.npy" % i))
+        b = np.load(tmp_path / "out_py" / ("example_%d.npy" % i))
+        assert a.shape == b.shape == (3000 - 2 * 600, 5) and a.tobytes() == b.tobytes(), i
+    cols = (tmp_path / "out_cxx" / "example_columns.txt").read_text().split()
+    assert cols == ["signal1", "signal2", "energy_resolution_0", "energy_scale_0", "likelihood"]
+
+    def limits(text):
+        line = [ln for ln in text.splitlines() if ln.startswith("sxmc: Upper limits:")][0]
+        return [float(x) for x in line.split(":", 2)[2].split(",") if x.strip()]
+    assert np.allclose(limits(rc.stdout), limits(rp.stdout), rtol=1e-5)
+    assert "sxmc: Median upper limit:" in rc.stdout
