@@ -147,64 +147,89 @@ void LikelihoodSpace::print_best_fit() const {                            // src
 
 // ---- MCMC ------------------------------------------------------------------------------
 
+// The parameter tables of MCMC::MCMC (src/mcmc.cpp:28-130) in the C ABI's form.
+namespace {
+struct ChainTables {
+  size_t nsources, nsignals, nsystematics, nparameters, nobservables, nfloat;
+  bool systematics_fixed;
+  std::vector<double> means, sigma, nexpected;
+  std::vector<int> fixed;
+  std::vector<sxmc_hist*> pdfs;
+  std::vector<unsigned> n_mc;
+  std::vector<short> source_id;
+  std::vector<std::string> names;
+  sxmc_chain_config cfg;
+
+  ChainTables(const std::vector<Source>& sources, const std::vector<Signal>& signals,
+              const std::vector<Systematic>& systematics, const std::vector<Observable>& observables)
+      : nsources(sources.size()), nsignals(signals.size()), nsystematics(systematics.size()), nparameters(0),
+        nobservables(observables.size()), nfloat(0), systematics_fixed(true) {
+    size_t npars = 0;
+    for (size_t i = 0; i < systematics.size(); ++i) npars += systematics[i].npars;
+    nparameters = nsources + npars;
+    means.resize(nparameters);
+    sigma.resize(nparameters);
+    fixed.resize(nparameters);
+    for (size_t i = 0; i < nsources; ++i) {
+      means[i] = sources[i].mean;
+      sigma[i] = sources[i].sigma;
+      fixed[i] = sources[i].fixed ? 1 : 0;
+      nfloat += sources[i].fixed ? 0 : 1;
+      names.push_back(sources[i].name);
+    }
+    size_t k = nsources;
+    for (size_t i = 0; i < systematics.size(); ++i) {
+      if (!systematics[i].fixed) systematics_fixed = false;
+      for (size_t j = 0; j < systematics[i].npars; ++j, ++k) {
+        means[k] = systematics[i].means[j];
+        sigma[k] = systematics[i].sigmas[j];
+        fixed[k] = systematics[i].fixed ? 1 : 0;
+        nfloat += systematics[i].fixed ? 0 : 1;
+        std::ostringstream oss;
+        oss << systematics[i].name << "_" << j;
+        names.push_back(oss.str());
+      }
+    }
+    names.push_back("likelihood");
+    pdfs.resize(nsignals);
+    nexpected.resize(nsignals);
+    n_mc.resize(nsignals);
+    source_id.resize(nsignals);
+    for (size_t i = 0; i < nsignals; ++i) {
+      pdfs[i] = signals[i].histogram ? signals[i].histogram->handle() : NULL;
+      nexpected[i] = signals[i].nexpected;
+      n_mc[i] = (unsigned)signals[i].n_mc;
+      source_id[i] = (short)signals[i].source.index;
+    }
+    cfg.nsources = (int)nsources;
+    cfg.nsignals = (int)nsignals;
+    cfg.nparameters = (int)nparameters;
+    cfg.nobservables = (int)nobservables;
+    cfg.parameter_means = means.data();
+    cfg.parameter_sigma = sigma.data();
+    cfg.parameter_fixed = fixed.data();
+    cfg.systematics_fixed = systematics_fixed ? 1 : 0;
+    cfg.nsystematics = (int)nsystematics;
+    cfg.pdfs = pdfs.data();
+    cfg.nexpected = nexpected.data();
+    cfg.n_mc = n_mc.data();
+    cfg.source_id = source_id.data();
+  }
+};
+}  // namespace
+
 MCMC::MCMC(const std::vector<Source>& sources, const std::vector<Signal>& signals,
            const std::vector<Systematic>& systematics, const std::vector<Observable>& observables)
     : nsources(sources.size()), nsignals(signals.size()), nsystematics(systematics.size()), nparameters(0),
       nobservables(observables.size()), nfloat(0), systematics_fixed(true), chain(NULL) {   // src/mcmc.cpp:28-130
-  size_t npars = 0;
-  for (size_t i = 0; i < systematics.size(); ++i) npars += systematics[i].npars;
-  nparameters = nsources + npars;
-  std::vector<double> means(nparameters), sigma(nparameters);
-  std::vector<int> fixed(nparameters);
-  for (size_t i = 0; i < nsources; ++i) {
-    means[i] = sources[i].mean;
-    sigma[i] = sources[i].sigma;
-    fixed[i] = sources[i].fixed ? 1 : 0;
-    nfloat += sources[i].fixed ? 0 : 1;
-    parameter_names.push_back(sources[i].name);
-  }
-  size_t k = nsources;
-  for (size_t i = 0; i < systematics.size(); ++i) {
-    if (!systematics[i].fixed) systematics_fixed = false;
-    for (size_t j = 0; j < systematics[i].npars; ++j, ++k) {
-      means[k] = systematics[i].means[j];
-      sigma[k] = systematics[i].sigmas[j];
-      fixed[k] = systematics[i].fixed ? 1 : 0;
-      nfloat += systematics[i].fixed ? 0 : 1;
-      std::ostringstream oss;
-      oss << systematics[i].name << "_" << j;
-      parameter_names.push_back(oss.str());
-    }
-  }
-  parameter_names.push_back("likelihood");
+  ChainTables t(sources, signals, systematics, observables);
+  nparameters = t.nparameters;
+  nfloat = t.nfloat;
+  systematics_fixed = t.systematics_fixed;
+  parameter_names = t.names;
   if (systematics.size() > 0 && systematics_fixed)
     std::cout << "MCMC::MCMC: All systematics are fixed, will not reevaluate PDFs." << std::endl;
-
-  std::vector<sxmc_hist*> pdfs(nsignals);
-  std::vector<double> nexpected(nsignals);
-  std::vector<unsigned> n_mc(nsignals);
-  std::vector<short> source_id(nsignals);
-  for (size_t i = 0; i < nsignals; ++i) {
-    pdfs[i] = signals[i].histogram ? signals[i].histogram->handle() : NULL;
-    nexpected[i] = signals[i].nexpected;
-    n_mc[i] = (unsigned)signals[i].n_mc;
-    source_id[i] = (short)signals[i].source.index;
-  }
-  sxmc_chain_config cfg;
-  cfg.nsources = (int)nsources;
-  cfg.nsignals = (int)nsignals;
-  cfg.nparameters = (int)nparameters;
-  cfg.nobservables = (int)nobservables;
-  cfg.parameter_means = means.data();
-  cfg.parameter_sigma = sigma.data();
-  cfg.parameter_fixed = fixed.data();
-  cfg.systematics_fixed = systematics_fixed ? 1 : 0;
-  cfg.nsystematics = (int)nsystematics;
-  cfg.pdfs = pdfs.data();
-  cfg.nexpected = nexpected.data();
-  cfg.n_mc = n_mc.data();
-  cfg.source_id = source_id.data();
-  check(sxmc_chain_create(&cfg, &chain));
+  check(sxmc_chain_create(&t.cfg, &chain));
 }
 
 MCMC::~MCMC() {
@@ -234,5 +259,71 @@ LikelihoodSpace* MCMC::operator()(std::vector<float>& data, unsigned nsteps, flo
   sxmc_chain_loop_ms(chain, &ms);
   std::cout << "MCMC: Elapsed time: " << ms * 1e-3f << "s, accepted " << acc << "/" << nsteps << " ("
             << (nsteps ? (float)acc / nsteps : 0.0f) << ")" << std::endl;   // src/mcmc.cpp:379-385
+  return new LikelihoodSpace(nt);
+}
+
+// ---- MCMCBatch -------------------------------------------------------------------------
+
+MCMCBatch::MCMCBatch(const std::vector<Source>& sources, const std::vector<Signal>& signals,
+                     const std::vector<Systematic>& systematics, const std::vector<Observable>& observables,
+                     int max_chains)
+    : nmax(max_chains), nparameters(0), nsignals(signals.size()), batch(NULL), gen(NULL) {
+  ChainTables t(sources, signals, systematics, observables);
+  nparameters = t.nparameters;
+  parameter_names = t.names;
+  int rc = sxmc_batch_create(&t.cfg, max_chains, &batch);
+  if (rc == SXMC_ESTATE) throw NotSmallFit(sxmc_last_error());
+  check(rc);
+  // the fake-data generator of the ensemble: efficiencies and sampling histograms at the
+  // systematics' means, observables' limits for the rejection test (src/generator.cpp:17-29)
+  std::vector<double> syst_vals;
+  for (size_t i = 0; i < systematics.size(); ++i)
+    for (size_t j = 0; j < systematics[i].npars; ++j) syst_vals.push_back(systematics[i].means[j]);
+  std::vector<float> upper, lower;
+  for (size_t i = 0; i < observables.size(); ++i) { upper.push_back(observables[i].upper); lower.push_back(observables[i].lower); }
+  rc = sxmc_generator_create(t.pdfs.data(), (int)t.pdfs.size(), t.nexpected.data(), t.n_mc.data(),
+                             syst_vals.empty() ? NULL : syst_vals.data(), (int)syst_vals.size(), upper.data(),
+                             lower.data(), (int)observables.size(), &gen);
+  if (rc != SXMC_OK) { sxmc_batch_destroy(batch); batch = NULL; check(rc); }
+}
+
+MCMCBatch::~MCMCBatch() {
+  if (gen) sxmc_generator_destroy(gen);
+  if (batch) sxmc_batch_destroy(batch);
+}
+
+void MCMCBatch::GenerateData(int slot, bool poisson, uint64_t seed, uint64_t experiment, std::vector<unsigned>* observed) {
+  std::vector<unsigned> obs(nsignals, 0);
+  check(sxmc_batch_generate_data(batch, slot, gen, poisson ? 1 : 0, seed, experiment, obs.data()));
+  if (observed) *observed = obs;
+}
+
+void MCMCBatch::SetData(int slot, const std::vector<float>& data) {
+  check(sxmc_batch_set_data(batch, slot, data.data(), data.size()));
+}
+
+void MCMCBatch::SetSeed(int slot, uint64_t seed, uint64_t stream_id) {
+  check(sxmc_batch_set_seed(batch, slot, seed, stream_id));
+}
+
+void MCMCBatch::Run(int nchains, unsigned nsteps, float burnin_fraction, bool debug_mode) {
+  const int rc = sxmc_batch_run(batch, nchains, nsteps, burnin_fraction, debug_mode ? 1 : 0);
+  if (rc == SXMC_ESTATE) throw NotSmallFit(sxmc_last_error());
+  check(rc);
+}
+
+long MCMCBatch::accepted(int slot) const {
+  long n = 0, a = 0;
+  check(sxmc_batch_nrows(batch, slot, &n, &a));
+  return a;
+}
+
+LikelihoodSpace* MCMCBatch::GetLikelihoodSpace(int slot) {
+  long nrows = 0, acc = 0;
+  check(sxmc_batch_nrows(batch, slot, &nrows, &acc));
+  NtupleRows* nt = new NtupleRows;
+  nt->names = parameter_names;
+  nt->rows.resize((size_t)nrows * (nparameters + 1));
+  if (nrows > 0) check(sxmc_batch_read(batch, slot, nt->rows.data(), nrows));
   return new LikelihoodSpace(nt);
 }

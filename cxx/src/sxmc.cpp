@@ -64,9 +64,68 @@ static void write_npy(const std::string& path, const NtupleRows& nt) {
   f.write((const char*)nt.rows.data(), nt.rows.size() * sizeof(float));
 }
 
+// what the loop of src/sxmc.cpp:110-134 does with a finished likelihood space
+static void report_experiment(FitConfig& fc, unsigned i, bool first, LikelihoodSpace* ls,
+                              const std::string& output_path, std::vector<float>& limits) {
+  float lm = 0;
+  std::map<std::string, Interval> best_fit = ls->extract_best_fit(lm, fc.confidence, fc.error_type);
+  std::cout << "-- Best fit --" << std::endl;
+  for (std::map<std::string, Interval>::const_iterator it = best_fit.begin(); it != best_fit.end(); ++it)
+    std::cout << " " << it->first << ": " << it->second.str() << std::endl;
+
+  if (fc.signal_name != "" && best_fit.find(fc.signal_name) != best_fit.end()) {
+    Interval bfi = best_fit[fc.signal_name];
+    std::cout << "ensemble: Signal " << fc.signal_name << ": " << bfi.str() << std::endl;
+    if (!bfi.one_sided) std::cerr << "ensemble: Warning: Two-sided limit!" << std::endl;
+    std::cout << "ensemble: lower = " << bfi.lower << ", upper = " << bfi.upper << ", coverage = " << bfi.coverage
+              << std::endl;
+    limits.push_back(bfi.upper);
+  }
+  std::ostringstream lsfile;
+  lsfile << output_path << fc.output_prefix << "_" << i << ".npy";
+  write_npy(lsfile.str(), *ls->get_samples());
+  if (first) {
+    std::ofstream cols((output_path + fc.output_prefix + "_columns.txt").c_str());
+    for (size_t k = 0; k < ls->get_samples()->names.size(); ++k) cols << ls->get_samples()->names[k] << "\n";
+  }
+}
+
 // src/sxmc.cpp:44-141
 static std::vector<float> ensemble(FitConfig& fc, const std::string& output_path, unsigned rank, unsigned world) {
   std::vector<float> limits;
+  if (fc.samples != "") throw std::runtime_error("fit.samples (re-reading a saved likelihood space) needs ROOT");
+  unsigned done = 0;                 // experiments of this rank already fitted by the batch path
+  if (fc.data.empty() && !std::getenv("SXMC_NO_BATCH")) {
+    // Fake-data ensembles of small fits: the fits of up to 148 experiments advance together in one
+    // cooperative launch, their data sets drawn on the device.  Experiment i is the chain the
+    // one-at-a-time loop below produces (same Philox stream), only ~70x sooner.
+    try {
+      MCMCBatch batch(fc.sources, fc.signals, fc.systematics, fc.observables);
+      std::vector<unsigned> mine;
+      for (unsigned i = rank; i < fc.nexperiments; i += world) mine.push_back(i);
+      for (size_t g0 = 0; g0 < mine.size(); g0 += (size_t)batch.max_chains()) {
+        const int n = (int)std::min(mine.size() - g0, (size_t)batch.max_chains());
+        for (int slot = 0; slot < n; ++slot) {
+          std::vector<unsigned> observed;
+          batch.GenerateData(slot, true, (uint64_t)fc.seed, mine[g0 + slot], &observed);
+          batch.SetSeed(slot, (uint64_t)fc.seed, mine[g0 + slot]);
+        }
+        batch.Run(n, fc.nsteps, fc.burnin_fraction, fc.debug_mode);
+        for (int slot = 0; slot < n; ++slot) {
+          const unsigned i = mine[g0 + slot];
+          std::cout << "Experiment " << i + 1 << " / " << fc.nexperiments << std::endl;
+          LikelihoodSpace* ls = batch.GetLikelihoodSpace(slot);
+          report_experiment(fc, i, i == rank, ls, output_path, limits);
+          delete ls;
+          ++done;
+        }
+      }
+      return limits;
+    } catch (const MCMCBatch::NotSmallFit& e) {
+      if (done) throw;
+      std::cout << "ensemble: one fit at a time (" << e.what() << ")" << std::endl;
+    }
+  }
   for (unsigned i = rank; i < fc.nexperiments; i += world) {
     std::cout << "Experiment " << i + 1 << " / " << fc.nexperiments << std::endl;
     std::vector<float> samples;
@@ -84,32 +143,10 @@ static std::vector<float> ensemble(FitConfig& fc, const std::string& output_path
         dynamic_cast<pdfz::EvalHist*>(it->second[i].histogram)->GetSamples(samples);
       }
     }
-    if (fc.samples != "") throw std::runtime_error("fit.samples (re-reading a saved likelihood space) needs ROOT");
-
     MCMC mcmc(fc.sources, fc.signals, fc.systematics, fc.observables);
     mcmc.SetSeed((uint64_t)fc.seed, i);
     LikelihoodSpace* ls = mcmc(samples, fc.nsteps, fc.burnin_fraction, fc.debug_mode);
-    float lm = 0;
-    std::map<std::string, Interval> best_fit = ls->extract_best_fit(lm, fc.confidence, fc.error_type);
-    std::cout << "-- Best fit --" << std::endl;
-    for (std::map<std::string, Interval>::const_iterator it = best_fit.begin(); it != best_fit.end(); ++it)
-      std::cout << " " << it->first << ": " << it->second.str() << std::endl;
-
-    if (fc.signal_name != "" && best_fit.find(fc.signal_name) != best_fit.end()) {
-      Interval bfi = best_fit[fc.signal_name];
-      std::cout << "ensemble: Signal " << fc.signal_name << ": " << bfi.str() << std::endl;
-      if (!bfi.one_sided) std::cerr << "ensemble: Warning: Two-sided limit!" << std::endl;
-      std::cout << "ensemble: lower = " << bfi.lower << ", upper = " << bfi.upper << ", coverage = " << bfi.coverage
-                << std::endl;
-      limits.push_back(bfi.upper);
-    }
-    std::ostringstream lsfile;
-    lsfile << output_path << fc.output_prefix << "_" << i << ".npy";
-    write_npy(lsfile.str(), *ls->get_samples());
-    if (i == rank) {
-      std::ofstream cols((output_path + fc.output_prefix + "_columns.txt").c_str());
-      for (size_t k = 0; k < ls->get_samples()->names.size(); ++k) cols << ls->get_samples()->names[k] << "\n";
-    }
+    report_experiment(fc, i, i == rank, ls, output_path, limits);
     delete ls;
   }
   return limits;

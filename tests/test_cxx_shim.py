@@ -158,10 +158,17 @@ def test_cxx_command_line_equals_python_command_line(tmp_path):
     rp = subprocess.run([sys.executable, "-m", "sxmc_b200", str(cfg), str(tmp_path / "out_py")], cwd=ROOT,
                         capture_output=True, text=True, timeout=900)
     assert rp.returncode == 0, rp.stdout[-3000:] + rp.stderr[-3000:]
+    # ... and once more with the C++ main forced onto its one-fit-at-a-time loop (MCMC::operator())
+    r1 = subprocess.run([SXMC_BIN, str(cfg), str(tmp_path / "out_cxx1")], capture_output=True, text=True, timeout=900,
+                        env=dict(os.environ, SXMC_NO_BATCH="1"))
+    assert r1.returncode == 0, r1.stdout[-3000:] + r1.stderr[-3000:]
+    assert "Sampling fake dataset" in r1.stdout and "Sampling fake dataset" not in rc.stdout
     for i in range(3):
         a = np.load(tmp_path / "out_cxx" / ("example_%d.npy" % i))
+        a1 = np.load(tmp_path / "out_cxx1" / ("example_%d.npy" % i))
         b = np.load(tmp_path / "out_py" / ("example_%d.npy" % i))
         assert a.shape == b.shape == (3000 - 2 * 600, 5) and a.tobytes() == b.tobytes(), i
+        assert a1.tobytes() == b.tobytes(), i
     cols = (tmp_path / "out_cxx" / "example_columns.txt").read_text().split()
     assert cols == ["signal1", "signal2", "energy_resolution_0", "energy_scale_0", "likelihood"]
 
@@ -169,4 +176,5 @@ def test_cxx_command_line_equals_python_command_line(tmp_path):
         line = [ln for ln in text.splitlines() if ln.startswith("sxmc: Upper limits:")][0]
         return [float(x) for x in line.split(":", 2)[2].split(",") if x.strip()]
     assert np.allclose(limits(rc.stdout), limits(rp.stdout), rtol=1e-5)
+    assert np.allclose(limits(r1.stdout), limits(rp.stdout), rtol=1e-5)
     assert "sxmc: Median upper limit:" in rc.stdout
