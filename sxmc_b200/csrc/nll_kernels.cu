@@ -85,9 +85,23 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
       const unsigned m = mult[b];
       if (!m) continue;
       double s = 0;
-      for (int j = 0; j < ns; ++j) {
-        float v = (float)((double)s_bins[j][b] / s_bn[j]);            // pdfz.cpp:429-432
-        if (isnan(v)) v = 0.0f;                                       // nll_kernels.cpp:107
+      int j = 0;
+      // eight signals' counts in flight at a time (the loads do not depend on the running sum, but
+      // a rolled loop issues them one L2 round trip after the other); same order of additions
+      for (; j + 8 <= ns; j += 8) {
+        unsigned h[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) h[q] = s_bins[j + q][b];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          float v = (float)((double)h[q] / s_bn[j + q]);              // pdfz.cpp:429-432
+          if (isnan(v)) v = 0.0f;                                     // nll_kernels.cpp:107
+          s = __dadd_rn(s, __dmul_rn(s_c[j + q], (double)v));
+        }
+      }
+      for (; j < ns; ++j) {
+        float v = (float)((double)s_bins[j][b] / s_bn[j]);
+        if (isnan(v)) v = 0.0f;
         s = __dadd_rn(s, __dmul_rn(s_c[j], (double)v));
       }
       if (s > 0) sum += (double)m * log(s);
