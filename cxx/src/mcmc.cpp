@@ -272,7 +272,7 @@ MCMCBatch::MCMCBatch(const std::vector<Source>& sources, const std::vector<Signa
   nparameters = t.nparameters;
   parameter_names = t.names;
   int rc = sxmc_batch_create(&t.cfg, max_chains, &batch);
-  if (rc == SXMC_ESTATE) throw NotSmallFit(sxmc_last_error());
+  if (rc == SXMC_ENOTSMALL) throw NotSmallFit(sxmc_last_error());
   check(rc);
   // the fake-data generator of the ensemble: efficiencies and sampling histograms at the
   // systematics' means, observables' limits for the rejection test (src/generator.cpp:17-29)
@@ -308,7 +308,7 @@ void MCMCBatch::SetSeed(int slot, uint64_t seed, uint64_t stream_id) {
 
 void MCMCBatch::Run(int nchains, unsigned nsteps, float burnin_fraction, bool debug_mode) {
   const int rc = sxmc_batch_run(batch, nchains, nsteps, burnin_fraction, debug_mode ? 1 : 0);
-  if (rc == SXMC_ESTATE) throw NotSmallFit(sxmc_last_error());
+  if (rc == SXMC_ENOTSMALL) throw NotSmallFit(sxmc_last_error());
   check(rc);
 }
 

@@ -25,6 +25,9 @@ extern "C" {
 #define SXMC_ECUDA 2   /* CUDA runtime / driver failure, or no device */
 #define SXMC_ESTATE 3  /* call sequence error (e.g. eval before buffers are bound) */
 #define SXMC_ENCCL 4   /* NCCL failure */
+#define SXMC_ENOTSMALL 5 /* sxmc_batch_*: the fit's samples do not fit on chip (or its shape has no batch
+                          * kernel): run its chains one at a time (sxmc_chain_run).  The ONLY code a
+                          * caller may answer with that fallback; timeouts and aborts are SXMC_ESTATE */
 
 /* numeric values of pdfz::Systematic::Type (src/pdfz.h:111-116) */
 #define SXMC_SYST_SHIFT 0
@@ -113,12 +116,21 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * generic (interpreting) kernel, bit 1 = force run-time systematic dispatch in the fast
  * kernel (no compile-time program), bit 2 = the chain batch never takes its monotone endpoint
  * path, bits 3-4 = form of the peer-memory all-reduce (0 automatic: two-shot above two ranks,
- * 1 one-shot, 2 two-shot) -- used by the parity tests and measurements to cover every path. */
+ * 1 one-shot, 2 two-shot), bit 5 = chains set up from now on look events up one by one even when
+ * every signal reads the same dataset (the multi-dataset form) -- used by the parity tests and
+ * measurements to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
 int sxmc_enable_kernel_timing(int on);
 int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);
+/* Profiling hook of the fast binning kernel (no reference counterpart): while enabled every
+ * launch writes [grid <= 256][32] %globaltimer stamps (ns) per CTA -- 0 entry, 1 pipeline
+ * initialised, 2 first data arrived, 3 = number of segments, 4+3s+{0,1,2} parameters resolved /
+ * warp 0 out of the chunk loop / histogram merged for segment s < 4, 16+w warp w out of the
+ * chunk loop of the last segment, 31 exit.  out256x32 (host, may be NULL) receives the stamps
+ * of the last launch.  tools/prof_bin.py prints the prologue / steady state / epilogue split. */
+int sxmc_bin_debug_stamps(int enable, unsigned long long* out256x32);
 
 /* ---- nll_kernels: standalone NLL of a materialised lut (MCMC::nll, src/mcmc.cpp:390-415:
  *      nll_event_chunks -> nll_event_reduce -> nll_total).  All pointers are DEVICE
@@ -260,7 +272,7 @@ int sxmc_chain_contour(sxmc_chain* c, float delta, float* lower_out, float* uppe
  *      over the same signals) advanced in lockstep by ONE cooperative launch.  Up to 148 chains
  *      (one per SM) share the Monte-Carlo samples, which stay resident in shared memory; each
  *      chain has its own data events, random stream and state.  Small fits only (the samples of
- *      a CTA must fit in shared memory: workloads A, B, E); others fail with SXMC_ESTATE and
+ *      a CTA must fit in shared memory: workloads A, B, E); others fail with SXMC_ENOTSMALL and
  *      run one chain at a time through sxmc_chain_run.  `cfg` as for sxmc_chain_create. ------- */
 typedef struct sxmc_batch sxmc_batch;
 int sxmc_batch_create(const sxmc_chain_config* cfg, int max_chains, sxmc_batch** out);

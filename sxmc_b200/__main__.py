@@ -56,7 +56,8 @@ def main(argv=None):
         # fake data sets drawn on the device, the fits of up to 148 experiments in one launch
         fit = fc.to_fitspec()
         r = ensemble.ensemble(fit, fc.nexperiments, signal_name=fc.signal_name, confidence=fc.confidence,
-                              seed=fc.seed, rank=rank, world=world, keep_chains=True)
+                              seed=fc.seed, rank=rank, world=world, keep_chains=True,
+                              debug_mode=fc.debug_mode)
         limits = r["limits"]
         columns = fit.names["sources"] + ["%s_%d" % (y.name, j) for y in fc.systematics for j in range(y.npars)]
         if fc.error_type == "projection":          # ERROR_PROJECTION: host estimator on the chain rows

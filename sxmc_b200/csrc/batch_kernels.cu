@@ -271,12 +271,12 @@ constexpr size_t BK_STATIC_RESERVE = 56 * 1024;   // static shared memory of the
 int plan_chain_batch(const BinLaunch& L0, int nchains, BatchPlan* plan) {
   if (!L0.fast || L0.njobs > FAST_MAX_JOBS || nchains < 1 || nchains > BATCH_MAX_CHAINS) {
     set_error("chain batch: fit shape not supported (fast binning path, <= 32 signals, <= 148 chains)");
-    return SXMC_ESTATE;
+    return SXMC_ENOTSMALL;
   }
   int dev = 0, sms = 0;
   SXMC_CUDA(cudaGetDevice(&dev));
   SXMC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  if (nchains > sms) { set_error("chain batch: more chains than SMs"); return SXMC_ESTATE; }
+  if (nchains > sms) { set_error("chain batch: more chains than SMs"); return SXMC_EINVAL; }
   for (int group = BATCH_MAX_GROUP; group >= 1; group >>= 1) {
     BinLaunch L = L0;
     if (!bin_fast_plan(L.nslots, group * L.max_total_nbins, BK_STATIC_RESERVE, &L.rows_per_stage, &L.nstages,
@@ -303,7 +303,7 @@ int plan_chain_batch(const BinLaunch& L0, int nchains, BatchPlan* plan) {
     return SXMC_OK;
   }
   set_error("chain batch: the samples do not fit in shared memory (not a small fit)");
-  return SXMC_ESTATE;
+  return SXMC_ENOTSMALL;
 }
 
 int launch_chain_batch(const BatchPlan& plan, const BatchParams& Q0, cudaStream_t stream) {
@@ -313,14 +313,14 @@ int launch_chain_batch(const BatchPlan& plan, const BatchParams& Q0, cudaStream_
     if (e.nobs == L.nobs && e.ns == L.nslots && e.nops == L.prog_nops &&
         (L.prog_nops <= 0 || e.codes == L.prog_codes))
       fk = e.k;
-  if (!fk) { set_error("chain batch: no instantiation for this shape"); return SXMC_ESTATE; }
+  if (!fk) { set_error("chain batch: no instantiation for this shape"); return SXMC_ENOTSMALL; }
   FastParams P;
   unsigned long long total = 0;
   build_fast_params(L, 0, L.njobs, plan.grid, P, &total);
   SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
   int occ = 0;
   SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fk, FAST_THREADS, L.smem_bytes));
-  if (occ < 1) { set_error("chain batch kernel does not fit on an SM"); return SXMC_ESTATE; }
+  if (occ < 1) { set_error("chain batch kernel does not fit on an SM"); return SXMC_ENOTSMALL; }
   BatchParams Q = Q0;
   Q.group = plan.group;
   void* args[2] = {(void*)&P, (void*)&Q};

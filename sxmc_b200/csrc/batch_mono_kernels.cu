@@ -387,13 +387,13 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
   if (!L.fast || L.nobs != 1 || L.nslots != 1 || L.njobs > FAST_MAX_JOBS || nchains < 1 ||
       nchains > BATCH_MAX_CHAINS) {
     set_error("monotone chain batch: fit shape not supported");
-    return SXMC_ESTATE;
+    return SXMC_ENOTSMALL;
   }
   int dev = 0, sms = 0;
   SXMC_CUDA(cudaGetDevice(&dev));
   SXMC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   if (sms > MONO_MAX_CTAS) sms = MONO_MAX_CTAS;
-  if (nchains > sms) { set_error("monotone chain batch: more chains than SMs"); return SXMC_ESTATE; }
+  if (nchains > sms) { set_error("monotone chain batch: more chains than SMs"); return SXMC_EINVAL; }
   const int nj = L.njobs;
   const int nranks = L.max_total_nbins + 3;
   // sorted samples of every job on the host, and the first position of every nominal rank
@@ -404,7 +404,7 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
   for (int j = 0; j < nj; ++j) {
     const BinJob& job = L.jobs_host[j];
     const unsigned long long n = nsamples[j];
-    if (n >= (1ull << 31)) { set_error("monotone chain batch: too many samples"); return SXMC_ESTATE; }
+    if (n >= (1ull << 31)) { set_error("monotone chain batch: too many samples"); return SXMC_ENOTSMALL; }
     std::vector<float> tiled((size_t)job.nwtiles * WT_SAMPLES);
     if (!tiled.empty())
       SXMC_CUDA(cudaMemcpy(tiled.data(), job.cols[job.slot_field[0]], sizeof(float) * tiled.size(),
@@ -425,7 +425,7 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
   }
   if (need_total > (unsigned long long)sms) {
     set_error("chain batch: the samples do not fit in shared memory (not a small fit)");
-    return SXMC_ESTATE;
+    return SXMC_ENOTSMALL;
   }
   // greedy cut of job j for an edge budget E: the ranges needed (optionally listed as pos, count)
   auto cut = [&](int j, int E, std::vector<unsigned>* out) {
@@ -545,7 +545,7 @@ int launch_chain_batch_mono(const MonoPlan& plan, const BatchParams& Q0, cudaStr
   SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   SXMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fk, MONO_THREADS, smem));
-  if (occ < 1) { set_error("monotone chain batch kernel does not fit on an SM"); return SXMC_ESTATE; }
+  if (occ < 1) { set_error("monotone chain batch kernel does not fit on an SM"); return SXMC_ENOTSMALL; }
   BatchParams Q = Q0;
   void* args[2] = {(void*)&plan.params, (void*)&Q};
   SXMC_CUDA(cudaLaunchCooperativeKernel((const void*)fk, dim3((unsigned)plan.grid), dim3(MONO_THREADS), args, smem,

@@ -34,16 +34,31 @@ __device__ __forceinline__ void resolve_syst(const BinJob& job, int k, SystRt& s
   s.onep = __dadd_rn(1.0, s.c0);
 }
 
+// x^3 rounded once from a double-double product (error ~2^-104 before the final rounding):
+// equals the correctly rounded cube except when the exact value lies within ~2^-50 ulp of a
+// rounding boundary.  glibc's pow (<0.53 ulp, the reference's `pow(x, 3)`) returns the correctly
+// rounded value except within ~2^-15 ulp of a boundary, so the two agree on all but ~1e-5 of
+// arguments; CUDA's own pow (up to 1 ulp off) does not.  Explicit FMAs: -fmad=false only stops
+// contraction.  Overflow, inf, NaN and signed zero come out as pow(x, 3) gives them.
+__device__ __forceinline__ double cube_rn(double x) {
+  const double p = __dmul_rn(x, x);
+  const double pe = __fma_rn(x, x, -p);        // x*x = p + pe exactly
+  const double q = __dmul_rn(p, x);
+  const double qe = __fma_rn(p, x, -q);        // p*x = q + qe exactly
+  const double r = __dadd_rn(q, __dadd_rn(qe, __dmul_rn(pe, x)));
+  return (r == r && fabs(q) <= 1.7976931348623157e308) ? r : q;   // inf - inf above: keep q
+}
+
 // p = sum_i par_i * pow(x, i) accumulated left to right (src/pdfz.cpp:310-314).
-// pow(x,0)=1 and pow(x,1)=x are exact; pow(x,2.0)==x*x for glibc; i=3 uses the
-// device pow (<=1 ulp-level difference from glibc possible; documented in DESIGN.md).
+// pow(x,0)=1 and pow(x,1)=x are exact; pow(x,2.0)==x*x for glibc; i=3 is the
+// once-rounded cube above (measured against the reference: tests/test_gpu_parity.py, P4 case).
 __device__ __forceinline__ double syst_poly(const SystRt& s, double x) {
   double p = s.c0;
   if (s.npars > 1) {
     p = __dadd_rn(p, __dmul_rn(s.c1, x));
     if (s.npars > 2) {
       p = __dadd_rn(p, __dmul_rn(s.c2, __dmul_rn(x, x)));
-      if (s.npars > 3) p = __dadd_rn(p, __dmul_rn(s.c3, pow(x, 3.0)));
+      if (s.npars > 3) p = __dadd_rn(p, __dmul_rn(s.c3, cube_rn(x)));
     }
   }
   return p;
@@ -310,6 +325,17 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     }                                                                                  \
   } while (0)
   BIN_DBG(0);
+  unsigned long long* const xd = P.xdbg ? P.xdbg + 32ull * blockIdx.x : nullptr;
+#define BIN_XDBG(slot, who)                                                            \
+  do {                                                                                 \
+    if (xd && (who)) {                                                                 \
+      unsigned long long t_;                                                           \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                           \
+      xd[slot] = t_;                                                                   \
+    }                                                                                  \
+  } while (0)
+  int xseg = 0;
+  BIN_XDBG(1, threadIdx.x == 0);
   const Geo& geo = P.geo;
   const int R = P.R, S = P.S;
   const int njobs = P.njobs;
@@ -366,6 +392,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
       for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) s_hist[b] = 0;
     __syncthreads();
     BIN_DBG(1);
+    if (xseg < 4) BIN_XDBG(4 + 3 * xseg, threadIdx.x == 0);
 
     // the segment's systematics, in registers
     int op_code[FAST_MAX_OPS];
@@ -392,6 +419,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     for (unsigned long long c = ca; c < cb; ++c, ++it) {
       const unsigned slot = it % (unsigned)S;
       mbar_wait(my_bar0 + 8u * slot, (it / (unsigned)S) & 1u);
+      if (xseg == 0 && c == ca) BIN_XDBG(2, threadIdx.x == 0);
       const unsigned src = my_stage0 + slot * stage_bytes + (unsigned)lane * 16u;
 #pragma unroll 1
       for (int r = 0; r < R; ++r) {
@@ -426,6 +454,8 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     }
     run_flush<SMEM>(acc, hist, geo.total_nbins);
     BIN_DBG(2);
+    if (xseg < 4) BIN_XDBG(5 + 3 * xseg, threadIdx.x == 0);
+    BIN_XDBG(16 + warp, lane == 0);
 
     // in-domain count: one global atomic per CTA and segment (all CTAs of a signal hit the
     // same address; per-warp atomics serialise in L2 and dominate small fits)
@@ -445,9 +475,12 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     }
     __syncthreads();   // s_syst / s_hist / s_norm are rewritten by the next segment
     BIN_DBG(3);
+    if (xseg < 4) BIN_XDBG(6 + 3 * xseg, threadIdx.x == 0);
+    ++xseg;
     t0 = tend;
     ++j;
   }
+  if (xd && threadIdx.x == 0) xd[3] = (unsigned long long)xseg;
   cx.it = it;
   cx.loaded = true;
 }
@@ -460,10 +493,20 @@ bin_fast_kernel(const __grid_constant__ FastParams P) {
   __shared__ __align__(8) unsigned long long s_bar[FAST_WARPS * FAST_MAX_STAGES];
   __shared__ unsigned s_norm;
   if (threadIdx.x == 0) s_norm = 0u;
+  if (P.xdbg && threadIdx.x == 0) {
+    unsigned long long t_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+    P.xdbg[32ull * blockIdx.x] = t_;
+  }
   FastCtx cx;
   fast_ctx_init<NS>(cx, P, smem_raw, s_bar);
   fast_bin_pass<NOBS, NS, SMEM, NOPS, CODES>(P, cx, reinterpret_cast<unsigned*>(smem_raw), s_syst,
                                              &s_norm, nullptr, nullptr);
+  if (P.xdbg && threadIdx.x == 0) {
+    unsigned long long t_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+    P.xdbg[32ull * blockIdx.x + 31] = t_;
+  }
 }
 
 // the programs kernels are instantiated for (bin_kernels.cu and chain_kernels.cu)

@@ -211,6 +211,9 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
   }
 }
 
+static unsigned long long* g_bin_xdbg = nullptr;   // profiling hook, NULL in production
+void set_bin_xdbg(unsigned long long* dev) { g_bin_xdbg = dev; }
+
 int launch_bin(const BinLaunch& L, cudaStream_t stream) {
   if (L.total_units == 0) return SXMC_OK;
   if (L.fast) {
@@ -229,6 +232,7 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
       const unsigned long long max_grid = (total + FAST_WARPS - 1) / FAST_WARPS;
       if (grid > max_grid) grid = max_grid;
       build_fast_params(L, g0, ng, (int)grid, P, &total);
+      P.xdbg = g_bin_xdbg;
       fk<<<(unsigned)grid, FAST_THREADS, L.smem_bytes, stream>>>(P);
       SXMC_CUDA(cudaGetLastError());
     }

@@ -31,6 +31,7 @@ static int g_force_generic = 0;
 static int g_force_dynamic = 0;
 static int g_p2p_form = 0;       // peer-memory all-reduce: 0 automatic (two-shot above 2 ranks), 1 one-shot, 2 two-shot
 static int g_no_mono = 0;        // chain batch: never take the monotone endpoint path (tests)
+static int g_no_group = 0;       // lookup: never group the events by bin (the multi-dataset form, on request)
 static long long g_persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent   // fast kernel with run-time systematic dispatch only
 static int g_timing = 0;
 static float g_last_bin_ms = -1.f, g_last_nll_ms = -1.f;
@@ -384,9 +385,25 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_force_dynamic = (force_generic >> 1) & 1;
   g_no_mono = (force_generic >> 2) & 1;
   g_p2p_form = (force_generic >> 3) & 3;
+  g_no_group = (force_generic >> 5) & 1;
   return SXMC_OK;
 }
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
+int sxmc_bin_debug_stamps(int enable, unsigned long long* out256x32) {
+  static unsigned long long* dev = nullptr;
+  const size_t bytes = sizeof(unsigned long long) * 256 * 32;
+  if (enable && !dev) {
+    SXMC_CUDA(cudaMalloc(&dev, bytes));
+    SXMC_CUDA(cudaMemset(dev, 0, bytes));
+  }
+  if (out256x32 && dev) {
+    SXMC_CUDA(cudaDeviceSynchronize());
+    SXMC_CUDA(cudaMemcpy(out256x32, dev, bytes, cudaMemcpyDeviceToHost));
+  }
+  if (!enable && dev) { cudaFree(dev); dev = nullptr; }
+  set_bin_xdbg(enable ? dev : nullptr);
+  return SXMC_OK;
+}
 int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms) {
   if (bin_ms) *bin_ms = g_last_bin_ms;
   if (nll_ms) *nll_ms = g_last_nll_ms;
@@ -1008,7 +1025,7 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
   cudaFree(c->mult_dev);
   c->mult_dev = nullptr;
   c->mult_fits_table = (size_t)c->nsignals * c->total_nbins <= (size_t)BATCH_PDF_TABLE;
-  if (shared) {
+  if (shared && !g_no_group) {
     SXMC_CUDA(cudaMalloc(&c->mult_dev, sizeof(unsigned) * (size_t)c->total_nbins));
     SXMC_TRY(launch_event_mult(c->pdfs[0]->read_bins_dev, (long long)c->nevents, c->total_nbins, c->mult_dev, c->stream));
   }

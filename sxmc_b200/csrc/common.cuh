@@ -100,6 +100,11 @@ struct FastParams {
   // so no CTA pays the per-segment overhead twice; aligned == 0: even split of all chunks
   unsigned short cta_first[FAST_MAX_JOBS + 1];
   int aligned;
+  // profiling hook (sxmc_bin_debug_stamps): [grid][32] %globaltimer stamps, NULL in production.
+  // Per CTA: 0 entry, 1 pipeline initialised, 2 first data arrived (warp 0), 3 segments done,
+  // 4+3s+{0,1,2} of segment s < 4: parameters resolved / warp 0 out of its chunk loop / merged,
+  // 16+w: warp w out of the chunk loop of the CTA's LAST segment, 31 exit.
+  unsigned long long* xdbg;
 };
 
 // Arguments of the persistent chain kernel (chain_kernels.cu), by value.

@@ -54,6 +54,7 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
 // chain_kernels.cu
 int launch_chain_persistent(const BinLaunch& L, const PersistParams& Q, cudaStream_t stream);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);
+void set_bin_xdbg(unsigned long long* dev);   // [256][32] stamps of the next fast launches, or NULL
 int launch_zero_jobs(const BinJob* jobs_dev, int njobs, cudaStream_t stream);
 int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,
                    const PrepGeo& g, int primary, bool sort, float* cols_dev,

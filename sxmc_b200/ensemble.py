@@ -258,7 +258,7 @@ def _fit_objects(fit, hists):
 
 
 def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps=None,
-             burnin_fraction=None, rank=0, world=1, keep_chains=False, batch=148):
+             burnin_fraction=None, rank=0, world=1, keep_chains=False, batch=148, debug_mode=False):
     """The loop of src/sxmc.cpp:62-134 over this rank's experiments.  Returns a dict with the
     experiment indices run here, their upper limits (`limits.push_back(bfi.upper)`, :126),
     per-experiment observed counts and timings.  Use ``sharding.gather_limits`` +
@@ -267,7 +267,9 @@ def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps
     ``batch`` > 1: the fits of up to that many experiments advance together in one cooperative
     launch (``MCMCBatch``) when the fit is small enough for its samples to stay on chip;
     otherwise (or with batch <= 1) one chain at a time.  Both give the same chains: experiment
-    ``i`` always uses Philox stream ``i``."""
+    ``i`` always uses Philox stream ``i``.  ``debug_mode`` is MCMC::operator()'s flag
+    (`mcmc(data, nsteps, burnin, debug_mode)`, src/sxmc.cpp:97): every step accepted, no reset of the
+    chain at burn-in."""
     from . import mcmc
     from ._lib import SxmcError
     nsteps = fit.nsteps if nsteps is None else int(nsteps)
@@ -288,7 +290,7 @@ def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps
                 for slot, i in enumerate(group):
                     obs.append(mb.generate_data(slot, gen, True, seed, i))   # make_fake_dataset(..., true)
                     mb.set_seed(slot, seed, i)
-                mb.run(len(group), nsteps, burnin)                           # MCMC::operator() x len(group)
+                mb.run(len(group), nsteps, burnin, bool(debug_mode))                           # MCMC::operator() x len(group)
                 out["loop_ms"] += mb.loop_ms()
                 out["launches"] += 1
                 for slot, i in enumerate(group):
@@ -301,7 +303,7 @@ def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps
             out["seconds"] = time.perf_counter() - t_all
             return out
         except SxmcError as e:
-            if e.code != 3 or out["limits"]:      # only "not a small fit" falls back
+            if e.code != 5 or out["limits"]:      # only SXMC_ENOTSMALL falls back; timeouts and aborts propagate
                 raise
         finally:
             gen.close()
@@ -313,7 +315,7 @@ def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps
     for i in mine:
         events, observed = gen(True, seed, i)                   # make_fake_dataset(..., true)
         chain.set_seed(seed, i)
-        chain.run_resident(events, nsteps, burnin)              # MCMC::operator(), rows stay on the device
+        chain.run_resident(events, nsteps, burnin, bool(debug_mode))              # MCMC::operator(), rows stay on the device
         best_fit, _ = contour_intervals(chain, confidence)      # ls->get_best_fit()
         out["limits"].append(best_fit[signal_name].upper if signal_name in best_fit else float("nan"))
         out["observed"].append(observed)

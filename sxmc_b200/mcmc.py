@@ -243,6 +243,22 @@ class MCMC:
         _check(lib().sxmc_chain_nll_at(self._c, ptr(p, c_dp), int(rebin), C.byref(v), C.byref(ev)))
         return v.value, ev.value
 
+    def nll_lut(self, lut, pars, norms):
+        """MCMC::nll(lut, nevents, v, nll, nexpected, n_mc, source_id, norms, ...) of
+        src/mcmc.cpp:390-415 on caller-held DEVICE buffers (``pdfz.Array``): the materialised PDF
+        lookup table [nsignals][nevents], the parameter vector and the normalisations."""
+        arrs = [pdfz.Array.from_host(v, t) for v, t in (
+            (self._means, np.float64), (self._sigmas, np.float64), (self._nexp, np.float64),
+            (self._n_mc, np.uint32), (self._sid, np.int16))]
+        v, ev = C.c_double(0), C.c_double(0)
+        nevents = lut.size() // max(1, self.nsignals)
+        _check(lib().sxmc_nll_eval(lut.readOnlyDevicePtr(), nevents, self.nsignals, pars.readOnlyDevicePtr(),
+                                   self.nparameters, self.nsources, *[a.readOnlyDevicePtr() for a in arrs],
+                                   norms.readOnlyDevicePtr(), C.byref(v), C.byref(ev)))
+        for a in arrs:
+            a.free()
+        return v.value, ev.value
+
     def norms(self):
         out = np.zeros(self.nsignals, dtype=np.uint32)
         _check(lib().sxmc_chain_get_norms(self._c, ptr(out, c_up)))
@@ -351,11 +367,13 @@ class MCMCBatch:
         return a.value, b.value
 
 
-def build_fit(fit, sort=True, batch=0):
+def build_fit(fit, sort=True, batch=0, hists=None):
     """FitSpec (sxmc_b200.workloads) -> (hists, MCMC), the way src/signal.cpp:112-169 and
-    src/sxmc.cpp:96 wire the reference objects."""
-    hists = []
-    for sig in fit.signals:
+    src/sxmc.cpp:96 wire the reference objects.  ``hists``: EvalHist objects already built for
+    this fit (a second MCMC over the same PDFs, as `plot_fit` reuses them in the reference)."""
+    reuse = hists is not None
+    hists = list(hists) if reuse else []
+    for sig in ([] if reuse else fit.signals):
         h = pdfz.EvalHist(sig.samples, sig.samples.shape[1], fit.nobs, fit.lower, fit.upper,
                           fit.nbins, sig.dataset)
         if not sort:

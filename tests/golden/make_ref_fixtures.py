@@ -19,6 +19,7 @@ import oracle  # noqa: E402
 from oracle import ref  # noqa: E402
 from sxmc_b200 import workloads as W  # noqa: E402
 from tests.test_oracle import SMALL, _pars  # noqa: E402
+from tests import cases  # noqa: E402
 
 
 def main():
@@ -45,8 +46,37 @@ def main():
     out["chainB_normals"] = normals
     out["chainB_uniforms"] = uniforms
     out["chainB_chain"] = r["chain"]
+    # CTSCALE and 2-, 3-, 4-coefficient series (src/pdfz.cpp:310-325), reference output
+    for name, make in cases.POLY_CASES.items():
+        fit = make()
+        pars = cases.off_nominal(fit, 31)
+        bins, norms, lut = ref.eval_all(fit, pars)
+        nll, ev = ref.nll(fit, lut, pars, norms)
+        out[name + "_pars"] = pars
+        out[name + "_bins"] = bins
+        out[name + "_norms"] = norms
+        out[name + "_lut"] = lut
+        out[name + "_nll"] = np.float64(nll)
+        out[name + "_evsum"] = np.float64(ev)
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", "ref_fixtures.npz"), **out)
     print("wrote", {k: v.shape for k, v in out.items()})
+    if "--full" in sys.argv:
+        # full-size C, D and the 200 000-bin D: SHA-256 of the reference's bins and lut, norms, NLL
+        import json
+        full = {}
+        for name, make in cases.FULL_CASES.items():
+            fit = make()
+            pars = cases.off_nominal(fit, 41)
+            bins, norms, lut = ref.eval_all(fit, pars)
+            nll, ev = ref.nll(fit, lut, pars, norms)
+            full[name] = {"pars": [float(v) for v in pars], "bins_sha256": cases.digest(bins),
+                          "lut_sha256": cases.digest(lut), "norms": [int(v) for v in norms],
+                          "nll": float(nll), "evsum": float(ev), "bins_sum": int(bins.sum()),
+                          "nonzero_bins": int((bins > 0).sum())}
+            print(name, full[name]["bins_sha256"][:16], full[name]["nll"])
+            del fit, bins, lut
+        with open(os.path.join(ROOT, "tests", "golden", "ref_full_size.json"), "w") as f:
+            json.dump(full, f, indent=1)
 
 
 if __name__ == "__main__":

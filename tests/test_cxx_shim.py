@@ -178,3 +178,22 @@ def test_cxx_command_line_equals_python_command_line(tmp_path):
     assert np.allclose(limits(rc.stdout), limits(rp.stdout), rtol=1e-5)
     assert np.allclose(limits(r1.stdout), limits(rp.stdout), rtol=1e-5)
     assert "sxmc: Median upper limit:" in rc.stdout
+
+    # fit.debug_mode reaches every experiment's MCMC::operator() (src/sxmc.cpp:97) on both command
+    # lines: every step accepted, no chain reset at burn-in -> nsteps rows, identical files
+    import json as _json
+    import re as _re
+    text = CONFIG.replace(".npz", ".npy")
+    assert '"debug_mode"' not in text
+    text = _re.sub(r'"nsteps"\s*:', '"debug_mode": true, "nsteps":', text, count=1)
+    cfgd = tmp_path / "fit_debug.json"
+    cfgd.write_text(text)
+    rd = subprocess.run([SXMC_BIN, str(cfgd), str(tmp_path / "dbg_cxx")], capture_output=True, text=True, timeout=900)
+    assert rd.returncode == 0, rd.stdout[-3000:] + rd.stderr[-3000:]
+    rq = subprocess.run([sys.executable, "-m", "sxmc_b200", str(cfgd), str(tmp_path / "dbg_py")], cwd=ROOT,
+                        capture_output=True, text=True, timeout=900)
+    assert rq.returncode == 0, rq.stdout[-3000:] + rq.stderr[-3000:]
+    for i in range(3):
+        a = np.load(tmp_path / "dbg_cxx" / ("example_%d.npy" % i))
+        b = np.load(tmp_path / "dbg_py" / ("example_%d.npy" % i))
+        assert a.shape == b.shape == (3000, 5) and a.tobytes() == b.tobytes(), i

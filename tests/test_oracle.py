@@ -140,6 +140,30 @@ def test_port_matches_committed_ref_fixtures():
         assert v == float(z[name + "_nll"]) and e == float(z[name + "_evsum"])
 
 
+@pytest.mark.parametrize("name", ["CT", "P2", "P3", "P4"])
+def test_port_equals_ref_on_ctscale_and_polynomial_systematics(name):
+    """CTSCALE and 2-, 3-, 4-coefficient series (src/pdfz.cpp:310-325): the restatement against
+    the compiled reference, live and against the committed reference output."""
+    from tests import cases
+    fit = cases.POLY_CASES[name]()
+    z = np.load(os.path.join(HERE, "golden", "ref_fixtures.npz"))
+    pars = cases.off_nominal(fit, 31)
+    assert np.array_equal(pars, z[name + "_pars"])
+    b0, n0, l0 = port.eval_all(fit, pars)
+    assert np.array_equal(b0, z[name + "_bins"]) and np.array_equal(n0, z[name + "_norms"])
+    assert l0.tobytes() == z[name + "_lut"].tobytes()
+    v0, e0 = port.nll(fit, l0, pars, n0)
+    assert v0 == float(z[name + "_nll"]) and e0 == float(z[name + "_evsum"])
+    assert int(n0.sum()) > 0 and int(n0.sum()) < fit.total_samples()      # the arms move samples across the edges
+    if oracle.have_ref():
+        from oracle import ref
+        for seed in (31, 32):
+            pars = cases.off_nominal(fit, seed)
+            b0, n0, l0 = port.eval_all(fit, pars)
+            b1, n1, l1 = ref.eval_all(fit, pars)
+            assert np.array_equal(b0, b1) and np.array_equal(n0, n1) and l0.tobytes() == l1.tobytes()
+
+
 def test_projection_estimator_walk_on_known_shapes():
     """sxmc::errors::Projection (src/error_estimators/projection.cpp:14-77), host restatement:
     a Gaussian column gives a central interval with about cl coverage around the mean; a column

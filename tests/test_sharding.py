@@ -76,23 +76,22 @@ def test_gloo_world2_gathers_limits_in_experiment_order(tmp_path):
 
 
 @pytest.mark.gpu
-def test_nccl_sample_sharded_chain_equals_single_gpu_chain(tmp_path):
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sample_sharded_chain_equals_single_gpu_chain(tmp_path, world):
+    """NCCL and both peer-memory exchanges at 2, 4 and 8 ranks: bins, norms, rows and the accepted
+    count of the sharded chain equal the unsharded chain bit for bit on EVERY rank.  Each world
+    size runs where the box has that many GPUs."""
     import torch
-    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    _torchrun(2, "nccl_sample_sharded", tmp_path)
-    z0 = np.load(tmp_path / "sharded_rank0.npz")
-    z1 = np.load(tmp_path / "sharded_rank1.npz")
-    for k in ("bins", "norms", "rows"):
-        assert np.array_equal(z0[k], z1[k]), k                 # ranks agree bit for bit
-        assert np.array_equal(z0[k], z0["single_" + k]), k     # and equal the unsharded chain
-    assert z0["accepted"] == z0["single_accepted"] == z1["accepted"]
+    if not torch.cuda.is_available() or torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (this box has %d)" % (world, torch.cuda.device_count() if torch.cuda.is_available() else 0))
+    _torchrun(world, "nccl_sample_sharded", tmp_path, timeout=900)
+    zs = [np.load(tmp_path / ("sharded_rank%d.npz" % r)) for r in range(world)]
+    z0 = zs[0]
     assert z0["rows"].shape[0] > 0
-    # the peer-memory exchange gives the same chain, on both ranks
-    # (p2p_: one-shot form, p2p2_: reduce-scatter + all-gather form)
-    for z in (z0, z1):
-        for pre in ("p2p_", "p2p2_"):
+    for z in zs:
+        for pre in ("", "p2p_", "p2p2_"):        # NCCL, one-shot, reduce-scatter + all-gather
             for k in ("bins", "norms", "rows"):
-                assert np.array_equal(z[pre + k], z0["single_" + k]), pre + k
+                assert np.array_equal(z[pre + k], z0["single_" + k]), (pre + k)
             assert z[pre + "accepted"] == z0["single_accepted"]
+        for pre in ("p2p_", "p2p2_"):
             assert not z[pre + "aborted"] and z[pre + "exchanges"] == 301     # initial evaluation + 300 steps
