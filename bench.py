@@ -102,6 +102,8 @@ def parse_args(argv=None):
     ap.add_argument("--flush", default="auto", choices=["auto", "always", "never"],
                     help="L2 flush (256 MiB memset) before every timed step; auto = only when a step "
                          "streams less than 4x the L2")
+    ap.add_argument("--static-bin", action="store_true",
+                    help="measurement knob: the static-partition binning kernel instead of the dynamic-tail one")
     ap.add_argument("--experiments", type=int, default=296,
                     help="workload E: fake experiments per GPU (whole batches of 148)")
     ap.add_argument("--esteps", type=int, default=20000, help="workload E: MCMC steps per experiment")
@@ -181,6 +183,7 @@ class ClockSampler:
 
     def __init__(self, index, period_s=0.025):
         self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.power_w, self.mem_mhz = [], []
         self.period_s = period_s
         self._stop = threading.Event()
         self._t = None
@@ -198,6 +201,8 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.mem_mhz.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_MEM)))
+                self.power_w.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
                 r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
                 for bit, name in self.REASONS.items():
                     if r & bit:
@@ -223,7 +228,11 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(self.reasons), "samples": len(self.samples),
-                "sample_period_ms": 1e3 * self.period_s}
+                "sample_period_ms": 1e3 * self.period_s,
+                "sm_mhz_min": float(np.min(self.samples)),
+                "mem_mhz": float(np.median(self.mem_mhz)) if self.mem_mhz else None,
+                "power_w_median": float(np.median(self.power_w)) if self.power_w else None,
+                "power_w_max": float(np.max(self.power_w)) if self.power_w else None}
 
 
 # ---------------------------------------------------------------------------------------
@@ -595,6 +604,9 @@ def extra_workload(name, args, local, peak, peak_src, steps, warmup, repeats):
 def run_own_arm(args, rank, world, local):
     import torch
     init_device(world, local)
+    if args.static_bin:
+        from sxmc_b200 import pdfz
+        pdfz.set_stream_tuning(False)
     peak, peak_src = measured_peak()
     sampler = ClockSampler(local)
     K = args.steps

@@ -86,25 +86,34 @@ class Parser {
     if (c == '{') {
       v.type = Value::OBJECT;
       ++i_;
+      skip();
+      if (i_ < s_.size() && s_[i_] == '}') { ++i_; return v; }
       for (;;) {
         skip();
-        if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }     // commas are separators, not required
-        if (i_ < s_.size() && s_[i_] == '}') { ++i_; break; }
-        if (i_ >= s_.size() || s_[i_] != '"') fail("member name expected");
+        if (i_ >= s_.size() || s_[i_] != '"') fail("Missing '}' or object member name");
         const std::string key = string();
         skip();
-        if (i_ >= s_.size() || s_[i_] != ':') fail("':' expected after \"" + key + "\"");
+        if (i_ >= s_.size() || s_[i_] != ':') fail("Missing ':' after object member name");
         ++i_;
         v.obj[key] = value();
+        skip();
+        // jsoncpp 0.6 (the reference's reader) insists on the separator: config/example.json as
+        // shipped, with its missing comma, does not load in the reference either
+        if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }
+        if (i_ < s_.size() && s_[i_] == '}') { ++i_; break; }
+        fail("Missing ',' or '}' in object declaration");
       }
     } else if (c == '[') {
       v.type = Value::ARRAY;
       ++i_;
+      skip();
+      if (i_ < s_.size() && s_[i_] == ']') { ++i_; return v; }
       for (;;) {
+        v.arr.push_back(value());
         skip();
         if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }
         if (i_ < s_.size() && s_[i_] == ']') { ++i_; break; }
-        v.arr.push_back(value());
+        fail("Missing ',' or ']' in array declaration");
       }
     } else if (c == '"') {
       v.type = Value::STRING;

@@ -331,7 +331,8 @@ FitConfig::FitConfig(std::string filename) {
     s.dataset = (unsigned)need(c, "dataset", where.c_str()).asInt();
     datasets.insert(s.dataset);
     if (c.isMember("rate") == c.isMember("scale")) fail(where + ": exactly one of 'rate' and 'scale' is required");
-    s.nexpected = c.isMember("rate") ? c["rate"].asFloat() : -1.0 / c["scale"].asFloat();
+    // `float nexpected = -1.0 / config["scale"].asFloat()` (src/config.cpp:213-221): rounded to float
+    s.nexpected = c.isMember("rate") ? c["rate"].asFloat() : (float)(-1.0 / c["scale"].asFloat());
     std::vector<Systematic> systs;
     const jsonmin::Value& slist = c["systematics"];
     for (size_t q = 0; q < slist.size(); ++q)

@@ -152,7 +152,82 @@ static std::vector<float> ensemble(FitConfig& fc, const std::string& output_path
   return limits;
 }
 
+// `sxmc --dump-config fit.json`: what FitConfig made of the file, as JSON text in the schema of
+// oracle/ref_glue.cpp::ref_config_dump (the same dump of the reference's own FitConfig) -- the
+// parity tests compare the two key by key.
+static void dump_config(const FitConfig& fc, std::ostream& o) {
+  o.precision(17);
+  o << "{\"nexperiments\": " << fc.nexperiments << ", \"nsteps\": " << fc.nsteps
+    << ", \"confidence\": " << (double)fc.confidence << ", \"burnin_fraction\": " << (double)fc.burnin_fraction
+    << ", \"debug_mode\": " << (fc.debug_mode ? "true" : "false") << ", \"plots\": " << (fc.plots ? "true" : "false")
+    << ", \"seed\": " << fc.seed << ", \"signal_name\": \"" << fc.signal_name << "\", \"output_prefix\": \""
+    << fc.output_prefix << "\", \"error_type\": \"" << (fc.error_type == ERROR_PROJECTION ? "projection" : "contour")
+    << "\", \"samples\": \"" << fc.samples << "\",\n \"sample_fields\": [";
+  for (size_t i = 0; i < fc.sample_fields.size(); i++) o << (i ? ", " : "") << "\"" << fc.sample_fields[i] << "\"";
+  o << "],\n \"datasets\": [";
+  size_t nd = 0;
+  for (std::set<unsigned>::const_iterator it = fc.datasets.begin(); it != fc.datasets.end(); ++it) o << (nd++ ? ", " : "") << *it;
+  o << "],\n \"observables\": [";
+  for (size_t i = 0; i < fc.observables.size(); i++) {
+    const Observable& b = fc.observables[i];
+    o << (i ? ", " : "") << "{\"name\": \"" << b.name << "\", \"field\": \"" << b.field << "\", \"field_index\": "
+      << b.field_index << ", \"bins\": " << b.bins << ", \"lower\": " << (double)b.lower << ", \"upper\": "
+      << (double)b.upper << "}";
+  }
+  o << "],\n \"cuts\": [";
+  for (size_t i = 0; i < fc.cuts.size(); i++) {
+    const Observable& b = fc.cuts[i];
+    o << (i ? ", " : "") << "{\"name\": \"" << b.name << "\", \"field\": \"" << b.field << "\", \"lower\": "
+      << (double)b.lower << ", \"upper\": " << (double)b.upper << "}";
+  }
+  o << "],\n \"sources\": [";
+  for (size_t i = 0; i < fc.sources.size(); i++) {
+    const Source& b = fc.sources[i];
+    o << (i ? ", " : "") << "{\"name\": \"" << b.name << "\", \"index\": " << b.index << ", \"mean\": "
+      << (double)b.mean << ", \"sigma\": " << (double)b.sigma << ", \"fixed\": " << (b.fixed ? "true" : "false") << "}";
+  }
+  o << "],\n \"systematics\": [";
+  for (size_t i = 0; i < fc.systematics.size(); i++) {
+    const Systematic& y = fc.systematics[i];
+    o << (i ? ", " : "") << "{\"name\": \"" << y.name << "\", \"type\": " << (int)y.type
+      << ", \"observable_field\": \"" << y.observable_field << "\", \"truth_field\": \"" << y.truth_field
+      << "\", \"observable_field_index\": " << y.observable_field_index << ", \"truth_field_index\": "
+      << (y.type == pdfz::Systematic::RESOLUTION_SCALE ? (long)y.truth_field_index : -1L)
+      << ", \"npars\": " << y.npars << ", \"fixed\": " << (y.fixed ? "true" : "false") << ", \"means\": [";
+    for (size_t k = 0; k < y.npars; k++) o << (k ? ", " : "") << y.means[k];
+    o << "], \"sigmas\": [";
+    for (size_t k = 0; k < y.npars; k++) o << (k ? ", " : "") << y.sigmas[k];
+    o << "], \"pidx\": [";
+    for (size_t k = 0; k < y.pidx.size(); k++) o << (k ? ", " : "") << y.pidx[k];
+    o << "]}";
+  }
+  o << "],\n \"signals\": [";
+  for (size_t i = 0; i < fc.signals.size(); i++) {
+    const Signal& g = fc.signals[i];
+    std::vector<float> rows;
+    if (g.histogram) {
+      rows.resize(sxmc_hist_nsamples(g.histogram->handle()) * fc.sample_fields.size());
+      if (!rows.empty() && sxmc_hist_get_samples(g.histogram->handle(), rows.data()) != SXMC_OK)
+        throw std::runtime_error(sxmc_last_error());
+    }
+    unsigned long long sum = 0;      // order-sensitive checksum of the sample rows, as in ref_config_dump
+    for (size_t k = 0; k < rows.size(); k++) {
+      unsigned bits;
+      std::memcpy(&bits, &rows[k], 4);
+      sum += (unsigned long long)(k + 1) * bits;
+    }
+    o << (i ? ", " : "") << "{\"name\": \"" << g.name << "\", \"filename\": \"" << g.filename << "\", \"dataset\": "
+      << g.dataset << ", \"source\": \"" << g.source.name << "\", \"source_index\": " << g.source.index
+      << ", \"nexpected\": " << g.nexpected << ", \"n_mc\": " << g.n_mc << ", \"nsample_floats\": " << rows.size()
+      << ", \"sample_checksum\": \"" << sum << "\", \"systematic_names\": [";
+    for (size_t k = 0; k < g.systematic_names.size(); k++) o << (k ? ", " : "") << "\"" << g.systematic_names[k] << "\"";
+    o << "]}";
+  }
+  o << "]}\n";
+}
+
 int main(int argc, char* argv[]) {
+  const bool dump = argc == 3 && std::string(argv[1]) == "--dump-config";
   if (argc != 3) {
     std::cerr << "Usage: " << argv[0] << " fit_configuration.json output_path" << std::endl;
     return 1;
@@ -165,6 +240,13 @@ int main(int argc, char* argv[]) {
     if (sxmc_init(dev ? std::atoi(dev) : 0) != SXMC_OK) {      // no CUDA device: there is no CPU path
       std::cerr << "sxmc: " << sxmc_last_error() << std::endl;
       return 3;
+    }
+    if (dump) {
+      std::streambuf* quiet = std::cout.rdbuf(NULL);      // FitConfig's progress lines
+      FitConfig fc(argv[2]);
+      std::cout.rdbuf(quiet);
+      dump_config(fc, std::cout);
+      return 0;
     }
     std::string output_path(argv[2]);
     if (output_path.empty() || output_path[output_path.size() - 1] != '/') output_path += "/";

@@ -120,6 +120,11 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * every signal reads the same dataset (the multi-dataset form) -- used by the parity tests and
  * measurements to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
+/* The binning kernel for launches that stream far more than the chip holds cuts a static share of
+ * every signal's samples over the SMs and hands the rest out in tiles through a global counter
+ * (dynamic tail).  enable 0 = always the static kernel; static_permille = static share of the fair
+ * per-SM load (default 700, < 0 keeps it); tile_chunks = 0 automatic.  Measurement knob. */
+int sxmc_set_stream_tuning(int enable, int static_permille, int tile_chunks);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
 int sxmc_enable_kernel_timing(int on);

@@ -185,3 +185,16 @@ def mcmc(fit, nsteps, burnin_fraction, normals, uniforms, debug_mode=False,
         for h in hists:
             h.close()
     return dict(chain=chain[:rows].copy(), tape_used=used)
+
+
+def config_dump(json_path, verbose=False):
+    """The reference's own FitConfig (src/config.cpp:19-297) run on `json_path` (signals in .npy
+    tables with .fields sidecars), as a dict: every ordering / rounding decision it took."""
+    import json
+    L = lib()
+    L.ref_config_dump.restype = C.c_long
+    buf = C.create_string_buffer(1 << 20)
+    n = L.ref_config_dump(str(json_path).encode(), int(verbose), buf, C.c_size_t(len(buf)))
+    if n < 0:
+        raise RefError("FitConfig threw")
+    return json.loads(buf.value.decode())

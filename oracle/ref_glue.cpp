@@ -11,8 +11,11 @@
 // oracle/root_stubs/*.h.  gRandom is a "tape" generator (root_stubs/TRandom.h) so the
 // reference chain can be driven by exactly the random numbers the CUDA chain draws.
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <fstream>
 #include <iostream>
+#include <sstream>
 #include <string>
 #include <vector>
 
@@ -30,6 +33,7 @@
 #include <sxmc/likelihood.h>
 #include <sxmc/utils.h>
 #include <sxmc/ttree_io.h>
+#include <sxmc/config.h>
 
 // ---- symbols the reference expects from ROOT / from TUs that need real ROOT ----
 static TRandom g_random_instance;
@@ -45,11 +49,43 @@ LikelihoodSpace::LikelihoodSpace(TNtuple* _samples, float _cl, ErrorType _error_
     : error_type(_error_type), nll(0), cl(_cl), samples(_samples) {}
 LikelihoodSpace::~LikelihoodSpace() { delete samples; }
 
-// src/io/ttree_io.cpp needs ROOT TFile/TTree; Signal's file-loading ctor is never used here.
+// src/io/ttree_io.cpp needs ROOT TFile/TTree.  Same signature and contract
+// (src/io/ttree_io.cpp:21-159: row-major float table, rank = {rows, columns}, column names), read
+// from the flat-table form this repo's command lines accept: `<file>.npy` holding a C-order
+// [n, k] '<f4' array next to a `<file>.npy.fields` text file with one column name per line.
+// Lets the reference's own FitConfig / Signal constructors run on the test configurations.
 namespace sxmc { namespace io {
-int read_float_vector_ttree(const std::string&, std::vector<float>&,
-                            std::vector<unsigned int>&, std::vector<std::string>&) {
-  return -1;
+int read_float_vector_ttree(const std::string& filename, std::vector<float>& data,
+                            std::vector<unsigned int>& rank, std::vector<std::string>& ttree_fields) {
+  data.clear(); rank.clear(); ttree_fields.clear();
+  std::ifstream ff((filename + ".fields").c_str());
+  std::string line;
+  while (std::getline(ff, line)) {
+    while (!line.empty() && (line[line.size() - 1] == '\r' || line[line.size() - 1] == ' ')) line.erase(line.size() - 1);
+    if (!line.empty()) ttree_fields.push_back(line);
+  }
+  std::ifstream f(filename.c_str(), std::ios::binary);
+  char magic[10];
+  if (!f.read(magic, 10) || std::memcmp(magic, "\x93NUMPY", 6) != 0) return -1;
+  size_t hlen = (unsigned char)magic[8] | ((size_t)(unsigned char)magic[9] << 8);
+  if (magic[6] != 1) {   // version 2/3: 4-byte header length
+    char more[2];
+    if (!f.read(more, 2)) return -1;
+    hlen |= ((size_t)(unsigned char)more[0] << 16) | ((size_t)(unsigned char)more[1] << 24);
+  }
+  std::string header(hlen, ' ');
+  if (!f.read(&header[0], hlen)) return -1;
+  if (header.find("'<f4'") == std::string::npos || header.find("'fortran_order': False") == std::string::npos) return -2;
+  size_t a = header.find("'shape': ("), b = header.find(")", a);
+  if (a == std::string::npos || b == std::string::npos) return -2;
+  unsigned long rows = 0, cols = 0;
+  if (std::sscanf(header.substr(a + 10, b - a - 10).c_str(), "%lu, %lu", &rows, &cols) != 2) return -2;
+  if (cols != ttree_fields.size()) return -3;
+  data.resize((size_t)rows * cols);
+  if (!data.empty() && !f.read((char*)&data[0], sizeof(float) * data.size())) return -4;
+  rank.push_back((unsigned)rows);
+  rank.push_back((unsigned)cols);
+  return 0;
 }
 } }
 
@@ -67,6 +103,12 @@ public:
   const int* ReadBins() { return read_bins ? read_bins->readOnlyHostPtr() : 0; }
   size_t NReadBins() { return read_bins ? read_bins->size() : 0; }
   double BinVolume() const { return bin_volume; }
+  // the sample rows of ANY EvalHist (protected member read through this subclass)
+  static std::vector<float> Rows(pdfz::EvalHist* h) {
+    EvalHistProbe* p = static_cast<EvalHistProbe*>(h);
+    const float* s = p->samples.readOnlyHostPtr();
+    return std::vector<float>(s, s + p->samples.size());
+  }
 };
 
 void set_err(char* err, int errlen, const std::string& msg) {
@@ -249,6 +291,92 @@ long ref_mcmc_run(int nsources, const float* src_mean, const float* src_sigma,
     std::memcpy(chain_out, &nt->rows[0], sizeof(float) * width * (size_t)ncopy);
   delete ls;
   return rows;
+}
+
+
+// The reference's own FitConfig (src/config.cpp:19-297) run on a JSON file whose signals point at
+// .npy tables, written out as JSON text: every ordering and rounding decision a drop-in FitConfig
+// has to reproduce.  Returns the text length (truncated to cap), or -1 when FitConfig throws.
+long ref_config_dump(const char* json_path, int verbose, char* out, size_t cap) {
+  std::ostringstream o;
+  o.precision(17);
+  try {
+    CoutSilencer quiet(!verbose);
+    FitConfig fc(json_path);
+    o << "{\"nexperiments\": " << fc.nexperiments << ", \"nsteps\": " << fc.nsteps
+      << ", \"confidence\": " << (double)fc.confidence << ", \"burnin_fraction\": " << (double)fc.burnin_fraction
+      << ", \"debug_mode\": " << (fc.debug_mode ? "true" : "false") << ", \"plots\": " << (fc.plots ? "true" : "false")
+      << ", \"seed\": " << fc.seed << ", \"signal_name\": \"" << fc.signal_name << "\", \"output_prefix\": \""
+      << fc.output_prefix << "\", \"error_type\": \"" << (fc.error_type == ERROR_PROJECTION ? "projection" : "contour")
+      << "\", \"samples\": \"" << fc.samples << "\",\n \"sample_fields\": [";
+    for (size_t i = 0; i < fc.sample_fields.size(); i++) o << (i ? ", " : "") << "\"" << fc.sample_fields[i] << "\"";
+    o << "],\n \"datasets\": [";
+    size_t nd = 0;
+    for (std::set<unsigned>::const_iterator it = fc.datasets.begin(); it != fc.datasets.end(); ++it) o << (nd++ ? ", " : "") << *it;
+    o << "],\n \"observables\": [";
+    for (size_t i = 0; i < fc.observables.size(); i++) {
+      const Observable& b = fc.observables[i];
+      o << (i ? ", " : "") << "{\"name\": \"" << b.name << "\", \"field\": \"" << b.field << "\", \"field_index\": "
+        << b.field_index << ", \"bins\": " << b.bins << ", \"lower\": " << (double)b.lower << ", \"upper\": "
+        << (double)b.upper << "}";
+    }
+    o << "],\n \"cuts\": [";
+    for (size_t i = 0; i < fc.cuts.size(); i++) {
+      const Observable& b = fc.cuts[i];
+      o << (i ? ", " : "") << "{\"name\": \"" << b.name << "\", \"field\": \"" << b.field << "\", \"lower\": "
+        << (double)b.lower << ", \"upper\": " << (double)b.upper << "}";
+    }
+    o << "],\n \"sources\": [";
+    for (size_t i = 0; i < fc.sources.size(); i++) {
+      const Source& b = fc.sources[i];
+      o << (i ? ", " : "") << "{\"name\": \"" << b.name << "\", \"index\": " << b.index << ", \"mean\": "
+        << (double)b.mean << ", \"sigma\": " << (double)b.sigma << ", \"fixed\": " << (b.fixed ? "true" : "false") << "}";
+    }
+    o << "],\n \"systematics\": [";
+    for (size_t i = 0; i < fc.systematics.size(); i++) {
+      const Systematic& y = fc.systematics[i];
+      o << (i ? ", " : "") << "{\"name\": \"" << y.name << "\", \"type\": " << (int)y.type
+        << ", \"observable_field\": \"" << y.observable_field << "\", \"truth_field\": \"" << y.truth_field
+        << "\", \"observable_field_index\": " << y.observable_field_index << ", \"truth_field_index\": "
+        << (y.type == pdfz::Systematic::RESOLUTION_SCALE ? (long)y.truth_field_index : -1L)
+        << ", \"npars\": " << y.npars << ", \"fixed\": " << (y.fixed ? "true" : "false") << ", \"means\": [";
+      for (size_t k = 0; k < y.npars; k++) o << (k ? ", " : "") << y.means[k];
+      o << "], \"sigmas\": [";
+      for (size_t k = 0; k < y.npars; k++) o << (k ? ", " : "") << y.sigmas[k];
+      o << "], \"pidx\": [";
+      for (size_t k = 0; k < y.pidx.size(); k++) o << (k ? ", " : "") << y.pidx[k];
+      o << "]}";
+    }
+    o << "],\n \"signals\": [";
+    for (size_t i = 0; i < fc.signals.size(); i++) {
+      const Signal& g = fc.signals[i];
+      std::vector<float> rows;
+      pdfz::EvalHist* h = dynamic_cast<pdfz::EvalHist*>(g.histogram);
+      if (h) rows = EvalHistProbe::Rows(h);      // all sample_fields columns, as the Signal built them
+      // order-sensitive checksum of the sample rows the PDF was built from (columns in
+      // sample_fields order, cuts applied): sum of (index+1) * bit pattern, mod 2^64
+      unsigned long long sum = 0;
+      for (size_t k = 0; k < rows.size(); k++) {
+        unsigned bits; std::memcpy(&bits, &rows[k], 4);
+        sum += (unsigned long long)(k + 1) * bits;
+      }
+      o << (i ? ", " : "") << "{\"name\": \"" << g.name << "\", \"filename\": \"" << g.filename << "\", \"dataset\": "
+        << g.dataset << ", \"source\": \"" << g.source.name << "\", \"source_index\": " << g.source.index
+        << ", \"nexpected\": " << g.nexpected << ", \"n_mc\": " << g.n_mc << ", \"nsample_floats\": " << rows.size()
+        << ", \"sample_checksum\": \"" << sum << "\", \"systematic_names\": [";
+      for (size_t k = 0; k < g.systematic_names.size(); k++) o << (k ? ", " : "") << "\"" << g.systematic_names[k] << "\"";
+      o << "]}";
+    }
+    o << "]}\n";
+  } catch (...) {
+    return -1;
+  }
+  const std::string t = o.str();
+  if (out && cap) {
+    std::strncpy(out, t.c_str(), cap - 1);
+    out[cap - 1] = 0;
+  }
+  return (long)t.size();
 }
 
 }  // extern "C"

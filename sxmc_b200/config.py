@@ -45,14 +45,14 @@ def _need(obj, key, where):
 
 
 def load_json(filename):
-    """jsoncpp is lenient where Python's json is not: it accepts // and /* */ comments and the
-    shipped example even lacks a comma between two members (`config/example.json:42-43`).
-    Comments are stripped and a missing comma between `}` and the next `"key":` is supplied."""
+    """jsoncpp accepts // and /* */ comments where Python's json does not: they are stripped.
+    Like the reference's reader (jsoncpp 0.6, pinned by tests/test_config.py against the compiled
+    reference) a missing comma is a parse error -- `config/example.json:42-43` as shipped does not
+    load in the reference either."""
     with open(filename) as f:
         text = f.read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     text = re.sub(r"(^|[^:\"])//[^\n]*", r"\1", text)
-    text = re.sub(r"([}\]])(\s*\n\s*)(\"[^\"\n]*\"\s*:)", r"\1,\2\3", text)
     try:
         return json.loads(text)
     except json.JSONDecodeError as e:
@@ -115,13 +115,17 @@ def read_dataset_to_samples(table, fields, dataset_id, sample_fields, cuts):
     """Signal::read_dataset_to_samples (src/signal.cpp:50-108): apply the cuts on the file's own
     columns, then pick the sample columns in `sample_fields` order and append the dataset tag."""
     keep = np.ones(table.shape[0], dtype=bool)
-    for c in cuts:
-        for j, name in enumerate(fields):
-            if name == c.field:
-                col = table[:, j]
-                # float column against the Observable's float bounds widened to double (:57-58,86)
-                keep &= ~((col.astype(np.float64) < float(np.float32(c.lower))) |
-                          (col.astype(np.float64) > float(np.float32(c.upper))))
+    for j, name in enumerate(fields):
+        # the lookup table of :57-67 holds ONE cut per file column: the last one naming it wins
+        cut = None
+        for c in cuts:
+            if c.field == name:
+                cut = c
+        if cut is not None:
+            col = table[:, j]
+            # float column against the Observable's float bounds widened to double (:57-58,86)
+            keep &= ~((col.astype(np.float64) < float(np.float32(cut.lower))) |
+                      (col.astype(np.float64) > float(np.float32(cut.upper))))
     idx = []
     for name in sample_fields[:-1]:
         if name not in fields:
@@ -294,7 +298,9 @@ class FitConfig:
             self.datasets.add(dataset)
             if ("rate" in cfg) == ("scale" in cfg):
                 raise ConfigError("%s: exactly one of 'rate' and 'scale' is required" % where)
-            nexpected = float(np.float32(cfg["rate"])) if "rate" in cfg else -1.0 / float(np.float32(cfg["scale"]))
+            # `float nexpected = -1.0 / config["scale"].asFloat()` (:213-221): the quotient is rounded to float
+            nexpected = (float(np.float32(cfg["rate"])) if "rate" in cfg
+                         else float(np.float32(-1.0 / float(np.float32(cfg["scale"])))))
             systs = [y for yname in cfg.get("systematics", []) for y in self.systematics if y.name == yname]
             source = next((s for s in self.sources if s.name == cfg.get("source", name)), None)
             if source is None:

@@ -65,6 +65,7 @@ struct Batch {
   unsigned long long* prefix_dev = nullptr;
   EvalPdfJob* ep_host = nullptr;   // pinned
   EvalPdfJob* ep_dev = nullptr;
+  unsigned* queue_dev = nullptr;   // tile queue of the streaming binning kernel (self re-arming)
   int cap = 0;
   BinLaunch launch;
   long long max_points = 0;
@@ -79,6 +80,8 @@ struct Batch {
     SXMC_CUDA(cudaMalloc(&prefix_dev, sizeof(unsigned long long) * (n + 1)));
     SXMC_CUDA(cudaMallocHost(&ep_host, sizeof(EvalPdfJob) * n));
     SXMC_CUDA(cudaMalloc(&ep_dev, sizeof(EvalPdfJob) * n));
+    SXMC_CUDA(cudaMalloc(&queue_dev, sizeof(unsigned) * 2));
+    SXMC_CUDA(cudaMemset(queue_dev, 0, sizeof(unsigned) * 2));
     cap = n;
     return SXMC_OK;
   }
@@ -89,6 +92,8 @@ struct Batch {
     if (prefix_dev) cudaFree(prefix_dev);
     if (ep_host) cudaFreeHost(ep_host);
     if (ep_dev) cudaFree(ep_dev);
+    if (queue_dev) cudaFree(queue_dev);
+    queue_dev = nullptr;
     host = nullptr; dev = nullptr; prefix_host = nullptr; prefix_dev = nullptr;
     ep_host = nullptr; ep_dev = nullptr; cap = 0;
   }
@@ -117,6 +122,7 @@ struct sxmc_hist {
   unsigned* bins_dev = nullptr;
   int* read_bins_dev = nullptr;
   size_t npoints = 0;
+  size_t read_bins_cap = 0;             // allocated ints (grow-only: the pointer is baked into chain tables / graphs)
   float* pdf_dev = nullptr; long pdf_offset = 0, pdf_stride = 1;
   unsigned* norm_dev = nullptr; long norm_offset = 0;
   const double* param_dev = nullptr; long param_offset = 0, param_stride = 1;
@@ -242,6 +248,7 @@ static void plan_launch(Batch& b, int n) {
   memset(&L, 0, sizeof L);
   L.jobs_host = b.host;
   L.jobs_dev = b.dev;
+  L.queue_dev = b.queue_dev;
   L.prefix_dev = b.prefix_dev;
   L.njobs = n;
   bool uniform = true;
@@ -388,6 +395,10 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_no_group = (force_generic >> 5) & 1;
   return SXMC_OK;
 }
+int sxmc_set_stream_tuning(int enable, int static_permille, int tile_chunks) {
+  set_bin_stream_tuning(enable, static_permille, tile_chunks);
+  return SXMC_OK;
+}
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
 int sxmc_bin_debug_stamps(int enable, unsigned long long* out256x32) {
   static unsigned long long* dev = nullptr;
@@ -502,24 +513,34 @@ int sxmc_hist_add_systematic(sxmc_hist* h, int type, int obs, int extra_field, i
   return SXMC_OK;
 }
 
+// SetEvalPoints from points already on the device, enqueued on `stream` without a host sync
+// (sxmc_chain_set_data uploads the data events once for all PDFs of a fit).
+static int hist_set_eval_points_dev(sxmc_hist* h, const float* pts_dev, size_t np, cudaStream_t stream) {
+  if (np > h->read_bins_cap || !h->read_bins_dev) {
+    cudaFree(h->read_bins_dev);
+    h->read_bins_dev = nullptr;
+    h->read_bins_cap = 0;
+    SXMC_CUDA(cudaMalloc(&h->read_bins_dev, sizeof(int) * (np ? np : 1)));
+    h->read_bins_cap = np ? np : 1;
+  }
+  h->npoints = np;
+  if (np == 0) return SXMC_OK;
+  PrepGeo g;
+  fill_prep_geo(h, g);
+  return launch_read_bins(pts_dev, (long long)np, h->nobs, g, h->dataset, h->read_bins_dev, stream);
+}
+
 int sxmc_hist_set_eval_points(sxmc_hist* h, const float* points, size_t nfloats) {
   if (!h) SXMC_INVAL("sxmc_hist_set_eval_points: NULL handle");
   if (nfloats % (size_t)(h->nobs + 1) != 0)
     SXMC_INVAL("Number of entries in evaluation points array not divisible by number of observables.");
   const size_t np = nfloats / (size_t)(h->nobs + 1);
-  cudaFree(h->read_bins_dev);
-  h->read_bins_dev = nullptr;
-  h->npoints = np;
-  SXMC_CUDA(cudaMalloc(&h->read_bins_dev, sizeof(int) * (np ? np : 1)));
-  if (np == 0) return SXMC_OK;
   float* pts = nullptr;
-  SXMC_CUDA(cudaMalloc(&pts, sizeof(float) * nfloats));
-  cudaError_t e = cudaMemcpyAsync(pts, points, sizeof(float) * nfloats, cudaMemcpyHostToDevice, h->stream);
+  if (np) SXMC_CUDA(cudaMalloc(&pts, sizeof(float) * nfloats));
+  cudaError_t e = np ? cudaMemcpyAsync(pts, points, sizeof(float) * nfloats, cudaMemcpyHostToDevice, h->stream) : cudaSuccess;
   int rc = SXMC_OK;
   if (e == cudaSuccess) {
-    PrepGeo g;
-    fill_prep_geo(h, g);
-    rc = launch_read_bins(pts, (long long)np, h->nobs, g, h->dataset, h->read_bins_dev, h->stream);
+    rc = hist_set_eval_points_dev(h, pts, np, h->stream);
     e = cudaStreamSynchronize(h->stream);
   }
   cudaFree(pts);
@@ -703,6 +724,13 @@ struct sxmc_chain {
   double* partials = nullptr;
   unsigned* ticket = nullptr;
   float* lut_dev = nullptr;
+  size_t lut_cap = 0;                   // floats (grow-only)
+  float* ptable_dev = nullptr;          // [nsignals][total_nbins] PDF values of the step (per-event lookup)
+  bool ptable_valid = false;            // holds the values of the histograms the fixed-systematics steps read
+  float* data_dev = nullptr;            // the data events, uploaded once per sxmc_chain_set_data
+  size_t data_cap = 0;                  // floats (grow-only)
+  std::vector<const void*> table_sig;   // what the uploaded tables and the captured graph bake: pointers and nevents
+  std::vector<const void*> layout_sig;  // the part of it the monotone plan depends on (sample columns, systematics)
   size_t nevents = 0;
   int nll_grid = 1;
   bool have_data = false;
@@ -776,8 +804,8 @@ static int chain_build_tables(sxmc_chain* c) {
                          std::max(1, c->batch[0].host[j].nslots);
     SXMC_TRY(upload_batch(c->batch[b], ns, c->stream));
     SXMC_CUDA(cudaMemcpyAsync(c->sigs_dev[b], sg.data(), sizeof(NllSignal) * ns, cudaMemcpyHostToDevice, c->stream));
-    SXMC_CUDA(cudaStreamSynchronize(c->stream));
   }
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));    // `sg` and the pinned staging tables may be reused after this
   return SXMC_OK;
 }
 
@@ -827,6 +855,16 @@ static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut
   L.grid = c->nll_grid;
   L.mult = c->mult_dev;
   L.mult_nbins = c->total_nbins;
+  L.ptable = nullptr;
+  // events looked up one by one (signals of several datasets): eval_pdf once per (signal, bin) first
+  if (c->ptable_dev && !c->mult_dev && !lut && mode == NLL_MODE_STEP && c->nevents * (size_t)c->nsignals >= 4096) {
+    if (zero_other || !c->ptable_valid) {        // zero_other == the step re-binned
+      SXMC_TRY(launch_pdf_table(L.sigs_dev, L.norms_dev, c->nsignals, c->total_nbins, c->ptable_dev, c->stream));
+      c->launches += 1;
+      c->ptable_valid = !zero_other;
+    }
+    L.ptable = c->ptable_dev;
+  }
   SXMC_TRY(launch_nll(L, c->stream));
   c->launches += 1;
   return SXMC_OK;
@@ -955,7 +993,7 @@ int sxmc_chain_destroy(sxmc_chain* c) {
   chain_drop_graph(c);
   cudaFree(c->flush_buf);
   cudaFree(c->bcast_dev); cudaFree(c->sync_dev); cudaFree(c->stamps_dev);
-  cudaFree(c->mult_dev); cudaFree(c->nevents_dev);
+  cudaFree(c->mult_dev); cudaFree(c->nevents_dev); cudaFree(c->data_dev);
   for (int p = 0; p < c->p2p_nranks; ++p)
     if (p != c->p2p_rank && c->p2p_peer[p]) cudaIpcCloseMemHandle(c->p2p_peer[p]);
   cudaFree(c->p2p_window); cudaFree(c->p2p_state);
@@ -966,7 +1004,7 @@ int sxmc_chain_destroy(sxmc_chain* c) {
   cudaFree(c->st_dev);
   if (c->st_host) cudaFreeHost(c->st_host);
   for (int b = 0; b < 2; ++b) { cudaFree(c->hist_own[b]); cudaFree(c->sigs_dev[b]); c->batch[b].release(); }
-  cudaFree(c->partials); cudaFree(c->ticket); cudaFree(c->lut_dev); cudaFree(c->rows_dev);
+  cudaFree(c->partials); cudaFree(c->ticket); cudaFree(c->lut_dev); cudaFree(c->rows_dev); cudaFree(c->ptable_dev);
   cudaFree(c->nll_trace_dev); cudaFree(c->prop_trace_dev); cudaFree(c->tape_n_dev); cudaFree(c->tape_u_dev);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
@@ -1011,28 +1049,69 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
   if (data_nfloats % (size_t)(c->nobs + 1) != 0)
     SXMC_INVAL("Number of entries in evaluation points array not divisible by number of observables.");
   c->nevents = data_nfloats / (size_t)(c->nobs + 1);
-  chain_drop_graph(c);   // the captured launches bake nevents and the table pointers
-  // p->SetEvalPoints(data) for every pdf (src/mcmc.cpp:235)
-  for (int j = 0; j < c->nsignals; ++j) SXMC_TRY(sxmc_hist_set_eval_points(c->pdfs[j], data, data_nfloats));
+  // One upload of the data events for all PDFs, then p->SetEvalPoints(data) for every pdf
+  // (src/mcmc.cpp:235) as launches on the chain's stream.  Buffers only ever grow, so that a fit
+  // re-run on new data of the same size keeps its tables and its captured step graph.
+  if (data_nfloats > c->data_cap || !c->data_dev) {
+    cudaFree(c->data_dev);
+    c->data_dev = nullptr;
+    c->data_cap = 0;
+    SXMC_CUDA(cudaMalloc(&c->data_dev, sizeof(float) * std::max<size_t>(1, data_nfloats)));
+    c->data_cap = std::max<size_t>(1, data_nfloats);
+  }
+  if (data_nfloats)
+    SXMC_CUDA(cudaMemcpyAsync(c->data_dev, data, sizeof(float) * data_nfloats, cudaMemcpyHostToDevice, c->stream));
+  for (int j = 0; j < c->nsignals; ++j) SXMC_TRY(hist_set_eval_points_dev(c->pdfs[j], c->data_dev, c->nevents, c->stream));
   c->nll_grid = nll_grid_for((long long)c->nevents);
-  cudaFree(c->lut_dev);
-  c->lut_dev = nullptr;
-  SXMC_CUDA(cudaMalloc(&c->lut_dev, sizeof(float) * std::max<size_t>(1, c->nevents * c->nsignals)));
-  SXMC_TRY(chain_build_tables(c));
-  // grouped lookup of the monotone path: events per bin, when all signals read one dataset
+  const size_t lut_need = std::max<size_t>(1, c->nevents * c->nsignals);
+  if (lut_need > c->lut_cap || !c->lut_dev) {
+    cudaFree(c->lut_dev);
+    c->lut_dev = nullptr;
+    c->lut_cap = 0;
+    SXMC_CUDA(cudaMalloc(&c->lut_dev, sizeof(float) * lut_need));
+    c->lut_cap = lut_need;
+  }
+  // grouped lookup: events per bin, when all signals read one dataset
   bool shared = true;
   for (int j = 1; j < c->nsignals; ++j) shared = shared && c->pdfs[j]->dataset == c->pdfs[0]->dataset;
-  cudaFree(c->mult_dev);
-  c->mult_dev = nullptr;
   c->mult_fits_table = (size_t)c->nsignals * c->total_nbins <= (size_t)BATCH_PDF_TABLE;
   if (shared && !g_no_group) {
-    SXMC_CUDA(cudaMalloc(&c->mult_dev, sizeof(unsigned) * (size_t)c->total_nbins));
+    if (!c->mult_dev) SXMC_CUDA(cudaMalloc(&c->mult_dev, sizeof(unsigned) * (size_t)c->total_nbins));
     SXMC_TRY(launch_event_mult(c->pdfs[0]->read_bins_dev, (long long)c->nevents, c->total_nbins, c->mult_dev, c->stream));
+  } else {
+    if (c->mult_dev) { cudaFree(c->mult_dev); c->mult_dev = nullptr; }
+    if (!c->ptable_dev)     // per-event lookup: the step's PDF values per (signal, bin)
+      SXMC_CUDA(cudaMalloc(&c->ptable_dev, sizeof(float) * (size_t)c->nsignals * (size_t)c->total_nbins));
   }
   if (!c->nevents_dev) SXMC_CUDA(cudaMalloc(&c->nevents_dev, sizeof(long long)));
   const long long ne = (long long)c->nevents;
   SXMC_CUDA(cudaMemcpyAsync(c->nevents_dev, &ne, sizeof ne, cudaMemcpyHostToDevice, c->stream));
-  SXMC_CUDA(cudaStreamSynchronize(c->stream));
+  // everything the uploaded tables and the captured graph depend on
+  std::vector<const void*> sig, lsig;
+  sig.push_back((const void*)(uintptr_t)c->nevents);
+  sig.push_back(c->lut_dev); sig.push_back(c->mult_dev);
+  sig.push_back(c->hist_buf[0]); sig.push_back(c->hist_buf[1]); sig.push_back(c->part_buf[0]); sig.push_back(c->part_buf[1]);
+  lsig.push_back((const void*)(uintptr_t)(g_smem_hist_max_bins * 8 + g_force_generic * 2 + g_force_dynamic));
+  for (int j = 0; j < c->nsignals; ++j) {
+    sxmc_hist* h = c->pdfs[j];
+    SXMC_TRY(ensure_prepared(h));
+    sig.push_back(h->read_bins_dev);
+    lsig.push_back(h->cols_dev);
+    lsig.push_back((const void*)(uintptr_t)(h->systs.size() * 16 + (size_t)h->primary + 1));
+  }
+  sig.insert(sig.end(), lsig.begin(), lsig.end());
+  if (sig != c->table_sig) {
+    chain_drop_graph(c);   // the captured launches bake nevents and the table pointers
+    SXMC_TRY(chain_build_tables(c));
+    c->table_sig = sig;
+  }
+  if (lsig != c->layout_sig) {
+    c->layout_sig = lsig;
+    c->mono_checked = false;
+    delete c->mono_plan;
+    c->mono_plan = nullptr;
+  }
+  SXMC_CUDA(cudaStreamSynchronize(c->stream));   // `data` may be freed by the caller after this returns
   c->have_data = true;
   return SXMC_OK;
 }
@@ -1115,6 +1194,18 @@ static int chain_p2p_check(sxmc_chain* c) {
   return SXMC_OK;
 }
 
+// Fixed systematics: every step reads the initial evaluation (buffer 0), so the PDF-value table of
+// the per-event lookup is computed once, outside any graph capture.
+static int chain_fixed_table(sxmc_chain* c, bool rebin) {
+  if (rebin || c->mult_dev || !c->ptable_dev || c->ptable_valid) return SXMC_OK;
+  if (c->nevents * (size_t)c->nsignals < 4096) return SXMC_OK;
+  SXMC_TRY(launch_pdf_table(c->sigs_dev[0], c->hist_buf[0] + (size_t)c->nsignals * c->total_nbins, c->nsignals,
+                            c->total_nbins, c->ptable_dev, c->stream));
+  c->launches += 1;
+  c->ptable_valid = true;
+  return SXMC_OK;
+}
+
 // one MCMC step enqueued on the chain's stream: [bin -> (allreduce)] -> lookup+nll+decide+propose
 static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b) {
   if (rebin) SXMC_TRY(chain_bin(c, b));
@@ -1154,12 +1245,14 @@ int sxmc_chain_begin(sxmc_chain* c, const float* data, size_t data_nfloats, unsi
 
   // initial evaluation at the means (src/mcmc.cpp:233-252): always bins, whatever is fixed
   for (int b = 0; b < 2; ++b) {
+    if (c->batch[b].queue_dev) SXMC_CUDA(cudaMemsetAsync(c->batch[b].queue_dev, 0, sizeof(unsigned) * 2, c->stream));
     SXMC_CUDA(cudaMemsetAsync(c->hist_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
     if (c->part_buf[b] != c->hist_buf[b])
       SXMC_CUDA(cudaMemsetAsync(c->part_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
   }
   SXMC_TRY(chain_bin(c, 0));
   SXMC_TRY(chain_nll(c, 0, NLL_MODE_INIT, false, nullptr));
+  c->ptable_valid = false;
   c->last_buf = 0;
   SXMC_CUDA(cudaStreamSynchronize(c->stream));
   return chain_p2p_check(c);
@@ -1174,6 +1267,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
   }
   const bool rebin = c->nsystematics > 0 && !c->systematics_fixed;   // src/mcmc.cpp:264
   const bool has_comm = (c->comm && c->comm->nranks > 1) || c->p2p_nranks > 1;
+  SXMC_TRY(chain_fixed_table(c, rebin));
   const unsigned GRAPH_STEPS = 16;   // even: the histogram double-buffer parity is preserved
   unsigned left = nsteps;
   // Small fits: the whole segment in one cooperative launch (chain_kernels.cu).  Chosen when a
@@ -1329,6 +1423,7 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
     return SXMC_ESTATE;
   }
   const bool rebin = c->nsystematics > 0 && !c->systematics_fixed;
+  SXMC_TRY(chain_fixed_table(c, rebin));
   if (flush_bytes > c->flush_bytes) {
     cudaFree(c->flush_buf);
     c->flush_buf = nullptr;
@@ -2158,6 +2253,7 @@ int sxmc_chain_p2p_connect(sxmc_chain* c, const void* handles, int nranks, int r
   c->part_buf[1] = c->p2p_window + c->p2p_pitch;
   c->hist_buf[0] = c->p2p_window + 2 * c->p2p_pitch;      // peers store their slices of the sum here
   c->hist_buf[1] = c->p2p_window + 3 * c->p2p_pitch;
+  c->table_sig.clear();
   if (c->have_data) SXMC_TRY(chain_build_tables(c));
   return SXMC_OK;
 }

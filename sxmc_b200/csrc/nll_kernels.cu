@@ -19,7 +19,8 @@ __global__ void __launch_bounds__(THREADS)
 lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict__ norms, int ns,
                   int np, int nsources, long long ne, ChainState* st, double* partials,
                   unsigned* ticket, int mode, float* lut, unsigned* zero_ptr,
-                  unsigned long long zero_words, const unsigned* __restrict__ mult, int mult_nbins) {
+                  unsigned long long zero_words, const unsigned* __restrict__ mult, int mult_nbins,
+                  const float* __restrict__ ptable) {
   __shared__ double s_c[NLL_MAX_SIGNALS];
   __shared__ double s_bn[NLL_MAX_SIGNALS];
   __shared__ const unsigned* s_bins[NLL_MAX_SIGNALS];
@@ -106,6 +107,62 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
       }
       if (s > 0) sum += (double)m * log(s);
     }
+  } else if (ptable && !lut) {
+    // Per-event lookup against the step's PDF-value table (pdf_table_kernel: eval_pdf's division
+    // done once per (signal, bin), NaN already mapped to 0): 4 B of read_bins per (event, signal)
+    // from HBM, one float gather from the L2-resident table, two FP64 operations.  Four events per
+    // thread (one 128-bit load per signal), four signals' loads in flight; the additions keep the
+    // reference's order within an event.
+    const int nb = mult_nbins;
+    const long long ne4 = ne & ~3ll;
+    for (long long i = gtid * 4; i < ne4; i += gstride * 4) {
+      double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+      int j = 0;
+      for (; j + 4 <= ns; j += 4) {
+        int4 rb[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) rb[q] = __ldcs(reinterpret_cast<const int4*>(s_rb[j + q] + i));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float* t = ptable + (size_t)(j + q) * nb;
+          const double c = s_c[j + q];
+          const float v0 = (unsigned)rb[q].x < (unsigned)nb ? __ldg(t + rb[q].x) : 0.0f;
+          const float v1 = (unsigned)rb[q].y < (unsigned)nb ? __ldg(t + rb[q].y) : 0.0f;
+          const float v2 = (unsigned)rb[q].z < (unsigned)nb ? __ldg(t + rb[q].z) : 0.0f;
+          const float v3 = (unsigned)rb[q].w < (unsigned)nb ? __ldg(t + rb[q].w) : 0.0f;
+          s0 = __dadd_rn(s0, __dmul_rn(c, (double)v0));
+          s1 = __dadd_rn(s1, __dmul_rn(c, (double)v1));
+          s2 = __dadd_rn(s2, __dmul_rn(c, (double)v2));
+          s3 = __dadd_rn(s3, __dmul_rn(c, (double)v3));
+        }
+      }
+      for (; j < ns; ++j) {
+        const int4 rb = __ldcs(reinterpret_cast<const int4*>(s_rb[j] + i));
+        const float* t = ptable + (size_t)j * nb;
+        const double c = s_c[j];
+        const float v0 = (unsigned)rb.x < (unsigned)nb ? __ldg(t + rb.x) : 0.0f;
+        const float v1 = (unsigned)rb.y < (unsigned)nb ? __ldg(t + rb.y) : 0.0f;
+        const float v2 = (unsigned)rb.z < (unsigned)nb ? __ldg(t + rb.z) : 0.0f;
+        const float v3 = (unsigned)rb.w < (unsigned)nb ? __ldg(t + rb.w) : 0.0f;
+        s0 = __dadd_rn(s0, __dmul_rn(c, (double)v0));
+        s1 = __dadd_rn(s1, __dmul_rn(c, (double)v1));
+        s2 = __dadd_rn(s2, __dmul_rn(c, (double)v2));
+        s3 = __dadd_rn(s3, __dmul_rn(c, (double)v3));
+      }
+      if (s0 > 0) sum += log(s0);
+      if (s1 > 0) sum += log(s1);
+      if (s2 > 0) sum += log(s2);
+      if (s3 > 0) sum += log(s3);
+    }
+    for (long long i = ne4 + gtid; i < ne; i += gstride) {
+      double s = 0;
+      for (int j = 0; j < ns; ++j) {
+        const int rb = s_rb[j][i];
+        const float v = (unsigned)rb < (unsigned)nb ? __ldg(ptable + (size_t)j * nb + rb) : 0.0f;
+        s = __dadd_rn(s, __dmul_rn(s_c[j], (double)v));
+      }
+      if (s > 0) sum += log(s);
+    }
   } else
   for (long long i = gtid; i < ne; i += gstride) {
     double s = 0;
@@ -163,6 +220,31 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
                 pre_rng ? &s_u : nullptr);
 }
 
+// eval_pdf's value (src/pdfz.cpp:429-432) for every (signal, bin) of this step, with the NaN of
+// an empty PDF already replaced by 0 as nll_event_chunks does (src/nll_kernels.cpp:107): the
+// per-event lookup then costs a gather instead of a double-precision division per (event, signal).
+__global__ void pdf_table_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict__ norms, int nb,
+                                 float* __restrict__ table) {
+  const int j = blockIdx.y;
+  const double bn = __dmul_rn((double)norms[j], sigs[j].bin_volume);        // pdfz.cpp:417
+  const unsigned* bins = sigs[j].bins;
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += gridDim.x * blockDim.x) {
+    float v = (float)((double)bins[b] / bn);
+    if (isnan(v)) v = 0.0f;
+    table[(size_t)j * nb + b] = v;
+  }
+}
+
+int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, float* table_dev,
+                     cudaStream_t stream) {
+  if (nsignals <= 0 || nbins <= 0) return SXMC_OK;
+  int gx = (nbins + 255) / 256;
+  if (gx > 64) gx = 64;
+  pdf_table_kernel<<<dim3((unsigned)gx, (unsigned)nsignals), 256, 0, stream>>>(sigs_dev, norms_dev, nbins, table_dev);
+  SXMC_CUDA(cudaGetLastError());
+  return SXMC_OK;
+}
+
 int nll_grid_for(long long nevents) {
   long long g = (nevents + NLL_THREADS - 1) / NLL_THREADS;
   if (g < 1) g = 1;
@@ -181,11 +263,11 @@ int launch_nll(const NllLaunch& L, cudaStream_t stream) {
   if (L.mult && !L.lut && L.mult_nbins <= 4096 && L.zero_words <= 65536) {
     lookup_nll_kernel<1024><<<1, 1024, 0, stream>>>(L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources,
                                                     L.nevents, L.state, L.partials, L.ticket, L.mode, L.lut,
-                                                    L.zero_ptr, L.zero_words, L.mult, L.mult_nbins);
+                                                    L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable);
   } else {
     lookup_nll_kernel<NLL_THREADS><<<L.grid, NLL_THREADS, 0, stream>>>(
         L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources, L.nevents, L.state, L.partials, L.ticket,
-        L.mode, L.lut, L.zero_ptr, L.zero_words, L.mult, L.mult_nbins);
+        L.mode, L.lut, L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable);
   }
   SXMC_CUDA(cudaGetLastError());
   return SXMC_OK;

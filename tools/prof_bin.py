@@ -30,6 +30,11 @@ def main():
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--stress", action="store_true")
     ap.add_argument("--json", default=None)
+    ap.add_argument("--static-kernel", action="store_true", help="force the static-partition kernel (no dynamic tail)")
+    ap.add_argument("--permille", type=int, default=-1, help="static share of the streaming kernel")
+    ap.add_argument("--tile", type=int, default=0, help="chunks per dynamic tile (0: automatic)")
+    ap.add_argument("--scatter", action="store_true", help="dynamic tiles in a scattered order")
+    ap.add_argument("--global-hist", action="store_true", help="histograms in global memory (L2 atomics only)")
     a = ap.parse_args()
     from sxmc_b200 import _lib, mcmc, sharding, workloads
     L = _lib.lib()
@@ -38,6 +43,10 @@ def main():
     if a.shard > 1:
         fit = sharding.shard_fit_samples(fit, 0, a.shard)
     nbytes = 4 * fit.needed_columns() * fit.total_samples()
+    from sxmc_b200 import pdfz
+    _lib.check(L.sxmc_set_stream_tuning((0 if a.static_kernel else 1) | (2 if a.scatter else 0), a.permille, a.tile))
+    if a.global_hist:
+        pdfz.set_bin_tuning(smem_hist_max_bins=0)
     hists, chain = mcmc.build_fit(fit)
     chain.set_seed(1, 0)
     chain.begin(fit.data, a.steps + 4, 0.1)
@@ -50,11 +59,14 @@ def main():
         s, b, n = chain.advance_timed(1, flush)
         _lib.check(L.sxmc_bin_debug_stamps(1, out.ctypes.data_as(C.POINTER(C.c_uint64))))
         st = out.astype(np.int64)
-        live = st[:, 31] > 0
+        # streaming kernel: exit stamp in slot 9 (slots 16..31 are its warps' ends of the static phase)
+        stream_k = bool((st[:, 3] == 0).all() and (st[:, 9] > 0).any())
+        endc = 9 if stream_k else 31
+        live = st[:, endc] > 0
         g = st[live]
         t0 = g[:, 0].min()
         us = lambda col: (g[:, col] - t0) / 1e3
-        end = us(31)
+        end = us(endc)
         warps = (g[:, 16:32 - 0][:, :16] - t0) / 1e3      # per-warp loop exit of the last segment
         warps = np.where(g[:, 16:32] > 0, warps, np.nan)[:, :16]
         rows.append({
@@ -62,6 +74,7 @@ def main():
             "entry": us(0), "init": us(1), "first_data": us(2), "seg0_params": us(4),
             "nseg": g[:, 3], "end": end, "warps_last": warps,
             "seg0_loop": us(5), "seg0_done": us(6), "seg1_params": us(7), "seg1_loop": us(8), "seg1_done": us(9),
+            "stream": stream_k,
         })
         out[:] = 0
     _lib.check(L.sxmc_bin_debug_stamps(0, None))
@@ -78,6 +91,14 @@ def main():
     print("  CTA entry                 %s" % q(r["entry"]))
     print("  pipeline initialised      %s" % q(r["init"]))
     print("  first data in smem        %s" % q(r["first_data"]))
+    if r["stream"]:
+        print("  (streaming kernel: static range per CTA + dynamic tiles per warp)")
+        print("  warps leave the static phase: first %s" % q(np.nanmin(r["warps_last"], axis=1)))
+        print("                                last  %s" % q(np.nanmax(r["warps_last"], axis=1)))
+        print("  CTA exit                  %s" % q(r["end"]))
+        print("  idle tail (kernel end - CTA exit), mean %.1f us = %.1f %% of the kernel" %
+              (float((r["end"].max() - r["end"]).mean()), 100 * float((r["end"].max() - r["end"]).mean()) / r["end"].max()))
+        return
     print("  seg 0 parameters resolved %s" % q(r["seg0_params"]))
     print("  segments per CTA          %s" % q(r["nseg"]))
     two = r["nseg"] >= 2
