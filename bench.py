@@ -102,8 +102,6 @@ def parse_args(argv=None):
     ap.add_argument("--flush", default="auto", choices=["auto", "always", "never"],
                     help="L2 flush (256 MiB memset) before every timed step; auto = only when a step "
                          "streams less than 4x the L2")
-    ap.add_argument("--static-bin", action="store_true",
-                    help="measurement knob: the static-partition binning kernel instead of the dynamic-tail one")
     ap.add_argument("--experiments", type=int, default=296,
                     help="workload E: fake experiments per GPU (whole batches of 148)")
     ap.add_argument("--esteps", type=int, default=20000, help="workload E: MCMC steps per experiment")
@@ -604,9 +602,6 @@ def extra_workload(name, args, local, peak, peak_src, steps, warmup, repeats):
 def run_own_arm(args, rank, world, local):
     import torch
     init_device(world, local)
-    if args.static_bin:
-        from sxmc_b200 import pdfz
-        pdfz.set_stream_tuning(False)
     peak, peak_src = measured_peak()
     sampler = ClockSampler(local)
     K = args.steps

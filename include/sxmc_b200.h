@@ -120,11 +120,6 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * every signal reads the same dataset (the multi-dataset form) -- used by the parity tests and
  * measurements to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
-/* The binning kernel for launches that stream far more than the chip holds cuts a static share of
- * every signal's samples over the SMs and hands the rest out in tiles through a global counter
- * (dynamic tail).  enable 0 = always the static kernel; static_permille = static share of the fair
- * per-SM load (default 700, < 0 keeps it); tile_chunks = 0 automatic.  Measurement knob. */
-int sxmc_set_stream_tuning(int enable, int static_permille, int tile_chunks);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
 int sxmc_enable_kernel_timing(int on);
@@ -132,7 +127,7 @@ int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);
 /* Profiling hook of the fast binning kernel (no reference counterpart): while enabled every
  * launch writes [grid <= 256][32] %globaltimer stamps (ns) per CTA -- 0 entry, 1 pipeline
  * initialised, 2 first data arrived, 3 = number of segments, 4+3s+{0,1,2} parameters resolved /
- * warp 0 out of the chunk loop / histogram merged for segment s < 4, 16+w warp w out of the
+ * warp 0 out of the chunk loop / histogram merged for segment s < 4, 11 = %smid + 1, 16+w warp w out of the
  * chunk loop of the last segment, 31 exit.  out256x32 (host, may be NULL) receives the stamps
  * of the last launch.  tools/prof_bin.py prints the prologue / steady state / epilogue split. */
 int sxmc_bin_debug_stamps(int enable, unsigned long long* out256x32);

@@ -73,7 +73,6 @@ SYMBOLS = {
     "sxmc_hist_set_layout": (C.c_int, [c_vp, C.c_int]),
     "sxmc_hist_prepare": (C.c_int, [c_vp]),
     "sxmc_set_bin_tuning": (C.c_int, [C.c_int, C.c_int, C.c_int]),
-    "sxmc_set_stream_tuning": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "sxmc_enable_kernel_timing": (C.c_int, [C.c_int]),
     "sxmc_last_kernel_ms": (C.c_int, [c_fp, c_fp]),
     "sxmc_bin_debug_stamps": (C.c_int, [C.c_int, C.POINTER(C.c_uint64)]),

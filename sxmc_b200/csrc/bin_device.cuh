@@ -497,6 +497,9 @@ bin_fast_kernel(const __grid_constant__ FastParams P) {
     unsigned long long t_;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
     P.xdbg[32ull * blockIdx.x] = t_;
+    unsigned smid_;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));
+    P.xdbg[32ull * blockIdx.x + 11] = (unsigned long long)smid_ + 1ull;
   }
   FastCtx cx;
   fast_ctx_init<NS>(cx, P, smem_raw, s_bar);

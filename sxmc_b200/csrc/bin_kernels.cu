@@ -9,7 +9,6 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "bin_device.cuh"
-#include "bin_stream.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -96,18 +95,15 @@ bin_generic_kernel(const BinJob* __restrict__ jobs, const unsigned long long* __
 // launch dispatch
 // =========================================================================================
 typedef void (*FastKernel)(const FastParams);
-typedef void (*StreamKernel)(const StreamParams);
 
 struct FastEntry {
   int nobs, ns, nops;
   unsigned codes;
   FastKernel k[2];   // [global-memory histogram, shared-memory histogram]
-  StreamKernel sk[2];
 };
 #define FE(NOBS, NS, NOPS, CODES)                                                   \
   { NOBS, NS, NOPS, (CODES),                                                        \
-    { bin_fast_kernel<NOBS, NS, false, NOPS, (CODES)>, bin_fast_kernel<NOBS, NS, true, NOPS, (CODES)> }, \
-    { bin_stream_kernel<NOBS, NS, false, NOPS, (CODES)>, bin_stream_kernel<NOBS, NS, true, NOPS, (CODES)> } }
+    { bin_fast_kernel<NOBS, NS, false, NOPS, (CODES)>, bin_fast_kernel<NOBS, NS, true, NOPS, (CODES)> } }
 static const FastEntry g_fast_table[] = { SXMC_FAST_TABLE(FE) };
 #undef FE
 
@@ -222,89 +218,12 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
 static unsigned long long* g_bin_xdbg = nullptr;   // profiling hook, NULL in production
 void set_bin_xdbg(unsigned long long* dev) { g_bin_xdbg = dev; }
 
-static int g_stream_enable = 1, g_stream_static_permille = 700, g_stream_tile = 0, g_stream_scatter = 0;
-void set_bin_stream_tuning(int enable, int static_permille, int tile_chunks) {
-  g_stream_scatter = (enable >> 1) & 1;
-  enable &= 1;
-  g_stream_enable = enable;
-  if (static_permille >= 0) g_stream_static_permille = std::min(static_permille, 1000);
-  g_stream_tile = tile_chunks;
-}
-constexpr unsigned long long STREAM_MIN_CHUNKS_PER_WARP = 64;
-
-// Plan of the streaming kernel: CTAs per job in proportion to the jobs' chunk counts, a static
-// share of `permille` of the fair per-CTA load, the rest in tiles.
-static void build_stream_params(const BinLaunch& L, int grid, StreamParams& P) {
-  memset(&P, 0, sizeof P);
-  FastParams F;
-  unsigned long long total = 0;
-  build_fast_params(L, 0, L.njobs, 0, F, &total);           // jobs, geometry, chunk prefix
-  memcpy(P.job, F.job, sizeof P.job);
-  P.geo = F.geo;
-  P.njobs = L.njobs; P.R = F.R; P.S = F.S; P.stage_off = F.stage_off;
-  const int ng = L.njobs;
-  std::vector<unsigned long long> n(ng);
-  for (int j = 0; j < ng; ++j) { n[j] = F.prefix[j + 1] - F.prefix[j]; P.nchunks[j] = (unsigned)n[j]; }
-  // CTAs per job: floor of the proportional share, the rest to whoever carries most per CTA
-  std::vector<int> cta(ng, 0);
-  int used = 0;
-  for (int j = 0; j < ng; ++j) { cta[j] = (int)(n[j] * (unsigned long long)grid / total); used += cta[j]; }
-  while (used < grid) {
-    int best = 0;
-    double score = -1;
-    for (int j = 0; j < ng; ++j) {
-      const double load = (double)n[j] / (cta[j] + 1);
-      if (load > score) { best = j; score = load; }
-    }
-    cta[best] += 1;
-    used += 1;
-  }
-  P.cta_first[0] = 0;
-  for (int j = 0; j < ng; ++j) P.cta_first[j + 1] = (unsigned short)(P.cta_first[j] + cta[j]);
-  const unsigned long long quota = total * (unsigned long long)g_stream_static_permille / 1000ull / (unsigned long long)grid;
-  unsigned long long dyn = 0;
-  for (int j = 0; j < ng; ++j) {
-    P.nstatic[j] = (unsigned)std::min<unsigned long long>(n[j], quota * (unsigned long long)cta[j]);
-    dyn += n[j] - P.nstatic[j];
-  }
-  // tiles: about 12 per warp, 4..32 chunks each (a tile is the grain of the end of the launch)
-  int T = g_stream_tile > 0 ? g_stream_tile : (int)(dyn / ((unsigned long long)grid * FAST_WARPS * 12ull));
-  T = std::max(4, std::min(T, 32));
-  P.T = T;
-  P.tprefix[0] = 0;
-  for (int j = 0; j < ng; ++j)
-    P.tprefix[j + 1] = P.tprefix[j] + (unsigned)((n[j] - P.nstatic[j] + (unsigned)T - 1) / (unsigned)T);
-  P.tmul = 1;
-  const unsigned nt = P.tprefix[ng];
-  if (g_stream_scatter && nt > 2) {
-    auto gcd = [](unsigned a, unsigned b) { while (b) { const unsigned t = a % b; a = b; b = t; } return a; };
-    unsigned m = (unsigned)(0.6180339887 * nt) | 1u;
-    while (gcd(m, nt) != 1) m += 2;
-    P.tmul = m % nt;
-  }
-}
-
 int launch_bin(const BinLaunch& L, cudaStream_t stream) {
   if (L.total_units == 0) return SXMC_OK;
   if (L.fast) {
     FastKernel fk = pick_fast(L.nobs, L.nslots, L.prog_nops, L.prog_codes, L.smem_hist);
     if (!fk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
     SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
-    // launches that stream far more than the chip holds: dynamic tail (bin_stream.cuh)
-    const FastEntry* fe = pick_entry(L.nobs, L.nslots, L.prog_nops, L.prog_codes);
-    const int sms = num_sms();
-    if (g_stream_enable && fe && L.queue_dev && L.njobs <= FAST_MAX_JOBS && L.nstages >= 2 &&
-        L.total_units >= STREAM_MIN_CHUNKS_PER_WARP * FAST_WARPS * (unsigned long long)sms) {
-      StreamKernel sk = fe->sk[L.smem_hist ? 1 : 0];
-      SXMC_CUDA(cudaFuncSetAttribute((const void*)sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
-      StreamParams SP;
-      build_stream_params(L, sms, SP);
-      SP.queue = L.queue_dev;
-      SP.xdbg = g_bin_xdbg;
-      sk<<<(unsigned)sms, FAST_THREADS, L.smem_bytes, stream>>>(SP);
-      SXMC_CUDA(cudaGetLastError());
-      return SXMC_OK;
-    }
     // jobs travel in the kernel parameters (constant bank), FAST_MAX_JOBS per launch
     for (int g0 = 0; g0 < L.njobs; g0 += FAST_MAX_JOBS) {
       const int ng = L.njobs - g0 < FAST_MAX_JOBS ? L.njobs - g0 : FAST_MAX_JOBS;

@@ -65,7 +65,6 @@ struct Batch {
   unsigned long long* prefix_dev = nullptr;
   EvalPdfJob* ep_host = nullptr;   // pinned
   EvalPdfJob* ep_dev = nullptr;
-  unsigned* queue_dev = nullptr;   // tile queue of the streaming binning kernel (self re-arming)
   int cap = 0;
   BinLaunch launch;
   long long max_points = 0;
@@ -80,8 +79,6 @@ struct Batch {
     SXMC_CUDA(cudaMalloc(&prefix_dev, sizeof(unsigned long long) * (n + 1)));
     SXMC_CUDA(cudaMallocHost(&ep_host, sizeof(EvalPdfJob) * n));
     SXMC_CUDA(cudaMalloc(&ep_dev, sizeof(EvalPdfJob) * n));
-    SXMC_CUDA(cudaMalloc(&queue_dev, sizeof(unsigned) * 2));
-    SXMC_CUDA(cudaMemset(queue_dev, 0, sizeof(unsigned) * 2));
     cap = n;
     return SXMC_OK;
   }
@@ -92,8 +89,6 @@ struct Batch {
     if (prefix_dev) cudaFree(prefix_dev);
     if (ep_host) cudaFreeHost(ep_host);
     if (ep_dev) cudaFree(ep_dev);
-    if (queue_dev) cudaFree(queue_dev);
-    queue_dev = nullptr;
     host = nullptr; dev = nullptr; prefix_host = nullptr; prefix_dev = nullptr;
     ep_host = nullptr; ep_dev = nullptr; cap = 0;
   }
@@ -248,7 +243,6 @@ static void plan_launch(Batch& b, int n) {
   memset(&L, 0, sizeof L);
   L.jobs_host = b.host;
   L.jobs_dev = b.dev;
-  L.queue_dev = b.queue_dev;
   L.prefix_dev = b.prefix_dev;
   L.njobs = n;
   bool uniform = true;
@@ -393,10 +387,6 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_no_mono = (force_generic >> 2) & 1;
   g_p2p_form = (force_generic >> 3) & 3;
   g_no_group = (force_generic >> 5) & 1;
-  return SXMC_OK;
-}
-int sxmc_set_stream_tuning(int enable, int static_permille, int tile_chunks) {
-  set_bin_stream_tuning(enable, static_permille, tile_chunks);
   return SXMC_OK;
 }
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
@@ -725,7 +715,7 @@ struct sxmc_chain {
   unsigned* ticket = nullptr;
   float* lut_dev = nullptr;
   size_t lut_cap = 0;                   // floats (grow-only)
-  float* ptable_dev = nullptr;          // [nsignals][total_nbins] PDF values of the step (per-event lookup)
+  double* ptable_dev = nullptr;         // [nsignals][total_nbins] PDF values of the step (per-event lookup)
   bool ptable_valid = false;            // holds the values of the histograms the fixed-systematics steps read
   float* data_dev = nullptr;            // the data events, uploaded once per sxmc_chain_set_data
   size_t data_cap = 0;                  // floats (grow-only)
@@ -1081,7 +1071,7 @@ int sxmc_chain_set_data(sxmc_chain* c, const float* data, size_t data_nfloats) {
   } else {
     if (c->mult_dev) { cudaFree(c->mult_dev); c->mult_dev = nullptr; }
     if (!c->ptable_dev)     // per-event lookup: the step's PDF values per (signal, bin)
-      SXMC_CUDA(cudaMalloc(&c->ptable_dev, sizeof(float) * (size_t)c->nsignals * (size_t)c->total_nbins));
+      SXMC_CUDA(cudaMalloc(&c->ptable_dev, sizeof(double) * (size_t)c->nsignals * (size_t)c->total_nbins));
   }
   if (!c->nevents_dev) SXMC_CUDA(cudaMalloc(&c->nevents_dev, sizeof(long long)));
   const long long ne = (long long)c->nevents;
@@ -1245,7 +1235,6 @@ int sxmc_chain_begin(sxmc_chain* c, const float* data, size_t data_nfloats, unsi
 
   // initial evaluation at the means (src/mcmc.cpp:233-252): always bins, whatever is fixed
   for (int b = 0; b < 2; ++b) {
-    if (c->batch[b].queue_dev) SXMC_CUDA(cudaMemsetAsync(c->batch[b].queue_dev, 0, sizeof(unsigned) * 2, c->stream));
     SXMC_CUDA(cudaMemsetAsync(c->hist_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));
     if (c->part_buf[b] != c->hist_buf[b])
       SXMC_CUDA(cudaMemsetAsync(c->part_buf[b], 0, sizeof(unsigned) * c->hist_words, c->stream));

@@ -103,24 +103,8 @@ struct FastParams {
   // profiling hook (sxmc_bin_debug_stamps): [grid][32] %globaltimer stamps, NULL in production.
   // Per CTA: 0 entry, 1 pipeline initialised, 2 first data arrived (warp 0), 3 segments done,
   // 4+3s+{0,1,2} of segment s < 4: parameters resolved / warp 0 out of its chunk loop / merged,
-  // 16+w: warp w out of the chunk loop of the CTA's LAST segment, 31 exit.
+  // 11: %smid + 1, 16+w: warp w out of the chunk loop of the CTA's LAST segment, 31 exit.
   unsigned long long* xdbg;
-};
-
-// Arguments of bin_stream_kernel (bin_stream.cuh), by value: every CTA owns a static chunk range
-// of ONE job; the rest of each job is handed out in tiles of T chunks through a global counter.
-struct StreamParams {
-  FastJob job[FAST_MAX_JOBS];
-  FastGeo geo;
-  unsigned nchunks[FAST_MAX_JOBS];            // chunks of job j (a chunk = R rows of a warp-tile)
-  unsigned nstatic[FAST_MAX_JOBS];            // of which [0, nstatic) are cut statically over the job's CTAs
-  unsigned tprefix[FAST_MAX_JOBS + 1];        // prefix sums of the jobs' dynamic tile counts
-  unsigned short cta_first[FAST_MAX_JOBS + 1];   // CTAs [cta_first[j], cta_first[j+1]) are at home on job j
-  int njobs, R, S, T;
-  unsigned stage_off;
-  unsigned tmul;                              // queue position -> tile: (pos * tmul) % ntiles, gcd(tmul, ntiles) == 1
-  unsigned* queue;                            // [0] next tile, [1] warps finished (the last one re-arms both)
-  unsigned long long* xdbg;                   // profiling hook, as FastParams::xdbg
 };
 
 // Arguments of the persistent chain kernel (chain_kernels.cu), by value.

@@ -29,7 +29,6 @@ struct BinLaunch {
   size_t smem_bytes;
   double lower[3], upper[3], scale[3];
   int stride[3];
-  unsigned* queue_dev;           // 2 zeroed words owned by the caller: tile queue of the streaming kernel (or NULL)
 };
 
 struct EvalPdfJob {
@@ -47,7 +46,7 @@ bool bin_fast_supported(int nobs, int nslots);
 bool bin_fast_has_program(int nobs, int nslots, int nops, unsigned codes);
 bool bin_fast_plan(int nslots, int hist_bins, size_t static_reserve, int* R_out, int* S_out,
                    unsigned* stage_off_out, size_t* smem_out);
-constexpr size_t BIN_STATIC_RESERVE = 4096;   // static shared memory of bin_fast_kernel / bin_stream_kernel
+constexpr size_t BIN_STATIC_RESERVE = 4096;   // static shared memory of bin_fast_kernel
 // FastParams of jobs [g0, g0+ng) of a planned launch; *total_out = their chunk count
 // `grid` = the CTA count the kernel will be launched with (decides the job-aligned partition)
 void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams& P,
@@ -55,9 +54,7 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
 // chain_kernels.cu
 int launch_chain_persistent(const BinLaunch& L, const PersistParams& Q, cudaStream_t stream);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);
-void set_bin_xdbg(unsigned long long* dev);
-// streaming kernel knobs: enable (default 1), static share in permille (default 700), chunks per tile (0: automatic)
-void set_bin_stream_tuning(int enable, int static_permille, int tile_chunks);   // [256][32] stamps of the next fast launches, or NULL
+void set_bin_xdbg(unsigned long long* dev);   // [256][32] stamps of the next fast launches, or NULL
 int launch_zero_jobs(const BinJob* jobs_dev, int njobs, cudaStream_t stream);
 int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,
                    const PrepGeo& g, int primary, bool sort, float* cols_dev,
@@ -84,10 +81,10 @@ struct NllLaunch {
   int grid;                     // fixed for the life of a chain (deterministic summation order)
   const unsigned* mult;         // optional events per bin [mult_nbins]: grouped lookup (all signals one dataset)
   int mult_nbins;               // bins per PDF (also the row length of ptable)
-  const float* ptable;          // optional [nsignals][mult_nbins] PDF values of this step (launch_pdf_table)
+  const double* ptable;         // optional [nsignals][mult_nbins] PDF values of this step (launch_pdf_table)
 };
 int nll_grid_for(long long nevents);
-int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, float* table_dev,
+int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, double* table_dev,
                      cudaStream_t stream);
 int launch_nll(const NllLaunch& L, cudaStream_t stream);
 

@@ -20,7 +20,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
                   int np, int nsources, long long ne, ChainState* st, double* partials,
                   unsigned* ticket, int mode, float* lut, unsigned* zero_ptr,
                   unsigned long long zero_words, const unsigned* __restrict__ mult, int mult_nbins,
-                  const float* __restrict__ ptable) {
+                  const double* __restrict__ ptable) {
   __shared__ double s_c[NLL_MAX_SIGNALS];
   __shared__ double s_bn[NLL_MAX_SIGNALS];
   __shared__ const unsigned* s_bins[NLL_MAX_SIGNALS];
@@ -110,7 +110,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   } else if (ptable && !lut) {
     // Per-event lookup against the step's PDF-value table (pdf_table_kernel: eval_pdf's division
     // done once per (signal, bin), NaN already mapped to 0): 4 B of read_bins per (event, signal)
-    // from HBM, one float gather from the L2-resident table, two FP64 operations.  Four events per
+    // from HBM, one gather from the L2-resident table (values widened to double once), two FP64 operations.  Four events per
     // thread (one 128-bit load per signal), four signals' loads in flight; the additions keep the
     // reference's order within an event.
     const int nb = mult_nbins;
@@ -124,30 +124,30 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
         for (int q = 0; q < 4; ++q) rb[q] = __ldcs(reinterpret_cast<const int4*>(s_rb[j + q] + i));
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const float* t = ptable + (size_t)(j + q) * nb;
+          const double* t = ptable + (size_t)(j + q) * nb;
           const double c = s_c[j + q];
-          const float v0 = (unsigned)rb[q].x < (unsigned)nb ? __ldg(t + rb[q].x) : 0.0f;
-          const float v1 = (unsigned)rb[q].y < (unsigned)nb ? __ldg(t + rb[q].y) : 0.0f;
-          const float v2 = (unsigned)rb[q].z < (unsigned)nb ? __ldg(t + rb[q].z) : 0.0f;
-          const float v3 = (unsigned)rb[q].w < (unsigned)nb ? __ldg(t + rb[q].w) : 0.0f;
-          s0 = __dadd_rn(s0, __dmul_rn(c, (double)v0));
-          s1 = __dadd_rn(s1, __dmul_rn(c, (double)v1));
-          s2 = __dadd_rn(s2, __dmul_rn(c, (double)v2));
-          s3 = __dadd_rn(s3, __dmul_rn(c, (double)v3));
+          const double v0 = (unsigned)rb[q].x < (unsigned)nb ? __ldg(t + rb[q].x) : 0.0;
+          const double v1 = (unsigned)rb[q].y < (unsigned)nb ? __ldg(t + rb[q].y) : 0.0;
+          const double v2 = (unsigned)rb[q].z < (unsigned)nb ? __ldg(t + rb[q].z) : 0.0;
+          const double v3 = (unsigned)rb[q].w < (unsigned)nb ? __ldg(t + rb[q].w) : 0.0;
+          s0 = __dadd_rn(s0, __dmul_rn(c, v0));
+          s1 = __dadd_rn(s1, __dmul_rn(c, v1));
+          s2 = __dadd_rn(s2, __dmul_rn(c, v2));
+          s3 = __dadd_rn(s3, __dmul_rn(c, v3));
         }
       }
       for (; j < ns; ++j) {
         const int4 rb = __ldcs(reinterpret_cast<const int4*>(s_rb[j] + i));
-        const float* t = ptable + (size_t)j * nb;
+        const double* t = ptable + (size_t)j * nb;
         const double c = s_c[j];
-        const float v0 = (unsigned)rb.x < (unsigned)nb ? __ldg(t + rb.x) : 0.0f;
-        const float v1 = (unsigned)rb.y < (unsigned)nb ? __ldg(t + rb.y) : 0.0f;
-        const float v2 = (unsigned)rb.z < (unsigned)nb ? __ldg(t + rb.z) : 0.0f;
-        const float v3 = (unsigned)rb.w < (unsigned)nb ? __ldg(t + rb.w) : 0.0f;
-        s0 = __dadd_rn(s0, __dmul_rn(c, (double)v0));
-        s1 = __dadd_rn(s1, __dmul_rn(c, (double)v1));
-        s2 = __dadd_rn(s2, __dmul_rn(c, (double)v2));
-        s3 = __dadd_rn(s3, __dmul_rn(c, (double)v3));
+        const double v0 = (unsigned)rb.x < (unsigned)nb ? __ldg(t + rb.x) : 0.0;
+        const double v1 = (unsigned)rb.y < (unsigned)nb ? __ldg(t + rb.y) : 0.0;
+        const double v2 = (unsigned)rb.z < (unsigned)nb ? __ldg(t + rb.z) : 0.0;
+        const double v3 = (unsigned)rb.w < (unsigned)nb ? __ldg(t + rb.w) : 0.0;
+        s0 = __dadd_rn(s0, __dmul_rn(c, v0));
+        s1 = __dadd_rn(s1, __dmul_rn(c, v1));
+        s2 = __dadd_rn(s2, __dmul_rn(c, v2));
+        s3 = __dadd_rn(s3, __dmul_rn(c, v3));
       }
       if (s0 > 0) sum += log(s0);
       if (s1 > 0) sum += log(s1);
@@ -158,8 +158,8 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
       double s = 0;
       for (int j = 0; j < ns; ++j) {
         const int rb = s_rb[j][i];
-        const float v = (unsigned)rb < (unsigned)nb ? __ldg(ptable + (size_t)j * nb + rb) : 0.0f;
-        s = __dadd_rn(s, __dmul_rn(s_c[j], (double)v));
+        const double v = (unsigned)rb < (unsigned)nb ? __ldg(ptable + (size_t)j * nb + rb) : 0.0;
+        s = __dadd_rn(s, __dmul_rn(s_c[j], v));
       }
       if (s > 0) sum += log(s);
     }
@@ -224,18 +224,18 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
 // an empty PDF already replaced by 0 as nll_event_chunks does (src/nll_kernels.cpp:107): the
 // per-event lookup then costs a gather instead of a double-precision division per (event, signal).
 __global__ void pdf_table_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict__ norms, int nb,
-                                 float* __restrict__ table) {
+                                 double* __restrict__ table) {
   const int j = blockIdx.y;
   const double bn = __dmul_rn((double)norms[j], sigs[j].bin_volume);        // pdfz.cpp:417
   const unsigned* bins = sigs[j].bins;
   for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += gridDim.x * blockDim.x) {
     float v = (float)((double)bins[b] / bn);
     if (isnan(v)) v = 0.0f;
-    table[(size_t)j * nb + b] = v;
+    table[(size_t)j * nb + b] = (double)v;      // widened here once: no conversion per (event, signal)
   }
 }
 
-int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, float* table_dev,
+int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, double* table_dev,
                      cudaStream_t stream) {
   if (nsignals <= 0 || nbins <= 0) return SXMC_OK;
   int gx = (nbins + 255) / 256;

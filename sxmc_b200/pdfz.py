@@ -270,11 +270,6 @@ def eval_hists_host(hists, params, param_offset, want_pdf=True):
     return norms, (pdf[:, :npts] if pdf is not None else None)
 
 
-def set_stream_tuning(enable=True, static_permille=-1, tile_chunks=0):
-    """Dynamic-tail binning kernel for large launches (bin_stream.cuh): on/off, static share, tile size."""
-    _check(lib().sxmc_set_stream_tuning(int(bool(enable)), int(static_permille), int(tile_chunks)))
-
-
 def set_bin_tuning(smem_hist_max_bins=-1, blocks_per_sm=0, force_generic=False,
                    force_dynamic=False, no_monotone=False, p2p_form=0, no_grouped_lookup=False):
     sel = (1 if force_generic else 0) | (2 if force_dynamic else 0) | (4 if no_monotone else 0) | ((int(p2p_form) & 3) << 3) | (32 if no_grouped_lookup else 0)

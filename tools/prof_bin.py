@@ -30,10 +30,8 @@ def main():
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--stress", action="store_true")
     ap.add_argument("--json", default=None)
-    ap.add_argument("--static-kernel", action="store_true", help="force the static-partition kernel (no dynamic tail)")
-    ap.add_argument("--permille", type=int, default=-1, help="static share of the streaming kernel")
-    ap.add_argument("--tile", type=int, default=0, help="chunks per dynamic tile (0: automatic)")
-    ap.add_argument("--scatter", action="store_true", help="dynamic tiles in a scattered order")
+    ap.add_argument("--block", type=int, default=1,
+                    help="steps back to back before the stamps of the LAST launch are read (1: isolated launches)")
     ap.add_argument("--global-hist", action="store_true", help="histograms in global memory (L2 atomics only)")
     a = ap.parse_args()
     from sxmc_b200 import _lib, mcmc, sharding, workloads
@@ -44,24 +42,22 @@ def main():
         fit = sharding.shard_fit_samples(fit, 0, a.shard)
     nbytes = 4 * fit.needed_columns() * fit.total_samples()
     from sxmc_b200 import pdfz
-    _lib.check(L.sxmc_set_stream_tuning((0 if a.static_kernel else 1) | (2 if a.scatter else 0), a.permille, a.tile))
     if a.global_hist:
         pdfz.set_bin_tuning(smem_hist_max_bins=0)
     hists, chain = mcmc.build_fit(fit)
     chain.set_seed(1, 0)
-    chain.begin(fit.data, a.steps + 4, 0.1)
+    chain.begin(fit.data, a.steps * a.block + 4, 0.1)
     flush = 0 if a.no_flush else (256 << 20)
     chain.advance_timed(3, flush)
     _lib.check(L.sxmc_bin_debug_stamps(1, None))
     out = np.zeros((256, 32), dtype=np.uint64)
     rows = []
     for _ in range(a.steps):
-        s, b, n = chain.advance_timed(1, flush)
+        s, b, n = chain.advance_timed(a.block, flush)
+        b /= a.block
         _lib.check(L.sxmc_bin_debug_stamps(1, out.ctypes.data_as(C.POINTER(C.c_uint64))))
         st = out.astype(np.int64)
-        # streaming kernel: exit stamp in slot 9 (slots 16..31 are its warps' ends of the static phase)
-        stream_k = bool((st[:, 3] == 0).all() and (st[:, 9] > 0).any())
-        endc = 9 if stream_k else 31
+        endc = 31
         live = st[:, endc] > 0
         g = st[live]
         t0 = g[:, 0].min()
@@ -74,7 +70,7 @@ def main():
             "entry": us(0), "init": us(1), "first_data": us(2), "seg0_params": us(4),
             "nseg": g[:, 3], "end": end, "warps_last": warps,
             "seg0_loop": us(5), "seg0_done": us(6), "seg1_params": us(7), "seg1_loop": us(8), "seg1_done": us(9),
-            "stream": stream_k,
+            "smid": g[:, 11] - 1,
         })
         out[:] = 0
     _lib.check(L.sxmc_bin_debug_stamps(0, None))
@@ -91,14 +87,6 @@ def main():
     print("  CTA entry                 %s" % q(r["entry"]))
     print("  pipeline initialised      %s" % q(r["init"]))
     print("  first data in smem        %s" % q(r["first_data"]))
-    if r["stream"]:
-        print("  (streaming kernel: static range per CTA + dynamic tiles per warp)")
-        print("  warps leave the static phase: first %s" % q(np.nanmin(r["warps_last"], axis=1)))
-        print("                                last  %s" % q(np.nanmax(r["warps_last"], axis=1)))
-        print("  CTA exit                  %s" % q(r["end"]))
-        print("  idle tail (kernel end - CTA exit), mean %.1f us = %.1f %% of the kernel" %
-              (float((r["end"].max() - r["end"]).mean()), 100 * float((r["end"].max() - r["end"]).mean()) / r["end"].max()))
-        return
     print("  seg 0 parameters resolved %s" % q(r["seg0_params"]))
     print("  segments per CTA          %s" % q(r["nseg"]))
     two = r["nseg"] >= 2
@@ -117,6 +105,25 @@ def main():
     print("  CTA lifetime              %s" % q(busy))
     print("  idle tail (kernel end - CTA exit), mean %.1f us = %.1f %% of the kernel" %
           (float((r["end"].max() - r["end"]).mean()), 100 * float((r["end"].max() - r["end"]).mean()) / r["end"].max()))
+    # are the same SMs slow launch after launch?  (lifetime of single-segment CTAs, by %smid)
+    life = {}
+    for x in rows:
+        one = x["nseg"] == 1
+        for sm, t in zip(x["smid"][one], (x["end"] - x["entry"])[one]):
+            life.setdefault(int(sm), []).append(float(t))
+    sms = sorted(k for k, v in life.items() if len(v) == len(rows))
+    if len(sms) > 8 and len(rows) >= 3:
+        m = np.array([life[k] for k in sms])            # [sm, launch]
+        rel = m / m.mean(axis=0, keepdims=True)
+        avg = rel.mean(axis=1)
+        cc = np.corrcoef(rel.T)
+        print("per-SM relative lifetime (single-segment CTAs, %d SMs, %d launches): launch-to-launch correlation "
+              "%.2f; persistent spread min %.3f max %.3f std %.3f" %
+              (len(sms), len(rows), float(cc[np.triu_indices(len(rows), 1)].mean()), avg.min(), avg.max(), avg.std()))
+        order = np.argsort(avg)
+        print("  fastest SMs (smid: rel): " + " ".join("%d:%.3f" % (sms[i], avg[i]) for i in order[:10]))
+        print("  slowest SMs (smid: rel): " + " ".join("%d:%.3f" % (sms[i], avg[i]) for i in order[-10:]))
+        print("  by smid: " + " ".join("%.3f" % avg[i] for i in range(len(sms))))
     if a.json:
         with open(a.json, "w") as f:
             json.dump({"workload": fit.name, "scale": a.scale, "shard": a.shard, "bytes": nbytes,
