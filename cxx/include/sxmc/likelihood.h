@@ -1,7 +1,8 @@
 // LikelihoodSpace -- the sink of a chain (reference: src/likelihood.h:25-100).  The TNtuple
 // of the reference is a row-major float table here (names + rows); the Contour estimator
-// (src/error_estimators/contour.cpp:18-69) runs as device reductions (sxmc_rows_contour).
-// ERROR_PROJECTION needs ROOT's TH1::Fit and is not provided.
+// (src/error_estimators/contour.cpp:18-69) runs as device reductions (sxmc_rows_contour); the
+// Projection estimator (projection.cpp:14-77) is host code, as in the reference, with ROOT's
+// auto-binned TH1F and Gaussian fit restated (cxx/src/projection.cpp).
 #ifndef SXMC_B200_LIKELIHOOD_H
 #define SXMC_B200_LIKELIHOOD_H
 #include <map>
@@ -17,6 +18,14 @@ struct NtupleRows {                     // stands in for TNtuple
   std::vector<float> rows;              // [nrows][names.size()]
   long nrows() const { return names.empty() ? 0 : (long)(rows.size() / names.size()); }
 };
+
+namespace sxmc {
+namespace errors {
+// Projection::get_interval on one column: values[i * stride], i < n
+Interval projection_interval(const float* values, long n, long stride, float cl, int nbins = 100);
+void root_axis_limits(double xmin, double xmax, int nbins, double& lo, double& hi, int& nb);
+}  // namespace errors
+}  // namespace sxmc
 
 class LikelihoodSpace {
  public:

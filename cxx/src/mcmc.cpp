@@ -105,8 +105,8 @@ LikelihoodSpace::~LikelihoodSpace() { delete samples; }
 
 std::map<std::string, Interval>
 LikelihoodSpace::extract_best_fit(float& lm, float _cl, ErrorType _error_type) {   // src/likelihood.cpp:104-137
-  if (_error_type != ERROR_CONTOUR) {
-    std::cerr << "LikelihoodSpace::extract_best_fit: only ERROR_CONTOUR is available without ROOT" << std::endl;
+  if (_error_type != ERROR_CONTOUR && _error_type != ERROR_PROJECTION) {
+    std::cerr << "LikelihoodSpace::extract_best_fit: Unknown error type" << std::endl;
     throw(5);
   }
   std::map<std::string, Interval> best_fit;
@@ -114,6 +114,14 @@ LikelihoodSpace::extract_best_fit(float& lm, float _cl, ErrorType _error_type) {
   const int ncols = (int)samples->names.size();
   if (nrows <= 0 || ncols < 2) { lm = 0; return best_fit; }
   const int np = ncols - 1;
+  if (_error_type == ERROR_PROJECTION) {          // host estimator on the rows (projection.cpp:14-77)
+    for (int i = 0; i < np; ++i)
+      best_fit[samples->names[i]] = sxmc::errors::projection_interval(samples->rows.data() + i, nrows, ncols, _cl);
+    float lmin = samples->rows[np];
+    for (long r = 1; r < nrows; ++r) lmin = std::min(lmin, samples->rows[(size_t)r * ncols + np]);
+    lm = lmin;                                    // samples->GetMinimum("likelihood")
+    return best_fit;
+  }
   void* dev = NULL;
   check(sxmc_buf_alloc(sizeof(float) * samples->rows.size(), &dev));
   int rc = sxmc_buf_upload(dev, samples->rows.data(), sizeof(float) * samples->rows.size());

@@ -258,7 +258,6 @@ int main(int argc, char* argv[]) {
     std::cout << "sxmc: Configuration: " << argv[1] << std::endl;
     FitConfig fc(argv[1]);
     fc.print();
-    if (fc.error_type != ERROR_CONTOUR) throw std::runtime_error("error_type 'projection' needs ROOT's histogram fit");
 
     std::cout << "sxmc: Running ensemble..." << std::endl;
     std::vector<float> limits = ensemble(fc, output_path, rank, world);

@@ -117,7 +117,8 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * kernel (no compile-time program), bit 2 = the chain batch never takes its monotone endpoint
  * path, bits 3-4 = form of the peer-memory all-reduce (0 automatic: two-shot above two ranks,
  * 1 one-shot, 2 two-shot), bit 5 = chains set up from now on look events up one by one even when
- * every signal reads the same dataset (the multi-dataset form) -- used by the parity tests and
+ * every signal reads the same dataset (the multi-dataset form), bit 6 = chain steps are launched
+ * without programmatic dependent launch -- used by the parity tests and
  * measurements to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
@@ -131,6 +132,12 @@ int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);
  * chunk loop of the last segment, 31 exit.  out256x32 (host, may be NULL) receives the stamps
  * of the last launch.  tools/prof_bin.py prints the prologue / steady state / epilogue split. */
 int sxmc_bin_debug_stamps(int enable, unsigned long long* out256x32);
+/* The same for the lookup + NLL + Metropolis kernel: [block < 1200][8] stamps -- 0 entry, 1 state
+ * prefetched and next histogram buffer cleared, 2 per-signal constants ready, 3 lookup loop done,
+ * 4 block sum done, 5 ticket taken -- and in row 1200 those of the block that finished the step plus
+ * 6 event total known, 7 step finished (row 1201, word 0: its block index).
+ * tools/prof_nll.py prints the phase split. */
+int sxmc_nll_debug_stamps(int enable, unsigned long long* out1202x8);
 
 /* ---- nll_kernels: standalone NLL of a materialised lut (MCMC::nll, src/mcmc.cpp:390-415:
  *      nll_event_chunks -> nll_event_reduce -> nll_total).  All pointers are DEVICE

@@ -76,6 +76,7 @@ SYMBOLS = {
     "sxmc_enable_kernel_timing": (C.c_int, [C.c_int]),
     "sxmc_last_kernel_ms": (C.c_int, [c_fp, c_fp]),
     "sxmc_bin_debug_stamps": (C.c_int, [C.c_int, C.POINTER(C.c_uint64)]),
+    "sxmc_nll_debug_stamps": (C.c_int, [C.c_int, C.POINTER(C.c_uint64)]),
     "sxmc_nll_eval": (C.c_int, [c_vp, _SIZE, _SIZE, c_vp, _SIZE, _SIZE, c_vp, c_vp, c_vp, c_vp,
                                 c_vp, c_vp, c_dp, c_dp]),
     "sxmc_chain_create": (C.c_int, [C.POINTER(ChainConfig), C.POINTER(c_vp)]),

@@ -351,7 +351,8 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
   unsigned long long t0, t1;
   int j = 0;
   fast_partition(P, t0, t1, j);
-  if (t0 >= t1) return;
+  if (t0 >= t1) { pdl_wait(); pdl_trigger(); return; }
+  bool first_segment = true;
 
   while (t0 < t1) {
     const FastJob& job = P.job[j];
@@ -380,6 +381,10 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     if (lane == 0 && !reuse)
       for (unsigned i = 0; i < (unsigned)S && ca + i < cb; ++i) issue(ca + i, (it + i) % (unsigned)S);
 
+    // Programmatic dependent launch: everything above (barriers, the first bulk copies of the
+    // sample columns) ran while the previous kernel of the stream -- the step before's lookup --
+    // was still finishing; the parameters it proposes are read from here on.
+    if (first_segment) { pdl_wait(); pdl_trigger(); first_segment = false; }
     if (threadIdx.x < nsyst) {   // p = 0 + par * pow(x, 0)  (src/pdfz.cpp:310-314, npars <= 1)
       SystRt& sr = s_syst[threadIdx.x];
       const double* pp = params_override ? params_override : job.params;

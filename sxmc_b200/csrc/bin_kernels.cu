@@ -237,8 +237,8 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
       if (grid > max_grid) grid = max_grid;
       build_fast_params(L, g0, ng, (int)grid, P, &total);
       P.xdbg = g_bin_xdbg;
-      fk<<<(unsigned)grid, FAST_THREADS, L.smem_bytes, stream>>>(P);
-      SXMC_CUDA(cudaGetLastError());
+      SXMC_CUDA(launch_kernel_pdl(fk, dim3((unsigned)grid), dim3(FAST_THREADS), L.smem_bytes, stream,
+                                  L.pdl && L.njobs <= FAST_MAX_JOBS, P));
     }
     return SXMC_OK;
   }

@@ -31,6 +31,7 @@ static int g_force_generic = 0;
 static int g_force_dynamic = 0;
 static int g_p2p_form = 0;       // peer-memory all-reduce: 0 automatic (two-shot above 2 ranks), 1 one-shot, 2 two-shot
 static int g_no_mono = 0;        // chain batch: never take the monotone endpoint path (tests)
+static int g_no_pdl = 0;         // steps without programmatic dependent launch (measurement knob)
 static int g_no_group = 0;       // lookup: never group the events by bin (the multi-dataset form, on request)
 static long long g_persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent   // fast kernel with run-time systematic dispatch only
 static int g_timing = 0;
@@ -387,6 +388,22 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_no_mono = (force_generic >> 2) & 1;
   g_p2p_form = (force_generic >> 3) & 3;
   g_no_group = (force_generic >> 5) & 1;
+  g_no_pdl = (force_generic >> 6) & 1;
+  return SXMC_OK;
+}
+int sxmc_nll_debug_stamps(int enable, unsigned long long* out1202x8) {
+  static unsigned long long* dev = nullptr;
+  const size_t bytes = sizeof(unsigned long long) * 1202 * 8;
+  if (enable && !dev) {
+    SXMC_CUDA(cudaMalloc(&dev, bytes));
+    SXMC_CUDA(cudaMemset(dev, 0, bytes));
+  }
+  if (out1202x8 && dev) {
+    SXMC_CUDA(cudaDeviceSynchronize());
+    SXMC_CUDA(cudaMemcpy(out1202x8, dev, bytes, cudaMemcpyDeviceToHost));
+  }
+  if (!enable && dev) { cudaFree(dev); dev = nullptr; }
+  set_nll_xdbg(enable ? dev : nullptr);
   return SXMC_OK;
 }
 int sxmc_enable_kernel_timing(int on) { g_timing = on; return SXMC_OK; }
@@ -799,8 +816,12 @@ static int chain_build_tables(sxmc_chain* c) {
   return SXMC_OK;
 }
 
-static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr) {
-  SXMC_TRY(launch_bin(c->batch[b].launch, c->stream));
+// in_step: the launch follows the previous step's lookup kernel in the stream -- its prologue may
+// overlap that kernel's tail (programmatic dependent launch)
+static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr, bool in_step = false) {
+  BinLaunch BL = c->batch[b].launch;
+  BL.pdl = in_step && !g_no_pdl;
+  SXMC_TRY(launch_bin(BL, c->stream));
   c->launches += 1;
   if (after_bin) SXMC_CUDA(cudaEventRecord(after_bin, c->stream));
   if (c->p2p_nranks > 1) {
@@ -846,6 +867,10 @@ static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut
   L.mult = c->mult_dev;
   L.mult_nbins = c->total_nbins;
   L.ptable = nullptr;
+  // a step that re-binned: the lookup's prologue overlaps the binning kernel's tail; the early clear
+  // of the other histogram buffer only when no peer can still be reading it
+  L.pdl = mode == NLL_MODE_STEP && zero_other && !g_no_pdl;
+  L.zero_early = L.pdl && !((c->comm && c->comm->nranks > 1) || c->p2p_nranks > 1);
   // events looked up one by one (signals of several datasets): eval_pdf once per (signal, bin) first
   if (c->ptable_dev && !c->mult_dev && !lut && mode == NLL_MODE_STEP && c->nevents * (size_t)c->nsignals >= 4096) {
     if (zero_other || !c->ptable_valid) {        // zero_other == the step re-binned
@@ -1198,7 +1223,7 @@ static int chain_fixed_table(sxmc_chain* c, bool rebin) {
 
 // one MCMC step enqueued on the chain's stream: [bin -> (allreduce)] -> lookup+nll+decide+propose
 static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b) {
-  if (rebin) SXMC_TRY(chain_bin(c, b));
+  if (rebin) SXMC_TRY(chain_bin(c, b, nullptr, true));
   SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));
   return SXMC_OK;
 }
@@ -1434,7 +1459,7 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
       const int b = rebin ? (int)((i + 1) & 1) : 0;
       if (flush_bytes) SXMC_CUDA(cudaMemsetAsync(c->flush_buf, (int)(i & 0xff), flush_bytes, c->stream));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k], c->stream));
-      if (rebin) SXMC_TRY(chain_bin(c, b, c->tev[3 * CHUNK + k]));
+      if (rebin) SXMC_TRY(chain_bin(c, b, c->tev[3 * CHUNK + k], true));
       else SXMC_CUDA(cudaEventRecord(c->tev[3 * CHUNK + k], c->stream));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 1], c->stream));
       SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));

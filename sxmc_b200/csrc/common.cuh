@@ -255,6 +255,31 @@ struct ContourLevels {
 
 enum NllMode { NLL_MODE_STEP = 0, NLL_MODE_INIT = 1, NLL_MODE_EVAL_ONLY = 2 };
 
+// ---- programmatic dependent launch ---------------------------------------------------------
+// A kernel launched with `pdl` may start while its predecessor in the stream is still running:
+// everything it does before pdl_wait() must not depend on (or disturb) the predecessor; pdl_wait()
+// returns once the predecessor has completed and its writes are visible.  pdl_trigger() lets the
+// successor's blocks be scheduled as soon as this grid's blocks have all called it (or exited).
+// Both are no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                     cudaStream_t stream, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // error plumbing --------------------------------------------------------------------------
 void set_error(const std::string& msg);
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);

@@ -22,6 +22,7 @@ struct BinLaunch {
   int nobs, nslots;
   int max_total_nbins;
   int blocks_per_sm;         // <=0: occupancy maximum (generic kernel)
+  bool pdl;                  // fast kernel: programmatic dependent launch on the previous kernel of the stream
   int prog_nops;                 // >= 0: compile-time systematic program, < 0: run-time dispatch
   unsigned prog_codes;
   int rows_per_stage, nstages;   // fast kernel pipeline shape
@@ -82,8 +83,11 @@ struct NllLaunch {
   const unsigned* mult;         // optional events per bin [mult_nbins]: grouped lookup (all signals one dataset)
   int mult_nbins;               // bins per PDF (also the row length of ptable)
   const double* ptable;         // optional [nsignals][mult_nbins] PDF values of this step (launch_pdf_table)
+  bool pdl;                     // programmatic dependent launch on the previous kernel of the stream (the binning)
+  bool zero_early;              // clear zero_ptr before waiting for that kernel (nobody else reads the buffer)
 };
 int nll_grid_for(long long nevents);
+void set_nll_xdbg(unsigned long long* dev);   // [1202][8] stamps of the next lookup launches, or NULL
 int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, double* table_dev,
                      cudaStream_t stream);
 int launch_nll(const NllLaunch& L, cudaStream_t stream);

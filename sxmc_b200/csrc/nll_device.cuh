@@ -294,14 +294,15 @@ static __device__ void finish_step(FinState& F, ChainState* st, int np, int ns, 
 // after the decision its two halves are independent -- warp 0 draws the next proposal while
 // warp 1 appends the row and updates the running sums.  Both read what they need of
 // current/proposed into registers, meet at a 64-thread barrier, then write.  Falls back to
-// finish_step (warp 0 alone) outside NLL_MODE_STEP and for more than 32 parameters.
+// finish_step (warp 0 alone) outside NLL_MODE_STEP and for more than 64 parameters (a lane owns
+// parameters lane and lane + 32).
 __device__ __forceinline__ void fin_bar64() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
 
 static __device__ void finish_step2(FinState& F, ChainState* st, int np, int ns, int nsources, double ev_new,
                                     int mode, const double* s_term, int lane, int wid,
                                     const double* pre_z = nullptr, const double* pre_u = nullptr,
                                     long long* clk = nullptr) {
-  if (np > 32 || mode != NLL_MODE_STEP) {
+  if (np > 64 || mode != NLL_MODE_STEP) {
     if (wid == 0) finish_step(F, st, np, ns, nsources, ev_new, mode, s_term, lane, pre_z, pre_u, clk);
     return;
   }
@@ -310,19 +311,25 @@ static __device__ void finish_step2(FinState& F, ChainState* st, int np, int ns,
   const unsigned step = F.step;
   const bool retune = step == F.burnin_steps || step == 2 * F.burnin_steps;
   const bool reset_stats = retune && !F.debug_mode;
+  // a lane owns parameters lane and lane + 32
+  const int k0 = lane, k1 = lane + 32;
   if (wid == 0) {
     // --- burn-in re-tune of the jump widths (src/mcmc.cpp:274-311), before this step's decision
     if (retune) {
       const double n = F.stat_n;
-      if (lane < np && !F.fixed[lane]) {
-        double rms = 0;
-        if (n > 0) {
-          const double m = F.stat_sx[lane] / n;
-          rms = sqrt(fabs(__dadd_rn(F.stat_sxx[lane] / n, -__dmul_rn(m, m))));
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int k = h ? k1 : k0;
+        if (k < np && !F.fixed[k]) {
+          double rms = 0;
+          if (n > 0) {
+            const double m = F.stat_sx[k] / n;
+            rms = sqrt(fabs(__dadd_rn(F.stat_sxx[k] / n, -__dmul_rn(m, m))));
+          }
+          const double fit_width = rms > 0 ? rms : (double)F.jump_width[k];
+          F.jump_width[k] = (float)__dmul_rn((double)F.scale_factor, fit_width);
+          st->jump_width[k] = F.jump_width[k];
         }
-        const double fit_width = rms > 0 ? rms : (double)F.jump_width[lane];
-        F.jump_width[lane] = (float)__dmul_rn((double)F.scale_factor, fit_width);
-        st->jump_width[lane] = F.jump_width[lane];
       }
       __syncwarp();
     }
@@ -367,28 +374,32 @@ static __device__ void finish_step2(FinState& F, ChainState* st, int np, int ns,
   }
   fin_bar64();                                   // the decision is visible to both warps
   const int accept = F.accept_flag;
-  const int k = lane;
   if (wid == 0) {
     // --- pick_new_vector_device (src/nll_kernels.cpp:31-53) from the point the chain is at now
-    const bool floating = k < np && F.jump_width[k] > 0;
-    const unsigned m = __ballot_sync(0xffffffffu, floating);
-    double v = 0;
-    if (k < np) {
-      v = accept ? F.proposed[k] : F.current[k];
-      if (floating) {
+    const bool fl0 = k0 < np && F.jump_width[k0] > 0, fl1 = k1 < np && F.jump_width[k1] > 0;
+    const unsigned m0 = __ballot_sync(0xffffffffu, fl0), m1 = __ballot_sync(0xffffffffu, fl1);
+    double v[2] = {0, 0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = h ? k1 : k0;
+      if (k >= np) continue;
+      double x = accept ? F.proposed[k] : F.current[k];
+      if (h ? fl1 : fl0) {
         double z;
-        if (F.tape_normals) {
-          const unsigned long long ti = F.i_normal + __popc(m & ((1u << lane) - 1));
+        if (F.tape_normals) {                    // normals are consumed in parameter order
+          const unsigned long long ti = F.i_normal + (h ? __popc(m0) : 0) + __popc((h ? m1 : m0) & ((1u << lane) - 1));
           z = ti < F.n_normals ? F.tape_normals[ti] : 0.0;
         } else {
           z = pre_z ? pre_z[k] : fin_normal(F, step, (unsigned)k, 1u);
         }
-        v = __dadd_rn(v, __dmul_rn((double)F.jump_width[k], z));
+        x = __dadd_rn(x, __dmul_rn((double)F.jump_width[k], z));
       }
+      v[h] = x;
     }
     fin_bar64();                                 // warp 1 has read the old proposal
-    if (k < np) { F.proposed[k] = v; st->proposed[k] = v; }
-    if (lane == 0 && F.tape_normals) { F.i_normal += __popc(m); st->i_normal = F.i_normal; }
+    if (k0 < np) { F.proposed[k0] = v[0]; st->proposed[k0] = v[0]; }
+    if (k1 < np) { F.proposed[k1] = v[1]; st->proposed[k1] = v[1]; }
+    if (lane == 0 && F.tape_normals) { F.i_normal += __popc(m0) + __popc(m1); st->i_normal = F.i_normal; }
     FIN_CLK(3);
     FIN_CLK(4);
   } else {
@@ -398,24 +409,32 @@ static __device__ void finish_step2(FinState& F, ChainState* st, int np, int ns,
     const double cur_nll = F.current_nll;
     const bool store = row < F.row_cap;
     float* out = F.rows + row * (np + 1);
-    double oldp = 0, cur = 0, sx0 = 0, sxx0 = 0;
-    if (k < np) {
-      oldp = F.proposed[k];
-      cur = accept ? oldp : F.current[k];
-      sx0 = reset_stats ? 0.0 : F.stat_sx[k];
-      sxx0 = reset_stats ? 0.0 : F.stat_sxx[k];
+    double oldp[2] = {0, 0}, cur[2] = {0, 0}, sx0[2] = {0, 0}, sxx0[2] = {0, 0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = h ? k1 : k0;
+      if (k < np) {
+        oldp[h] = F.proposed[k];
+        cur[h] = accept ? oldp[h] : F.current[k];
+        sx0[h] = reset_stats ? 0.0 : F.stat_sx[k];
+        sxx0[h] = reset_stats ? 0.0 : F.stat_sxx[k];
+      }
     }
     fin_bar64();                                 // warp 0 has read current / proposed
-    if (k < np) {
-      if (F.prop_trace) F.prop_trace[(unsigned long long)step * np + k] = oldp;
-      if (accept) { F.current[k] = cur; st->current[k] = cur; }
-      const float xf = (float)cur;
-      if (store) out[k] = xf;
-      const double x = (double)xf;
-      F.stat_sx[k] = __dadd_rn(sx0, x);
-      F.stat_sxx[k] = __dadd_rn(sxx0, __dmul_rn(x, x));
-      st->stat_sx[k] = F.stat_sx[k];
-      st->stat_sxx[k] = F.stat_sxx[k];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = h ? k1 : k0;
+      if (k < np) {
+        if (F.prop_trace) F.prop_trace[(unsigned long long)step * np + k] = oldp[h];
+        if (accept) { F.current[k] = cur[h]; st->current[k] = cur[h]; }
+        const float xf = (float)cur[h];
+        if (store) out[k] = xf;
+        const double x = (double)xf;
+        F.stat_sx[k] = __dadd_rn(sx0[h], x);
+        F.stat_sxx[k] = __dadd_rn(sxx0[h], __dmul_rn(x, x));
+        st->stat_sx[k] = F.stat_sx[k];
+        st->stat_sxx[k] = F.stat_sxx[k];
+      }
     }
     if (lane == 0) {
       if (store) out[np] = (float)cur_nll;

@@ -20,7 +20,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
                   int np, int nsources, long long ne, ChainState* st, double* partials,
                   unsigned* ticket, int mode, float* lut, unsigned* zero_ptr,
                   unsigned long long zero_words, const unsigned* __restrict__ mult, int mult_nbins,
-                  const double* __restrict__ ptable) {
+                  const double* __restrict__ ptable, unsigned long long* xdbg, int zero_early) {
   __shared__ double s_c[NLL_MAX_SIGNALS];
   __shared__ double s_bn[NLL_MAX_SIGNALS];
   __shared__ const unsigned* s_bins[NLL_MAX_SIGNALS];
@@ -36,16 +36,36 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
   const int tid = threadIdx.x;
   const long long gtid = blockIdx.x * (long long)THREADS + tid;
   const long long gstride = (long long)gridDim.x * THREADS;
+  // profiling hook (sxmc_nll_debug_stamps): [block < 1200][8] %globaltimer stamps, the block that
+  // finishes the step also writes row 1200
+#define NLL_DBG(k)                                                                         \
+  do {                                                                                     \
+    if (xdbg && tid == 0) {                                                                \
+      unsigned long long t_;                                                               \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                               \
+      xdbg[8ull * (blockIdx.x < 1200u ? blockIdx.x : 1199u) + (k)] = t_;                   \
+    }                                                                                      \
+  } while (0)
+  NLL_DBG(0);
 
+  // ---- prologue that does not depend on this step's histograms: under programmatic dependent
+  // launch it runs while the binning kernel is still streaming.  The chain state was written by the
+  // previous step's launch, which completed before the binning kernel let this one start.
   prefetch_state(F, st, np, tid, THREADS);
-  // per-signal tables; norms[j] is addressed directly so that it does not wait for sigs[j]
   NllSignal my_sig;
   unsigned my_norm = 0;
-  if (tid < ns) { my_sig = sigs[tid]; my_norm = norms[tid]; }
-
-  // clear the histogram buffer the NEXT step bins into (double-buffered; nobody reads it now)
-  for (unsigned long long w = gtid; w < zero_words; w += gstride) zero_ptr[w] = 0u;
+  if (tid < ns) my_sig = sigs[tid];
+  // clear the histogram buffer the NEXT step bins into (double-buffered; nobody reads it now --
+  // unless peers may still be summing it: then only after the wait)
+  if (zero_early)
+    for (unsigned long long w = gtid; w < zero_words; w += gstride) zero_ptr[w] = 0u;
+  pdl_wait();
+  pdl_trigger();
+  if (!zero_early)
+    for (unsigned long long w = gtid; w < zero_words; w += gstride) zero_ptr[w] = 0u;
+  if (tid < ns) my_norm = norms[tid];
   __syncthreads();
+  NLL_DBG(1);
 
   // block 0's last warp draws the step's random numbers while everybody looks up events; the
   // block that finishes last picks them up (ordered by block 0's ticket, as its partial sum is)
@@ -75,6 +95,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     s_term[ns + i] = t;
   }
   __syncthreads();
+  NLL_DBG(2);
 
   double sum = 0;
   if (mult && !lut) {
@@ -84,28 +105,27 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     // (signal, event); no gather.
     for (long long b = gtid; b < mult_nbins; b += gstride) {
       const unsigned m = mult[b];
-      if (!m) continue;
       double s = 0;
-      int j = 0;
-      // eight signals' counts in flight at a time (the loads do not depend on the running sum, but
-      // a rolled loop issues them one L2 round trip after the other); same order of additions
-      for (; j + 8 <= ns; j += 8) {
-        unsigned h[8];
+      // up to 32 signals' counts in flight at once, issued together with the multiplicity: ONE L2
+      // round trip per bin instead of one per group of signals (the loads do not depend on the
+      // running sum; a rolled loop issues them one after the other).  Same order of additions.
+      // (width 32 in the many-bin launch of 128-thread blocks; 8 elsewhere, where registers are short)
+      constexpr int LW = THREADS == 128 ? 32 : 8;
+      for (int j0 = 0; j0 < ns; j0 += LW) {
+        unsigned h[LW];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) h[q] = s_bins[j + q][b];
+        for (int q = 0; q < LW; ++q) h[q] = (j0 + q < ns) ? s_bins[j0 + q][b] : 0u;
+        if (!m) break;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          float v = (float)((double)h[q] / s_bn[j + q]);              // pdfz.cpp:429-432
-          if (isnan(v)) v = 0.0f;                                     // nll_kernels.cpp:107
-          s = __dadd_rn(s, __dmul_rn(s_c[j + q], (double)v));
+        for (int q = 0; q < LW; ++q) {
+          if (j0 + q < ns) {
+            float v = (float)((double)h[q] / s_bn[j0 + q]);           // pdfz.cpp:429-432
+            if (isnan(v)) v = 0.0f;                                   // nll_kernels.cpp:107
+            s = __dadd_rn(s, __dmul_rn(s_c[j0 + q], (double)v));
+          }
         }
       }
-      for (; j < ns; ++j) {
-        float v = (float)((double)s_bins[j][b] / s_bn[j]);
-        if (isnan(v)) v = 0.0f;
-        s = __dadd_rn(s, __dmul_rn(s_c[j], (double)v));
-      }
-      if (s > 0) sum += (double)m * log(s);
+      if (m && s > 0) sum += (double)m * log(s);
     }
   } else if (ptable && !lut) {
     // Per-event lookup against the step's PDF-value table (pdf_table_kernel: eval_pdf's division
@@ -184,7 +204,9 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     }
     if (s > 0) sum += log(s);
   }
+  NLL_DBG(3);
   const double bsum = block_sum<THREADS>(sum, s_warp);
+  NLL_DBG(4);
   if (gridDim.x == 1) {
     // small fit, one block (launch_nll): no partials, no ticket round trip, no second reduction
     if (tid == 0) s_warp[0] = bsum;
@@ -201,6 +223,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
       s_last = (t == gridDim.x - 1);
     }
     __syncthreads();
+    NLL_DBG(5);
     if (!s_last) return;
 
     // ---- last block: total the partials in a fixed order, then finish the step -------------
@@ -215,9 +238,18 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
     }
   }
   __syncthreads();
+  NLL_DBG(6);
   if (tid < 64)
     finish_step2(F, st, np, ns, nsources, s_warp[0], mode, s_term, tid & 31, tid >> 5, pre_rng ? s_z : nullptr,
                 pre_rng ? &s_u : nullptr);
+  if (xdbg && tid == 0) {
+    unsigned long long t_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+    xdbg[8ull * 1200 + 7] = t_;
+    for (int k = 0; k < 7; ++k) xdbg[8ull * 1200 + k] = xdbg[8ull * (blockIdx.x < 1200u ? blockIdx.x : 1199u) + k];
+    xdbg[8ull * 1201] = blockIdx.x;
+  }
+#undef NLL_DBG
 }
 
 // eval_pdf's value (src/pdfz.cpp:429-432) for every (signal, bin) of this step, with the NaN of
@@ -245,6 +277,9 @@ int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int n
   return SXMC_OK;
 }
 
+static unsigned long long* g_nll_xdbg = nullptr;   // profiling hook, NULL in production
+void set_nll_xdbg(unsigned long long* dev) { g_nll_xdbg = dev; }
+
 int nll_grid_for(long long nevents) {
   long long g = (nevents + NLL_THREADS - 1) / NLL_THREADS;
   if (g < 1) g = 1;
@@ -261,13 +296,21 @@ int launch_nll(const NllLaunch& L, cudaStream_t stream) {
   // hand-over (store, fence, ticket, last block's reload: ~3 us of dependent round trips) from a
   // kernel that is latency from end to end.  1024 threads: one bin per thread for workload B.
   if (L.mult && !L.lut && L.mult_nbins <= 4096 && L.zero_words <= 65536) {
-    lookup_nll_kernel<1024><<<1, 1024, 0, stream>>>(L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources,
+    SXMC_CUDA(launch_kernel_pdl(lookup_nll_kernel<1024>, dim3(1), dim3(1024), 0, stream, L.pdl, L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources,
                                                     L.nevents, L.state, L.partials, L.ticket, L.mode, L.lut,
-                                                    L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable);
+                                                    L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable, g_nll_xdbg, L.zero_early ? 1 : 0));
+  } else if (L.mult && !L.lut) {
+    // grouped lookup over many bins: one bin per thread, 128-thread blocks so that every SM gets
+    // one (25 000 bins: 196 blocks), no block without work
+    int grid = (L.mult_nbins + 127) / 128;
+    if (grid > 148 * 8) grid = 148 * 8;
+    SXMC_CUDA(launch_kernel_pdl(lookup_nll_kernel<128>, dim3((unsigned)grid), dim3(128), 0, stream, L.pdl, L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources,
+                                                     L.nevents, L.state, L.partials, L.ticket, L.mode, L.lut,
+                                                     L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable, g_nll_xdbg, L.zero_early ? 1 : 0));
   } else {
-    lookup_nll_kernel<NLL_THREADS><<<L.grid, NLL_THREADS, 0, stream>>>(
+    SXMC_CUDA(launch_kernel_pdl(lookup_nll_kernel<NLL_THREADS>, dim3((unsigned)L.grid), dim3(NLL_THREADS), 0, stream, L.pdl,
         L.sigs_dev, L.norms_dev, L.nsignals, L.nparameters, L.nsources, L.nevents, L.state, L.partials, L.ticket,
-        L.mode, L.lut, L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable);
+        L.mode, L.lut, L.zero_ptr, L.zero_words, L.mult, L.mult_nbins, L.ptable, g_nll_xdbg, L.zero_early ? 1 : 0));
   }
   SXMC_CUDA(cudaGetLastError());
   return SXMC_OK;

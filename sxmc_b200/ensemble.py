@@ -174,15 +174,59 @@ def _root_axis_limits(xmin, xmax, nbins=100):
     return bwid * lwid, bwid * kwid, int(kwid - lwid)
 
 
+def _fit_gaus_mu(x, y, a0, mu0, s0):
+    """Chi-square fit of A exp(-(x-mu)^2 / 2 s^2) to (x_i, y_i +- sqrt(y_i)) by Levenberg-Marquardt; the
+    same iteration, step for step, as cxx/src/projection.cpp::fit_gaus_mu.  Returns mu."""
+    p = np.array([a0, mu0, s0], dtype=np.float64)
+    w = 1.0 / np.sqrt(y)
+
+    def chi2(q):
+        z = (x - q[1]) / q[2]
+        r = (q[0] * np.exp(-0.5 * z * z) - y) * w
+        return float(np.dot(r, r))
+
+    lam, c0 = 1e-3, chi2(p)
+    for _ in range(200):
+        z = (x - p[1]) / p[2]
+        e = np.exp(-0.5 * z * z)
+        r = (p[0] * e - y) * w
+        J = np.stack([e * w, p[0] * e * z / p[2] * w, p[0] * e * z * z / p[2] * w], axis=1)
+        JtJ, Jtr = J.T @ J, J.T @ r
+        improved = False
+        for _ in range(30):
+            A = JtJ + lam * np.diag(np.diag(JtJ))
+            try:
+                step = np.linalg.solve(A, -Jtr)
+            except np.linalg.LinAlgError:
+                lam *= 10
+                continue
+            q = p + step
+            if not (q[2] > 0) or not np.isfinite(q[0]) or not np.isfinite(q[1]):
+                lam *= 10
+                continue
+            c1 = chi2(q)
+            if c1 <= c0:
+                gain = c0 - c1
+                p, c0 = q, c1
+                lam = max(lam * 0.3, 1e-12)
+                improved = True
+                if gain <= 1e-12 * (1.0 + c0):
+                    return float(p[1])
+                break
+            lam *= 10
+        if not improved:
+            break
+    return float(p[1])
+
+
 def projection_interval(values, cl, nbins=100):
     """sxmc::errors::Projection::get_interval (src/error_estimators/projection.cpp:14-77) on one
     column of the chain.  Host code: the 1-D projection (`LikelihoodSpace::get_projection`,
     src/likelihood.cpp:76-85 = TTree::Draw into an auto-binned TH1F), a chi-square Gaussian fit of
-    its bins (TH1::Fit("gaus"): bins with content, error sqrt(n)) for the mode, then the
+    its bins (TH1::Fit("gaus"): bins with content, error sqrt(n); Levenberg-Marquardt) for the mode, then the
     reference's bin walk: one-sided limit when less than cl/2 of the probability lies at or
     below the mode's bin, else cl/2 to each side.  The walk is the reference's arithmetic; the axis
     finder and the fit restate ROOT (unpinned)."""
-    from scipy.optimize import least_squares
     v = np.asarray(values, dtype=np.float32).astype(np.float64)
     if v.size == 0:
         raise ValueError("projection_interval: empty chain")
@@ -198,10 +242,7 @@ def projection_interval(values, cl, nbins=100):
     rms = float(np.sqrt(np.average((centers - mean) ** 2, weights=y))) if y.sum() > 0 else 0.0
     mu = mean
     if use.sum() >= 3 and rms > 0:
-        def resid(p):
-            return (p[0] * np.exp(-0.5 * ((centers[use] - p[1]) / p[2]) ** 2) - y[use]) / np.sqrt(y[use])
-        fit = least_squares(resid, [float(y.max()), mean, rms])
-        mu = float(fit.x[1])
+        mu = _fit_gaus_mu(centers[use], y[use], float(y.max()), mean, rms)
     total = content.sum()                              # Integral(0, -1) includes under/overflow
 
     def integral(a, b):

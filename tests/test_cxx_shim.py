@@ -80,6 +80,34 @@ def test_shim_library_and_runner_are_built():
         assert r.returncode == 3 and "no CPU fallback" in r.stderr
 
 
+def test_cxx_projection_estimator_equals_the_python_host_estimator():
+    """sxmc::errors::Projection (src/error_estimators/projection.cpp:14-77) in cxx/src/projection.cpp
+    against sxmc_b200.ensemble.projection_interval: same axis, same bin walk; the Gaussian fits are two
+    implementations (Levenberg-Marquardt here, scipy there) of the same chi-square minimum."""
+    from sxmc_b200 import ensemble
+    lib = ctypes.CDLL(SHIM)
+    fn = lib.sxmc_cxx_projection_interval
+    fn.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_long, ctypes.c_long, ctypes.c_float,
+                   ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int)]
+    rng = np.random.default_rng(3)
+    cols = {"gauss": rng.normal(5.0, 0.5, 200000), "exp": rng.exponential(1.0, 200000),
+            "narrow": rng.normal(1e-3, 2e-5, 50000), "skew": rng.gamma(3.0, 2.0, 100000),
+            "const": np.full(1000, 2.5)}
+    table = np.stack([v[:1000] for v in cols.values()], axis=1).astype(np.float32)      # strided access
+    for k, (name, v) in enumerate(cols.items()):
+        for cl in (0.683, 0.9):
+            for arr, n, stride in ((np.ascontiguousarray(v, np.float32), len(v), 1),
+                                   (table[:, k:].ravel(), 1000, table.shape[1] - k)):
+                want = ensemble.projection_interval(arr[::stride][:n] if stride > 1 else arr, cl)
+                out = (ctypes.c_float * 5)()
+                one = ctypes.c_int(0)
+                assert fn(arr.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), n, stride, cl, out, ctypes.byref(one)) == 0
+                assert bool(one.value) == want.one_sided, (name, cl)
+                assert abs(out[0] - want.point_estimate) <= 2e-4 * max(1e-6, abs(want.point_estimate)) + 1e-9, (name, cl)
+                assert np.float32(out[1]) == np.float32(want.lower) and np.float32(out[2]) == np.float32(want.upper), (name, cl)
+                assert abs(out[4] - want.coverage) < 1e-6 and abs(out[3] - cl) < 1e-6
+
+
 def test_case_files_round_trip(tmp_path):
     write_cases(tmp_path / "cases.txt")
     text = (tmp_path / "cases.txt").read_text()
