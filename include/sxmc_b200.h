@@ -118,7 +118,8 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * path, bits 3-4 = form of the peer-memory all-reduce (0 automatic: two-shot above two ranks,
  * 1 one-shot, 2 two-shot), bit 5 = chains set up from now on look events up one by one even when
  * every signal reads the same dataset (the multi-dataset form), bit 6 = chain steps are launched
- * without programmatic dependent launch -- used by the parity tests and
+ * without programmatic dependent launch, bit 7 = no run-time compilation of systematic programs (below)
+ * -- used by the parity tests and
  * measurements to cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
@@ -132,6 +133,14 @@ int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);
  * chunk loop of the last segment, 31 exit.  out256x32 (host, may be NULL) receives the stamps
  * of the last launch.  tools/prof_bin.py prints the prologue / steady state / epilogue split. */
 int sxmc_bin_debug_stamps(int enable, unsigned long long* out256x32);
+/* The fast binning kernel takes a fit's systematic program (which type acts on which column, in which
+ * order; apply_systematic, src/pdfz.cpp:306-331) as a template parameter.  The build instantiates the
+ * BASELINE workloads' programs; any other program of up to four single-coefficient systematics is
+ * compiled for the fit with NVRTC when it is first planned (~0.4 s, cached per process; SXMC_NO_JIT=1
+ * or kernel_select bit 7 keeps the run-time dispatching kernel instead).  This entry point only compiles (no GPU needed) and reports the cubin
+ * size: nslots = columns the kernel loads, codes = 8 bits per systematic, type | slot_obs << 2 |
+ * slot_extra << 5. */
+int sxmc_jit_compile_check(int nobs, int nslots, int smem_hist, int nops, unsigned codes, size_t* cubin_bytes_out);
 /* The same for the lookup + NLL + Metropolis kernel: [block < 1200][8] stamps -- 0 entry, 1 state
  * prefetched and next histogram buffer cleared, 2 per-signal constants ready, 3 lookup loop done,
  * 4 block sum done, 5 ticket taken -- and in row 1200 those of the block that finished the step plus
@@ -204,6 +213,10 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
 /* the part of bin_ms_sum of the last sxmc_chain_advance_timed spent between the end of the
  * binning kernel and the end of the histogram all-reduce (sample-sharded chains; else ~0) */
 int sxmc_chain_last_comm_ms(sxmc_chain* c, float* ms_out);
+/* which binning kernel the chain's steps launch (decided when the data are set): 0 per-sample interpreter
+ * (multi-coefficient systematics, > 3 observables), 1 fast kernel with run-time dispatch of the systematics,
+ * 2 fast kernel with a compile-time program of the build's table, 3 the same compiled for this fit by NVRTC */
+int sxmc_chain_bin_kernel_kind(sxmc_chain* c, int* kind_out);
 /* the ntuple rows: nparameters+1 floats each (src/nll_kernels.cpp:78-84) */
 int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows);
 int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out);

@@ -77,6 +77,7 @@ SYMBOLS = {
     "sxmc_last_kernel_ms": (C.c_int, [c_fp, c_fp]),
     "sxmc_bin_debug_stamps": (C.c_int, [C.c_int, C.POINTER(C.c_uint64)]),
     "sxmc_nll_debug_stamps": (C.c_int, [C.c_int, C.POINTER(C.c_uint64)]),
+    "sxmc_jit_compile_check": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, C.POINTER(_SIZE)]),
     "sxmc_nll_eval": (C.c_int, [c_vp, _SIZE, _SIZE, c_vp, _SIZE, _SIZE, c_vp, c_vp, c_vp, c_vp,
                                 c_vp, c_vp, c_dp, c_dp]),
     "sxmc_chain_create": (C.c_int, [C.POINTER(ChainConfig), C.POINTER(c_vp)]),
@@ -103,6 +104,7 @@ SYMBOLS = {
     "sxmc_chain_get_bins": (C.c_int, [c_vp, c_up]),
     "sxmc_chain_set_mode": (C.c_int, [c_vp, C.c_int]),
     "sxmc_chain_last_comm_ms": (C.c_int, [c_vp, c_fp]),
+    "sxmc_chain_bin_kernel_kind": (C.c_int, [c_vp, C.POINTER(C.c_int)]),
     "sxmc_chain_last_path": (C.c_int, [c_vp, C.POINTER(C.c_int)]),
     "sxmc_chain_phase_stamps": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_uint64)]),
     "sxmc_generator_create": (C.c_int, [C.POINTER(c_vp), C.c_int, c_dp, c_up, c_dp, C.c_int, c_fp, c_fp,

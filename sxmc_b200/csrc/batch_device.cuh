@@ -98,7 +98,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
 #pragma unroll
         for (int j = 0; j < DIRECT_NS; ++j) {
           if (j < ns) {
-            float v = (float)((double)hreg[j] / S.bn[j]);                       // pdfz.cpp:429-432
+            float v = pdf_value(hreg[j], S.bn[j]);                              // pdfz.cpp:429-432
             if (isnan(v)) v = 0.0f;                                              // nll_kernels.cpp:107
             acc = __dadd_rn(acc, __dmul_rn(S.c[j], (double)v));
           }
@@ -114,7 +114,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
     // instead of once per (signal, event), and the values live in shared memory.
     for (int q = tid; q < ns * tnb; q += BATCH_THREADS) {
       const int j = q / tnb;
-      float v = (float)((double)__ldcg(my_hist + q) / S.bn[j]);              // pdfz.cpp:429-432
+      float v = pdf_value(__ldcg(my_hist + q), S.bn[j]);                     // pdfz.cpp:429-432
       if (isnan(v)) v = 0.0f;                                                  // nll_kernels.cpp:107
       S.pdf[q] = v;
     }
@@ -135,7 +135,7 @@ __device__ __forceinline__ void batch_lookup_tail(BatchShared& S, const BatchPar
       const int rb = S.rb[j][i];
       float v = 0.0f;
       if (rb >= 0 && rb < tnb) {
-        v = (float)((double)__ldcg(my_hist + (size_t)j * tnb + rb) / S.bn[j]);   // pdfz.cpp:429-432
+        v = pdf_value(__ldcg(my_hist + (size_t)j * tnb + rb), S.bn[j]);          // pdfz.cpp:429-432
         if (isnan(v)) v = 0.0f;                                                  // nll_kernels.cpp:107
       }
       acc = __dadd_rn(acc, __dmul_rn(S.c[j], (double)v));

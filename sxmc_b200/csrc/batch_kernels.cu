@@ -310,8 +310,8 @@ int launch_chain_batch(const BatchPlan& plan, const BatchParams& Q0, cudaStream_
   const BinLaunch& L = plan.launch;
   BatchKernel fk = nullptr;
   for (const BatchEntry& e : g_batch_table)
-    if (e.nobs == L.nobs && e.ns == L.nslots && e.nops == L.prog_nops &&
-        (L.prog_nops <= 0 || e.codes == L.prog_codes))
+    if (e.nobs == L.nobs && e.ns == L.nslots && e.nops == (L.jit ? -1 : L.prog_nops) &&      // (a program compiled
+        (L.jit || L.prog_nops <= 0 || e.codes == L.prog_codes))                              // by NVRTC exists for bin_fast_kernel only)
       fk = e.k;
   if (!fk) { set_error("chain batch: no instantiation for this shape"); return SXMC_ENOTSMALL; }
   FastParams P;

@@ -531,8 +531,8 @@ int plan_chain_batch_mono(const BinLaunch& L, const unsigned long long* nsamples
   plan->grid = sms;
   plan->smem_bytes = MONO_SHARED_BYTES + (((size_t)max_n * sizeof(float) + 127) & ~(size_t)127);
   plan->max_edges = max_edges;
-  plan->prog_nops = L.prog_nops;
-  plan->prog_codes = L.prog_codes;
+  plan->prog_nops = L.jit ? -1 : L.prog_nops;      // NVRTC-compiled programs exist for bin_fast_kernel only
+  plan->prog_codes = L.jit ? 0u : L.prog_codes;
   return SXMC_OK;
 }
 

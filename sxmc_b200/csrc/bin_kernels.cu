@@ -222,8 +222,11 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
   if (L.total_units == 0) return SXMC_OK;
   if (L.fast) {
     FastKernel fk = pick_fast(L.nobs, L.nslots, L.prog_nops, L.prog_codes, L.smem_hist);
-    if (!fk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
-    SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
+    void* jk = nullptr;          // the fit's own program, compiled at run time (jit.cu)
+    if (!fk && L.jit) jk = jit_bin_fast_kernel(L.nobs, L.nslots, L.smem_hist, L.prog_nops, L.prog_codes);
+    if (!fk && !jk) fk = pick_fast(L.nobs, L.nslots, -1, 0u, L.smem_hist);      // run-time dispatch
+    if (!fk && !jk) { set_error("launch_bin: no fast kernel for this shape"); return SXMC_ESTATE; }
+    if (fk) SXMC_CUDA(cudaFuncSetAttribute((const void*)fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes));
     // jobs travel in the kernel parameters (constant bank), FAST_MAX_JOBS per launch
     for (int g0 = 0; g0 < L.njobs; g0 += FAST_MAX_JOBS) {
       const int ng = L.njobs - g0 < FAST_MAX_JOBS ? L.njobs - g0 : FAST_MAX_JOBS;
@@ -237,8 +240,13 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
       if (grid > max_grid) grid = max_grid;
       build_fast_params(L, g0, ng, (int)grid, P, &total);
       P.xdbg = g_bin_xdbg;
-      SXMC_CUDA(launch_kernel_pdl(fk, dim3((unsigned)grid), dim3(FAST_THREADS), L.smem_bytes, stream,
-                                  L.pdl && L.njobs <= FAST_MAX_JOBS, P));
+      const bool pdl = L.pdl && L.njobs <= FAST_MAX_JOBS;
+      if (jk) {
+        const int rc = jit_launch_bin(jk, (unsigned)grid, L.smem_bytes, stream, pdl, P);
+        if (rc) return rc;
+      } else {
+        SXMC_CUDA(launch_kernel_pdl(fk, dim3((unsigned)grid), dim3(FAST_THREADS), L.smem_bytes, stream, pdl, P));
+      }
     }
     return SXMC_OK;
   }
@@ -437,7 +445,7 @@ __global__ void eval_pdf_kernel(const EvalPdfJob* __restrict__ jobs, int njobs) 
     if (b == -2) v = 0.0f;
     else if (b < 0) v = __int_as_float(0x7fc00000);
     else if (b >= job.total_nbins) v = 0.0f;   // reference reads past the array (undefined)
-    else v = (float)((double)job.bins[b] / bin_norm);
+    else v = pdf_value(job.bins[b], bin_norm);
     job.out[job.stride * i] = v;
   }
 }

@@ -31,6 +31,7 @@ static int g_force_generic = 0;
 static int g_force_dynamic = 0;
 static int g_p2p_form = 0;       // peer-memory all-reduce: 0 automatic (two-shot above 2 ranks), 1 one-shot, 2 two-shot
 static int g_no_mono = 0;        // chain batch: never take the monotone endpoint path (tests)
+static int g_no_jit = 0;         // programs outside the build's table keep the run-time dispatching kernel
 static int g_no_pdl = 0;         // steps without programmatic dependent launch (measurement knob)
 static int g_no_group = 0;       // lookup: never group the events by bin (the multi-dataset form, on request)
 static long long g_persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent   // fast kernel with run-time systematic dispatch only
@@ -306,7 +307,17 @@ static void plan_launch(Batch& b, int n) {
         if (j == 0) codes = cj;
         else if (cj != codes) same = false;
       }
-      if (same && bin_fast_has_program(L.nobs, max_slots, nops, codes)) { L.prog_nops = nops; L.prog_codes = codes; }
+      if (same && bin_fast_has_program(L.nobs, max_slots, nops, codes)) {
+        L.prog_nops = nops;
+        L.prog_codes = codes;
+      } else if (same && nops >= 1 && nops <= FAST_MAX_OPS && !g_no_jit &&
+                 jit_bin_fast_kernel(L.nobs, max_slots, L.smem_hist, nops, codes)) {
+        // not a program the build instantiated: compiled for this fit now (NVRTC, cached), so that
+        // the steps never wait for it
+        L.prog_nops = nops;
+        L.prog_codes = codes;
+        L.jit = true;
+      }
     }
   }
   // work units: chunks of rows_per_stage rows (fast) or block-tiles of BIN_WARPS warp-tiles
@@ -389,7 +400,11 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_p2p_form = (force_generic >> 3) & 3;
   g_no_group = (force_generic >> 5) & 1;
   g_no_pdl = (force_generic >> 6) & 1;
+  g_no_jit = (force_generic >> 7) & 1;
   return SXMC_OK;
+}
+int sxmc_jit_compile_check(int nobs, int nslots, int smem_hist, int nops, unsigned codes, size_t* cubin_bytes_out) {
+  return jit_compile_check(nobs, nslots, smem_hist, nops, codes, cubin_bytes_out);
 }
 int sxmc_nll_debug_stamps(int enable, unsigned long long* out1202x8) {
   static unsigned long long* dev = nullptr;
@@ -1517,6 +1532,13 @@ int sxmc_chain_loop_ms(sxmc_chain* c, float* ms_out) { *ms_out = c->loop_ms; ret
 int sxmc_chain_launches(sxmc_chain* c, long* launches_out) { *launches_out = c->launches; return SXMC_OK; }
 int sxmc_chain_last_path(sxmc_chain* c, int* path_out) { *path_out = c->last_path; return SXMC_OK; }
 int sxmc_chain_last_comm_ms(sxmc_chain* c, float* ms_out) { *ms_out = c->last_comm_ms; return SXMC_OK; }
+int sxmc_chain_bin_kernel_kind(sxmc_chain* c, int* kind_out) {
+  if (!c || !kind_out) SXMC_INVAL("sxmc_chain_bin_kernel_kind: NULL argument");
+  if (!c->have_data) { set_error("sxmc_chain_bin_kernel_kind: no data set (the launch is planned with the data)"); return SXMC_ESTATE; }
+  const BinLaunch& L = c->batch[0].launch;
+  *kind_out = !L.fast ? 0 : (L.prog_nops < 0 ? 1 : (L.jit ? 3 : 2));
+  return SXMC_OK;
+}
 
 int sxmc_chain_read_trace(sxmc_chain* c, double* nll_trace_out, double* proposed_out, unsigned nsteps) {
   if (!c->nll_trace_dev || nsteps > c->trace_steps) { set_error("trace was not enabled for that many steps"); return SXMC_ESTATE; }

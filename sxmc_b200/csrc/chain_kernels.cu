@@ -162,7 +162,7 @@ chain_persistent_kernel(const __grid_constant__ FastParams P, const __grid_const
         const int rb = s_rb[j][i];
         float v = 0.0f;
         if (rb >= 0 && rb < tnb) {
-          v = (float)((double)__ldcg(hb + (size_t)j * tnb + rb) / s_bn[j]);   // pdfz.cpp:429-432
+          v = pdf_value(__ldcg(hb + (size_t)j * tnb + rb), s_bn[j]);          // pdfz.cpp:429-432
           if (isnan(v)) v = 0.0f;                                            // nll_kernels.cpp:107
         }
         acc = __dadd_rn(acc, __dmul_rn(s_c[j], (double)v));
@@ -256,8 +256,8 @@ int launch_chain_persistent(const BinLaunch& L0, const PersistParams& Q, cudaStr
   }
   PersistKernel fk = nullptr;
   for (const PersistEntry& e : g_persist_table)
-    if (e.nobs == L.nobs && e.ns == L.nslots && e.nops == L.prog_nops &&
-        (L.prog_nops <= 0 || e.codes == L.prog_codes))
+    if (e.nobs == L.nobs && e.ns == L.nslots && e.nops == (L.jit ? -1 : L.prog_nops) &&      // (a program compiled
+        (L.jit || L.prog_nops <= 0 || e.codes == L.prog_codes))                              // by NVRTC exists for bin_fast_kernel only)
       fk = e.k[L.smem_hist ? 1 : 0];
   if (!fk) { set_error("persistent chain kernel: no instantiation for this shape"); return SXMC_ESTATE; }
   FastParams P;

@@ -1,10 +1,27 @@
 // common.cuh -- shared device-side structures of libsxmc_b200 (sm_100a only).
 #pragma once
+#ifdef __CUDACC_RTC__
+// NVRTC translation unit (jit.cu compiles bin_fast_kernel for a fit's own systematic program at run
+// time): no host headers there.  The limits of include/sxmc_b200.h restated -- the normal build
+// below checks that the two stay in step.
+#define SXMC_SYST_SHIFT 0
+#define SXMC_SYST_SCALE 1
+#define SXMC_SYST_RESOLUTION_SCALE 2
+#define SXMC_SYST_CTSCALE 3
+#define SXMC_MAX_NFIELDS 10
+#define SXMC_MAX_SYST 8
+#define SXMC_MAX_NPARS 4
+#define SXMC_MAX_PARAMETERS 256
+#else
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
 
 #include "../../include/sxmc_b200.h"
+static_assert(SXMC_SYST_SHIFT == 0 && SXMC_SYST_SCALE == 1 && SXMC_SYST_RESOLUTION_SCALE == 2 && SXMC_SYST_CTSCALE == 3 &&
+                  SXMC_MAX_NFIELDS == 10 && SXMC_MAX_SYST == 8 && SXMC_MAX_NPARS == 4 && SXMC_MAX_PARAMETERS == 256,
+              "common.cuh: the NVRTC block above restates these");
+#endif
 
 namespace sxmc {
 
@@ -255,6 +272,15 @@ struct ContourLevels {
 
 enum NllMode { NLL_MODE_STEP = 0, NLL_MODE_INIT = 1, NLL_MODE_EVAL_ONLY = 2 };
 
+// eval_pdf's value, (float)(count / (norm * bin_volume)) (src/pdfz.cpp:429-432).  A zero count is the
+// common case (a signal occupies a fraction of the bins), and a zero numerator sends CUDA's double
+// division down its out-of-line slow path (ncu: 7 calls per warp in workload D's lookup): answer it
+// directly -- 0 / bn is 0 for every bn except 0 and NaN, where it is NaN, as the division gives.
+__device__ __forceinline__ float pdf_value(unsigned count, double bn) {
+  if (count == 0u) return (bn == 0.0 || bn != bn) ? __int_as_float(0x7fc00000) : 0.0f;
+  return (float)((double)count / bn);
+}
+
 // ---- programmatic dependent launch ---------------------------------------------------------
 // A kernel launched with `pdl` may start while its predecessor in the stream is still running:
 // everything it does before pdl_wait() must not depend on (or disturb) the predecessor; pdl_wait()
@@ -264,6 +290,7 @@ enum NllMode { NLL_MODE_STEP = 0, NLL_MODE_INIT = 1, NLL_MODE_EVAL_ONLY = 2 };
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+#ifndef __CUDACC_RTC__
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_kernel_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                      cudaStream_t stream, bool pdl, Args... args) {
@@ -280,6 +307,9 @@ inline cudaError_t launch_kernel_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+#endif
+
+#ifndef __CUDACC_RTC__
 // error plumbing --------------------------------------------------------------------------
 void set_error(const std::string& msg);
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
@@ -289,5 +319,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
     cudaError_t _e = (expr);                                                  \
     if (_e != cudaSuccess) return ::sxmc::cuda_fail(_e, #expr, __FILE__, __LINE__); \
   } while (0)
+
+#endif
 
 }  // namespace sxmc

@@ -23,6 +23,7 @@ struct BinLaunch {
   int max_total_nbins;
   int blocks_per_sm;         // <=0: occupancy maximum (generic kernel)
   bool pdl;                  // fast kernel: programmatic dependent launch on the previous kernel of the stream
+  bool jit;                  // the program has no instantiation in the build: NVRTC-compiled kernel (jit.cu)
   int prog_nops;                 // >= 0: compile-time systematic program, < 0: run-time dispatch
   unsigned prog_codes;
   int rows_per_stage, nstages;   // fast kernel pipeline shape
@@ -55,6 +56,10 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
 // chain_kernels.cu
 int launch_chain_persistent(const BinLaunch& L, const PersistParams& Q, cudaStream_t stream);
 int launch_bin(const BinLaunch& L, cudaStream_t stream);
+// ---- jit.cu: bin_fast_kernel NVRTC-compiled for a program outside the build's table
+void* jit_bin_fast_kernel(int nobs, int ns, bool smem, int nops, unsigned codes);   // nullptr: not available
+int jit_launch_bin(void* fn, unsigned grid, size_t smem_bytes, cudaStream_t stream, bool pdl, const FastParams& P);
+int jit_compile_check(int nobs, int ns, int smem, int nops, unsigned codes, size_t* cubin_bytes_out);
 void set_bin_xdbg(unsigned long long* dev);   // [256][32] stamps of the next fast launches, or NULL
 int launch_zero_jobs(const BinJob* jobs_dev, int njobs, cudaStream_t stream);
 int prepare_layout(const float* aos_dev, unsigned long long n, int nfields, int nobs,

@@ -119,7 +119,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
 #pragma unroll
         for (int q = 0; q < LW; ++q) {
           if (j0 + q < ns) {
-            float v = (float)((double)h[q] / s_bn[j0 + q]);           // pdfz.cpp:429-432
+            float v = pdf_value(h[q], s_bn[j0 + q]);                         // pdfz.cpp:429-432
             if (isnan(v)) v = 0.0f;                                   // nll_kernels.cpp:107
             s = __dadd_rn(s, __dmul_rn(s_c[j0 + q], (double)v));
           }
@@ -193,7 +193,7 @@ lookup_nll_kernel(const NllSignal* __restrict__ sigs, const unsigned* __restrict
       if (rb >= s_nb[j]) {
         // one-past-the-end index of a point within an ulp of `upper`: undefined in the reference
       } else if (rb >= 0) {
-        v = (float)((double)s_bins[j][rb] / s_bn[j]);               // pdfz.cpp:429-432
+        v = pdf_value(s_bins[j][rb], s_bn[j]);                      // pdfz.cpp:429-432
         vlut = v;
         if (isnan(v)) v = 0.0f;                                     // nll_kernels.cpp:107
       } else if (rb == -1) {
@@ -261,7 +261,7 @@ __global__ void pdf_table_kernel(const NllSignal* __restrict__ sigs, const unsig
   const double bn = __dmul_rn((double)norms[j], sigs[j].bin_volume);        // pdfz.cpp:417
   const unsigned* bins = sigs[j].bins;
   for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += gridDim.x * blockDim.x) {
-    float v = (float)((double)bins[b] / bn);
+    float v = pdf_value(bins[b], bn);
     if (isnan(v)) v = 0.0f;
     table[(size_t)j * nb + b] = (double)v;      // widened here once: no conversion per (event, signal)
   }

@@ -218,6 +218,12 @@ class MCMC:
         _check(lib().sxmc_chain_last_comm_ms(self._c, C.byref(v)))
         return v.value
 
+    def bin_kernel_kind(self):
+        """0 interpreter, 1 run-time dispatch, 2 compile-time program of the build, 3 NVRTC-compiled program"""
+        v = C.c_int(0)
+        _check(lib().sxmc_chain_bin_kernel_kind(self._c, C.byref(v)))
+        return v.value
+
     def last_path(self):
         """1 graph / stream launches, 2 persistent kernel, 4 monotone edge-search kernel"""
         v = C.c_int(0)

@@ -77,3 +77,24 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dp, fn)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt, fn
                 assert "liboracle" not in txt and "libsxmc_ref" not in txt, fn
+
+
+def test_nvrtc_compiles_a_systematic_program_outside_the_table():
+    """jit.cu: bin_fast_kernel instantiated for a program the build does not carry -- compile only, no GPU.
+    codes = 8 bits per systematic: type | slot_obs << 2 | slot_extra << 5 (src/pdfz.h:111-116 types)."""
+    import ctypes as C
+    from sxmc_b200 import _lib
+    L = _lib.lib()
+    SHIFT, SCALE, RES, CT = 0, 1, 2, 3
+    n = C.c_size_t(0)
+    programs = [(3, 3, 1, 2, (SHIFT | 1 << 2) | ((CT | 2 << 2) << 8)),                    # shift(radius), ctscale(costheta)
+                (3, 3, 0, 2, (SHIFT | 1 << 2) | ((CT | 2 << 2) << 8)),                    # ... histograms in global memory
+                (2, 3, 1, 4, SCALE | ((RES | 2 << 5) << 8) | ((SHIFT | 1 << 2) << 16) | ((SCALE | 1 << 2) << 24)),
+                (1, 1, 1, 1, CT)]
+    for nobs, ns, smem, nops, codes in programs:
+        rc = L.sxmc_jit_compile_check(nobs, ns, smem, nops, codes, C.byref(n))
+        assert rc == 0, L.sxmc_last_error().decode()
+        assert n.value > 20000
+    # a program that addresses a slot the kernel does not load must not compile (static_assert in apply_static)
+    rc = L.sxmc_jit_compile_check(1, 1, 1, 1, RES | 0 << 2 | 3 << 5, C.byref(n))
+    assert rc != 0 and "NVRTC could not compile" in L.sxmc_last_error().decode()

@@ -317,6 +317,52 @@ def test_ctscale_and_polynomial_systematics_against_reference_output(name):
         h.close()
 
 
+@pytest.mark.parametrize("case", ["D_shift_ctscale", "C_four_ops", "B_ctscale"])
+def test_programs_outside_the_build_table_run_nvrtc_compiled_and_bit_exact(case):
+    """A fit whose systematic program the build did not instantiate gets bin_fast_kernel compiled for it by
+    NVRTC (jit.cu): bins, norms, lut bit-exact against the oracle, the same through the run-time dispatching
+    kernel (JIT switched off), and a short chain identical between the two."""
+    from sxmc_b200 import mcmc, pdfz
+    if case == "D_shift_ctscale":
+        fit = W.config_D(0.01)
+        fit.systematics = [W.SystSpec(type=W.SHIFT, obs=1, means=[0.0], sigmas=[0.01]),
+                           W.SystSpec(type=W.CTSCALE, obs=2, means=[0.0], sigmas=[0.01])]
+    elif case == "C_four_ops":
+        fit = W.config_C(0.01)
+        fit.systematics = [W.SystSpec(type=W.SCALE, obs=0, means=[0.0], sigmas=[0.01]),
+                           W.SystSpec(type=W.RESOLUTION_SCALE, obs=0, extra=2, means=[0.0], sigmas=[0.001]),
+                           W.SystSpec(type=W.SHIFT, obs=1, means=[0.0], sigmas=[0.01]),
+                           W.SystSpec(type=W.SCALE, obs=1, means=[0.0], sigmas=[0.01])]
+    else:
+        fit = W.config_B(0.05)
+        fit.systematics = [W.SystSpec(type=W.CTSCALE, obs=0, means=[0.0], sigmas=[0.01])]
+    fit.finalize()
+    for sig in fit.signals:
+        sig.systematics = list(range(len(fit.systematics)))
+    out = {}
+    for jit in (True, False):
+        pdfz.set_bin_tuning(no_jit=not jit)
+        hists, chain = mcmc.build_fit(fit)
+        chain.set_data(fit.data)
+        assert chain.bin_kernel_kind() == (3 if jit else 1)
+        for seed in (1, 2):
+            pars = _pars(fit, seed)
+            nll, ev = chain.nll(pars)
+            bins, norms, lut = port.eval_all(fit, pars)
+            want, _ = port.nll(fit, lut, pars, norms)
+            assert np.array_equal(chain.bins(), bins) and np.array_equal(chain.norms(), norms)
+            assert chain.lut().tobytes() == lut.tobytes()
+            assert abs(nll - want) <= NLL_RTOL * abs(want)
+        chain.set_seed(7, 0)
+        chain.set_mode(1)
+        out[jit] = chain(fit.data, 200, 0.1).get_samples()
+        chain.close()
+        for h in hists:
+            h.close()
+    pdfz.set_bin_tuning()
+    assert out[True].shape[0] > 0 and out[True].tobytes() == out[False].tobytes()
+
+
 def test_pdfz_group_ragged_batch_matches_oracle():
     """29 PDFs from 100 to 3x10^5 samples in ONE batched launch (the reference's pdfz_group
     benchmark shape at 1/10 size): bins, norms and PDF values bit-exact."""

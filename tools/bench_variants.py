@@ -25,6 +25,7 @@ def run(fit, label, steps=20, rounds=5, **tuning):
     chain.set_seed(1, 0)
     chain.begin(fit.data, (rounds + 1) * steps + 8, 0.1)
     chain.advance_timed(4, 0)
+    kind = {0: "interpreter", 1: "run-time dispatch", 2: "compile-time program (build)", 3: "compile-time program (NVRTC)"}[chain.bin_kernel_kind()]
     v = []
     for _ in range(rounds):
         s, b, n = chain.advance_timed(steps, 0)
@@ -37,7 +38,7 @@ def run(fit, label, steps=20, rounds=5, **tuning):
     nbytes = 4 * fit.needed_columns() * fit.total_samples()
     peak, _ = bench.measured_peak()
     med = float(np.median(v))
-    out = {"case": label, "bytes": nbytes, "bin_us": round(med, 2), "gbs": round(nbytes / med / 1e3, 1),
+    out = {"case": label, "kernel": kind, "bytes": nbytes, "bin_us": round(med, 2), "gbs": round(nbytes / med / 1e3, 1),
            "frac": round(nbytes / med / 1e3 / peak, 4), "peak_gbs": peak}
     print(json.dumps(out), flush=True)
 
@@ -58,6 +59,7 @@ def main():
             for sig in other.signals:
                 sig.systematics = [0, 1]
             run(other, "D shape, shift(radius)+ctscale(costheta) [not in the table]")
+            run(other, "D shape, shift(radius)+ctscale(costheta), JIT off", no_jit=True)
         del fit
     run(W.config_D(1.0, stress=True), "D stress 200000 bins (global histograms)")
 
