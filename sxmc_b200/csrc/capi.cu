@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -999,7 +1000,9 @@ int sxmc_chain_create(const sxmc_chain_config* cfg, sxmc_chain** out) {
   if (e == cudaSuccess) e = cudaMalloc(&c->st_dev, sizeof(ChainState));
   if (e == cudaSuccess) e = cudaMallocHost(&c->st_host, sizeof(ChainState));
   for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
-    e = cudaMalloc(&c->hist_buf[b], sizeof(unsigned) * c->hist_words);
+    const size_t padded = (c->hist_words + 31) & ~(size_t)31;     // whole 128-byte lines (staged peer exchange copies uint4)
+    e = cudaMalloc(&c->hist_buf[b], sizeof(unsigned) * padded);
+    if (e == cudaSuccess) e = cudaMemset(c->hist_buf[b], 0, sizeof(unsigned) * padded);
     c->part_buf[b] = c->hist_buf[b];
     c->hist_own[b] = c->hist_buf[b];
     if (e == cudaSuccess) e = cudaMalloc(&c->sigs_dev[b], sizeof(NllSignal) * c->nsignals);
@@ -1486,10 +1489,10 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
       float a = 0, b2 = 0;
       SXMC_CUDA(cudaEventElapsedTime(&a, c->tev[3 * k], c->tev[3 * k + 1]));
       SXMC_CUDA(cudaEventElapsedTime(&b2, c->tev[3 * k + 1], c->tev[3 * k + 2]));
-      t_bin += a; t_nll += b2; t_step += a + b2;
       float cm = 0;     // binning kernel end -> all-reduce end (0 without a communicator)
       SXMC_CUDA(cudaEventElapsedTime(&cm, c->tev[3 * CHUNK + k], c->tev[3 * k + 1]));
       t_comm += cm;
+      t_bin += a - cm; t_nll += b2; t_step += a + b2;      // bin = the binning launch alone
     }
     left -= n;
   }
