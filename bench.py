@@ -454,6 +454,9 @@ def build_chain(fit, args, rank, world, local, exchange):
     fit_local = fit
     if exchange is not None and world > 1:
         fit_local = sharding.shard_fit_samples(fit, rank, world)
+    if exchange == "p2p":                # handles copy the knobs when they are created
+        from sxmc_b200 import pdfz
+        pdfz.set_bin_tuning(p2p_form=args.p2p_form)
     hists, chain = mcmc.build_fit(fit_local)
     if exchange is not None and world > 1:
         comm = attach_exchange(chain, exchange, args, rank, world, local)
@@ -466,7 +469,6 @@ def build_chain(fit, args, rank, world, local, exchange):
 def attach_exchange(chain, exchange, args, rank, world, local):
     from sxmc_b200 import pdfz, sharding
     if exchange == "p2p":
-        pdfz.set_bin_tuning(p2p_form=args.p2p_form)
         sharding.connect_p2p(chain, rank, world)
         return "p2p"
     comm = sharding.Comm(device=local)
@@ -675,7 +677,8 @@ def run_own_arm(args, rank, world, local):
         other = "nccl" if args.exchange == "p2p" else "p2p"
         try:
             close_chain(chain, comm)
-            from sxmc_b200 import mcmc
+            from sxmc_b200 import mcmc, pdfz
+            pdfz.set_bin_tuning(p2p_form=args.p2p_form)
             _, chain = mcmc.build_fit(fit_local, hists=hists)
             comm = attach_exchange(chain, other, args, rank, world, local)
             r2 = measure_chain(fit, fit_local, hists, chain, args, rank, comm, flush, do_e2e=False,

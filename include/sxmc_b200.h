@@ -110,7 +110,9 @@ int sxmc_hist_get_samples(sxmc_hist* h, float* host_out);
  * sort=0 keeps the caller's sample order (used to measure what sorting buys). */
 int sxmc_hist_set_layout(sxmc_hist* h, int sort);
 int sxmc_hist_prepare(sxmc_hist* h);
-/* tuning knobs of the binning launch (EvalHist::OptimizeBin analogue, src/pdfz.cpp:630-727):
+/* tuning knobs of the binning launch (EvalHist::OptimizeBin analogue, src/pdfz.cpp:630-727).  The call
+ * sets the DEFAULTS: every handle (hist, chain, batch) copies them when it is created and keeps them,
+ * so two fits in one process can be tuned independently (set, create, set differently, create).
  * smem_hist_max_bins: histograms up to this many bins are privatised in shared memory;
  * blocks_per_sm <= 0 keeps the default;  kernel_select: 0 = automatic, bit 0 = force the
  * generic (interpreting) kernel, bit 1 = force run-time systematic dispatch in the fast
@@ -125,7 +127,7 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_se
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */
 int sxmc_enable_kernel_timing(int on);
-int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);
+int sxmc_last_kernel_ms(float* bin_ms, float* nll_ms);            /* of whichever chain was timed last */
 /* Profiling hook of the fast binning kernel (no reference counterpart): while enabled every
  * launch writes [grid <= 256][32] %globaltimer stamps (ns) per CTA -- 0 entry, 1 pipeline
  * initialised, 2 first data arrived, 3 = number of segments, 4+3s+{0,1,2} parameters resolved /
@@ -217,6 +219,9 @@ int sxmc_chain_last_comm_ms(sxmc_chain* c, float* ms_out);
  * (multi-coefficient systematics, > 3 observables), 1 fast kernel with run-time dispatch of the systematics,
  * 2 fast kernel with a compile-time program of the build's table, 3 the same compiled for this fit by NVRTC */
 int sxmc_chain_bin_kernel_kind(sxmc_chain* c, int* kind_out);
+/* device time (ms) of THIS chain's last evaluate-only pass (sxmc_chain_nll_at) while
+ * sxmc_enable_kernel_timing is on; -1 before the first */
+int sxmc_chain_last_kernel_ms(sxmc_chain* c, float* bin_ms, float* nll_ms);
 /* the ntuple rows: nparameters+1 floats each (src/nll_kernels.cpp:78-84) */
 int sxmc_chain_read(sxmc_chain* c, float* rows_out, long max_rows);
 int sxmc_chain_accepted(sxmc_chain* c, long* accepted_out);

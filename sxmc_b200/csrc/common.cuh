@@ -199,6 +199,7 @@ struct P2PParams {
   int parity;
   int nranks, rank;
   int twoshot;                           // reduce-scatter + all-gather (nranks > 2)
+  unsigned long long peer_timeout_ns;    // wall-clock bound of a wait for the other ranks (they are other processes)
 };
 
 // One signal as seen by the lookup + event-likelihood kernel.

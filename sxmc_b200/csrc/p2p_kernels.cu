@@ -35,13 +35,15 @@ __device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
 
 // Spin until every peer's flag in this rank's own flag row `base` has reached `seq`.
 __device__ __forceinline__ int wait_peers(const P2PParams& W, const unsigned* base, unsigned seq) {
-  const long long t0 = clock64();
+  // The peers are other host processes: their skew (a GIL stall, a lazy module load, a graph
+  // instantiation) is bounded in wall-clock time, far above the grid barriers' cycle budget.
+  const unsigned long long t0 = globaltimer_ns();
   for (int p = 0; p < W.nranks; ++p) {
     unsigned n = 0;
     while ((int)(ld_acquire_sys_u32(base + p) - seq) < 0) {
       if ((++n & 63u) == 0) {
         if (*(volatile unsigned*)W.abort_flag) return 0;
-        if (clock64() - t0 > PK_TIMEOUT_CYCLES) { atomicExch(W.abort_flag, 1u); return 0; }
+        if (globaltimer_ns() - t0 > W.peer_timeout_ns) { atomicExch(W.abort_flag, 1u); return 0; }
       }
     }
   }

@@ -165,6 +165,31 @@ def test_chain_eval_matches_oracle(name, scale, variant):
     pdfz.set_bin_tuning(8192, 0, False)
 
 
+def test_two_fits_in_one_process_keep_their_own_tuning():
+    """The kernel-selection knobs are defaults that a handle copies when it is created: three chains
+    over the same fit, created under three settings, keep three different kernels side by side (and
+    agree on every histogram)."""
+    from sxmc_b200 import mcmc, pdfz
+    fit = W.config_C(0.003)
+    chains = []
+    for kw in (dict(), dict(force_dynamic=True), dict(force_generic=True)):
+        pdfz.set_bin_tuning(**kw)
+        chains.append(mcmc.build_fit(fit))
+    pdfz.set_bin_tuning()
+    pars = _pars(fit, 4)
+    outs = []
+    for hists, chain in chains:              # used only now, after the defaults went back to normal
+        chain.set_data(fit.data)
+        chain.nll(pars)
+        outs.append((chain.bin_kernel_kind(), chain.bins(), chain.norms()))
+    assert [o[0] for o in outs] == [2, 1, 0]
+    assert all(np.array_equal(o[1], outs[0][1]) and np.array_equal(o[2], outs[0][2]) for o in outs)
+    for hists, chain in chains:
+        chain.close()
+        for h in hists:
+            h.close()
+
+
 def test_unsorted_layout_gives_identical_histograms():
     from sxmc_b200 import mcmc
     fit = W.config_C(0.003)

@@ -20,19 +20,24 @@ def main():
     from sxmc_b200 import _lib, mcmc, pdfz, workloads
     _lib.check(_lib.lib().sxmc_init(0))
     fit = workloads.WORKLOADS[a.workload](1.0)
-    hists, chain = mcmc.build_fit(fit)
-    chain.set_seed(1, 0)
-    chain.begin(fit.data, (2 * a.rounds + 2) * a.steps + 8, 0.1)
-    chain.advance(a.steps)
+    # two chains over the same PDFs: a handle keeps the knobs it was created with
+    hists, chain_pdl = mcmc.build_fit(fit)
+    pdfz.set_bin_tuning(no_pdl=True)
+    _, chain_off = mcmc.build_fit(fit, hists=hists)
+    pdfz.set_bin_tuning()
+    chains = {"pdl": chain_pdl, "no pdl": chain_off}
+    for c in chains.values():
+        c.set_seed(1, 0)
+        c.begin(fit.data, (a.rounds + 2) * a.steps + 8, 0.1)
+        c.advance(a.steps)
     res = {"pdl": [], "no pdl": []}
     for _ in range(a.rounds):
-        for name, off in (("pdl", False), ("no pdl", True)):
-            pdfz.set_bin_tuning(no_pdl=off)
-            ms0 = chain.loop_ms()
-            chain.advance(a.steps)
-            res[name].append(1e3 * (chain.loop_ms() - ms0) / a.steps)
-    pdfz.set_bin_tuning()
-    chain.end()
+        for name, c in chains.items():
+            ms0 = c.loop_ms()
+            c.advance(a.steps)
+            res[name].append(1e3 * (c.loop_ms() - ms0) / a.steps)
+    for c in chains.values():
+        c.end()
     for name, v in res.items():
         print("%s %-7s us per step: median %7.2f  min %7.2f  max %7.2f" % (fit.name, name, np.median(v), min(v), max(v)))
 
