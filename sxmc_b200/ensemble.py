@@ -321,17 +321,22 @@ def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps
     delta = contour_delta(confidence)
     t_all = time.perf_counter()
     if batch > 1 and mine:
+        tb = time.perf_counter()
         hists, mb = mcmc.build_fit(fit, batch=min(int(batch), 148))
         gen = FakeDataGenerator(*_fit_objects(fit, hists))
+        out["phases_s"] = {"build": time.perf_counter() - tb, "generate": 0.0, "run": 0.0, "limits": 0.0}
         try:
             k = mb.parameter_names.index(signal_name) if signal_name in mb.parameter_names[:-1] else -1
             for c0 in range(0, len(mine), mb.max_chains):
                 group = mine[c0:c0 + mb.max_chains]
                 obs = []
+                tg = time.perf_counter()
                 for slot, i in enumerate(group):
                     obs.append(mb.generate_data(slot, gen, True, seed, i))   # make_fake_dataset(..., true)
                     mb.set_seed(slot, seed, i)
+                tr = time.perf_counter()
                 mb.run(len(group), nsteps, burnin, bool(debug_mode))                           # MCMC::operator() x len(group)
+                tl = time.perf_counter()
                 out["loop_ms"] += mb.loop_ms()
                 out["launches"] += 1
                 for slot, i in enumerate(group):
@@ -340,6 +345,10 @@ def ensemble(fit, nexperiments, signal_name="s0", confidence=0.9, seed=0, nsteps
                     out["observed"].append(obs[slot])
                     if keep_chains:
                         out["chains"].append(mb.rows(slot))
+                te = time.perf_counter()
+                out["phases_s"]["generate"] += tr - tg
+                out["phases_s"]["run"] += tl - tr
+                out["phases_s"]["limits"] += te - tl
             out["mode"] = "batch"
             out["seconds"] = time.perf_counter() - t_all
             return out
