@@ -20,13 +20,14 @@ sample columns streamed per step) -- the largest BASELINE configuration that fit
 
 Own arm (`--impl b200`, default):
   value  MCMC steps/s with everything resident in HBM.  The K-step block is repeated
-         `repeats` times (a 20-step block of D lasts 7 ms: one block is at the mercy of a single
-         host hiccup); every step of a block is timed by CUDA events on the chain's stream
-         (kernel by kernel: bin | exchange | lookup+NLL+Metropolis); block time = sum of its
-         steps; value = K / (max over ranks of the MEDIAN block).  The per-rank min / median /
-         max block is printed so a straggler is visible.  L2: C and D stream 10x the L2 per
-         step (no flush needed, none done); A/B/E-sized fits get a 256 MiB memset before each
-         step, outside the intervals.
+         `repeats` times (a 20-step block of D lasts 6 ms: one block is at the mercy of a single
+         host hiccup); value = K / (max over ranks of the MEDIAN block); the per-rank min /
+         median / max block is printed so a straggler is visible.  C and D stream 10x the L2 per
+         step (no flush applies, none done): a block is K steps issued back to back the way a
+         fit runs them (sxmc_chain_advance), one CUDA-event interval on the chain's stream
+         around it; kernels_ms_per_step and the roofline come from a second pass with an event
+         around every kernel (bin | exchange | lookup+NLL+Metropolis).  A/B/E-sized fits are
+         timed step by step with a 256 MiB memset before each step, outside the intervals.
   e2e    the same metric through the public call a user makes -- MCMC.__call__
          (sxmc_chain_run + sxmc_chain_read over the C ABI) with HOST buffers: upload of the
          data events, SetEvalPoints, initial evaluation, graph capture, the K-step loop and
