@@ -14,10 +14,11 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--stress", action="store_true", help="workload D with 100 x 50 x 40 = 200 000 bins")
     a = ap.parse_args()
     from sxmc_b200 import _lib, mcmc, workloads
     _lib.check(_lib.lib().sxmc_init(0))
-    fit = workloads.WORKLOADS[a.workload](a.scale)
+    fit = workloads.config_D(a.scale, stress=True) if a.stress else workloads.WORKLOADS[a.workload](a.scale)
     hists, chain = mcmc.build_fit(fit)
     chain.set_seed(1, 0)
     chain.begin(fit.data, a.steps, 0.1)
