@@ -120,9 +120,12 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * path, bits 3-4 = form of the peer-memory all-reduce (0 automatic: two-shot above two ranks,
  * 1 one-shot, 2 two-shot), bit 5 = chains set up from now on look events up one by one even when
  * every signal reads the same dataset (the multi-dataset form), bit 6 = chain steps are launched
- * without programmatic dependent launch, bit 7 = no run-time compilation of systematic programs (below)
- * -- used by the parity tests and
- * measurements to cover every path. */
+ * without programmatic dependent launch, bit 7 = no run-time compilation of systematic programs (below),
+ * bits 8-9 = how the fast binning kernel deals its chunks (0 production: a CTA's range dealt to its
+ * warps round robin, global-memory histograms with warps independent of each other; 1 one contiguous
+ * range per warp inside per-CTA segments; 2 global histograms, one contiguous range per warp of the
+ * grid; 3 global histograms by per-CTA segments) -- used by the parity tests and measurements to
+ * cover every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */

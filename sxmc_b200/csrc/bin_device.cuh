@@ -254,7 +254,9 @@ __device__ __forceinline__ float4 lds128(unsigned addr) {
 
 // One persistent CTA per SM, FAST_WARPS warps.  Work unit = a "chunk": R consecutive rows
 // (R x 512 B per column) of a warp-tile.  The chunk sequence of all jobs is cut evenly over
-// the CTAs; inside a CTA each job segment is cut into one CONTIGUOUS chunk range per warp.
+// the CTAs; inside a CTA each job segment is dealt to the warps round robin (one contiguous range
+// per warp measured 7 % slower on workload C: the CTA's copies in flight then read 16 distant
+// addresses per column instead of neighbouring ones).
 // Every warp runs its own S-stage pipeline: lane 0 issues one bulk async copy (TMA unit)
 // per column per chunk into the warp's private shared-memory stages, completion is signalled
 // on a per-stage mbarrier, and the warp consumes the stage with conflict-free LDS.128 --
@@ -364,10 +366,12 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
 #pragma unroll
     for (int c = 0; c < NS; ++c) col[c] = reinterpret_cast<const unsigned char*>(job.col[c]);
 
-    // this warp's contiguous chunk range [ca, cb) of the job (chunk c starts at byte c * col_bytes)
+    // this warp's chunks ca, ca + cstep, ... < cb of the job (chunk c starts at byte c * col_bytes)
     const unsigned long long n = tend - t0;
-    const unsigned long long ca = (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
-    const unsigned long long cb = (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
+    const bool rr = P.cta_split != 1;   // chunks dealt to the warps round robin (1: contiguous, measurement)
+    const unsigned cstep = rr ? FAST_WARPS : 1u;
+    const unsigned long long ca = rr ? (t0 - jbeg) + (unsigned)warp : (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
+    const unsigned long long cb = rr ? (tend - jbeg) : (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
 
     auto issue = [&](unsigned long long c, unsigned slot) {   // lane 0 only
       const unsigned bar = my_bar0 + 8u * slot;
@@ -379,7 +383,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     // first thing in the segment: get the copies going (everything they need is in the
     // constant bank); the parameter loads and the histogram clear overlap with them
     if (lane == 0 && !reuse)
-      for (unsigned i = 0; i < (unsigned)S && ca + i < cb; ++i) issue(ca + i, (it + i) % (unsigned)S);
+      for (unsigned i = 0; i < (unsigned)S && ca + i * cstep < cb; ++i) issue(ca + i * cstep, (it + i) % (unsigned)S);
 
     // Programmatic dependent launch: everything above (barriers, the first bulk copies of the
     // sample columns) ran while the previous kernel of the stream -- the step before's lookup --
@@ -421,7 +425,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     acc.cur = -1;
     acc.cnt = 0;
 #pragma unroll 1
-    for (unsigned long long c = ca; c < cb; ++c, ++it) {
+    for (unsigned long long c = ca; c < cb; c += cstep, ++it) {
       const unsigned slot = it % (unsigned)S;
       mbar_wait(my_bar0 + 8u * slot, (it / (unsigned)S) & 1u);
       if (xseg == 0 && c == ca) BIN_XDBG(2, threadIdx.x == 0);
@@ -455,7 +459,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
         run_push4<SMEM>(acc, bq, hist, geo.total_nbins);
       }
       __syncwarp();                       // every lane has read the stage before it is refilled
-      if (lane == 0 && !reuse && c + (unsigned)S < cb) issue(c + (unsigned)S, slot);
+      if (lane == 0 && !reuse && c + (unsigned)S * cstep < cb) issue(c + (unsigned)S * cstep, slot);
     }
     run_flush<SMEM>(acc, hist, geo.total_nbins);
     BIN_DBG(2);
@@ -490,6 +494,156 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
   cx.loaded = true;
 }
 
+// The same pass for launches whose histograms live in GLOBAL memory (more bins than fit beside the
+// pipeline stages: workload D's 25 000, the 200 000-bin stress case).  Without a shared-memory
+// histogram nothing ties a CTA to one signal at a time, so no warp ever waits for another: the
+// concatenated chunk sequence of all signals is cut evenly over the CTAs, a CTA's range is dealt to
+// its 16 warps round robin, and every warp streams its chunks through its own pipeline -- across
+// signal boundaries without draining (flush the run, one atomic for the in-domain count, resolve
+// the next signal's parameters by shuffle).  No CTA-wide barrier, no segment switch, no
+// whole-CTAs-per-signal imbalance: the 1/8 shard of workload D bins in 59 us instead of 66
+// (profiles/r02_bin_split_ab.txt).
+template <int NOBS, int NS, int NOPS, unsigned CODES>
+__device__ __forceinline__ void fast_bin_pass_warp(const FastParams& P, const FastCtx& cx) {
+  const Geo& geo = P.geo;
+  const int R = P.R, S = P.S;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned col_bytes = (unsigned)R * 512u, stage_bytes = NS * col_bytes;
+  const unsigned my_stage0 = cx.my_stage0, my_bar0 = cx.my_bar0;
+  unsigned long long* const xd = P.xdbg ? P.xdbg + 32ull * blockIdx.x : nullptr;
+  const unsigned long long total = P.prefix[P.njobs];
+  // the CTA takes a contiguous range and deals its chunks to the warps round robin: its 16 x S copies
+  // in flight read neighbouring addresses of the same columns (measurement knob cta_split = 2: one
+  // contiguous range per warp of the grid -- 3-5 % slower on workload D)
+  unsigned long long t0, t1;
+  unsigned tstep;
+  if (P.cta_split == 0) {
+    t0 = total * blockIdx.x / gridDim.x + (unsigned)warp;
+    t1 = total * (blockIdx.x + 1ull) / gridDim.x;
+    tstep = FAST_WARPS;
+  } else {
+    const unsigned long long nw = (unsigned long long)gridDim.x * FAST_WARPS, w = (unsigned long long)blockIdx.x * FAST_WARPS + warp;
+    t0 = total * w / nw;
+    t1 = total * (w + 1ull) / nw;
+    tstep = 1;
+  }
+  if (t0 >= t1) { pdl_wait(); pdl_trigger(); return; }
+
+  // issue cursor (lane 0 only): chunk index, end of its signal, the chunk's address in every column
+  unsigned long long ti = t0, ji_end = 0;
+  int ji = 0;
+  const unsigned char* icol[NS];
+  const unsigned long long step_bytes = (unsigned long long)tstep * col_bytes;
+  auto issue = [&](unsigned slot) {
+    if (ti >= ji_end) {
+      while (P.prefix[ji + 1] <= ti) ++ji;
+      ji_end = P.prefix[ji + 1];
+      const unsigned long long off = (ti - P.prefix[ji]) * col_bytes;
+#pragma unroll
+      for (int k = 0; k < NS; ++k) icol[k] = reinterpret_cast<const unsigned char*>(P.job[ji].col[k]) + off;
+    }
+    const unsigned bar = my_bar0 + 8u * slot;
+    const unsigned dst = my_stage0 + slot * stage_bytes;
+    mbar_expect_tx(bar, stage_bytes);
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+      bulk_g2s(dst + k * col_bytes, icol[k], col_bytes, bar);
+      icol[k] += step_bytes;
+    }
+    ti += tstep;
+  };
+  if (lane == 0)
+    for (int i = 0; i < S && ti < t1; ++i) issue((unsigned)i);
+  // the sample columns never depend on the previous kernel of the stream; the parameters do
+  pdl_wait();
+  pdl_trigger();
+
+  int jc = -1;
+  unsigned long long jc_end = 0;
+  int op_code[FAST_MAX_OPS];
+  double op_c0[FAST_MAX_OPS], op_onep[FAST_MAX_OPS];
+  int nsyst = 0;
+  unsigned* gbins = nullptr;
+  RunAcc acc;
+  acc.norm = 0; acc.cur = -1; acc.cnt = 0;
+  auto close_job = [&]() {
+    run_flush<false>(acc, gbins, geo.total_nbins);
+    const unsigned wnorm = __reduce_add_sync(0xffffffffu, acc.norm);
+    if (lane == 0 && wnorm) atomicAdd(P.job[jc].norm, wnorm);
+    acc.norm = 0; acc.cur = -1; acc.cnt = 0;
+  };
+  unsigned it = 0;
+#pragma unroll 1
+  for (unsigned long long tc = t0; tc < t1; tc += tstep, ++it) {
+    if (tc >= jc_end) {                                // this warp enters a (new) signal
+      if (jc >= 0) close_job();
+      jc = jc < 0 ? 0 : jc + 1;
+      while (P.prefix[jc + 1] <= tc) ++jc;
+      jc_end = P.prefix[jc + 1];
+      const FastJob& job = P.job[jc];
+      nsyst = job.nsyst;
+      // p = 0 + par * pow(x, 0) (src/pdfz.cpp:310-314): lane k resolves systematic k, then broadcast
+      double c0 = 0.0;
+      if (lane < nsyst && lane < FAST_MAX_OPS) {
+        const double par = job.npars[lane] ? job.params[(long long)job.pidx[lane] * job.param_stride] : 0.0;
+        c0 = __dadd_rn(0.0, __dmul_rn(par, 1.0));
+      }
+#pragma unroll
+      for (int k = 0; k < FAST_MAX_OPS; ++k) {
+        op_code[k] = job.code[k];
+        op_c0[k] = __shfl_sync(0xffffffffu, c0, k);
+        op_onep[k] = __dadd_rn(1.0, op_c0[k]);
+      }
+      gbins = job.bins;
+    }
+    const unsigned slot = it % (unsigned)S;
+    mbar_wait(my_bar0 + 8u * slot, (it / (unsigned)S) & 1u);
+    if (xd && it == 0 && threadIdx.x == 0) {
+      unsigned long long t_;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+      xd[2] = t_;
+    }
+    const unsigned src = my_stage0 + slot * stage_bytes + (unsigned)lane * 16u;
+#pragma unroll 1
+    for (int r = 0; r < R; ++r) {
+      double f[NS][4];
+#pragma unroll
+      for (int k = 0; k < NS; ++k) {
+        const float4 v = lds128(src + k * col_bytes + r * 512u);
+        f[k][0] = (double)v.x; f[k][1] = (double)v.y; f[k][2] = (double)v.z; f[k][3] = (double)v.w;
+      }
+      if constexpr (NOPS < 0) {
+#pragma unroll
+        for (int k = 0; k < FAST_MAX_OPS; ++k)
+          if (k < nsyst) apply_op<NS>(f, op_code[k], op_c0[k], op_onep[k]);
+      } else {
+        if constexpr (NOPS > 0) apply_static<NS, (CODES >> 0) & 255>(f, op_c0[0], op_onep[0]);
+        if constexpr (NOPS > 1) apply_static<NS, (CODES >> 8) & 255>(f, op_c0[1], op_onep[1]);
+        if constexpr (NOPS > 2) apply_static<NS, (CODES >> 16) & 255>(f, op_c0[2], op_onep[2]);
+        if constexpr (NOPS > 3) apply_static<NS, (CODES >> 24) & 255>(f, op_c0[3], op_onep[3]);
+      }
+      int bq[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        double x[NOBS];
+#pragma unroll
+        for (int o = 0; o < NOBS; ++o) x[o] = f[o][k];
+        bq[k] = flat_bin<NOBS>(x, geo);
+      }
+      run_push4<false>(acc, bq, gbins, geo.total_nbins);
+    }
+    __syncwarp();                       // every lane has read the stage before it is refilled
+    if (lane == 0 && ti < t1) issue(slot);
+  }
+  close_job();
+  if (xd && lane == 0) {
+    unsigned long long t_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+    xd[16 + warp] = t_;
+    if (warp == 0) xd[3] = 1ull;
+  }
+}
+
 template <int NOBS, int NS, bool SMEM, int NOPS, unsigned CODES>
 __global__ void __launch_bounds__(FAST_THREADS, 1)
 bin_fast_kernel(const __grid_constant__ FastParams P) {
@@ -508,8 +662,13 @@ bin_fast_kernel(const __grid_constant__ FastParams P) {
   }
   FastCtx cx;
   fast_ctx_init<NS>(cx, P, smem_raw, s_bar);
-  fast_bin_pass<NOBS, NS, SMEM, NOPS, CODES>(P, cx, reinterpret_cast<unsigned*>(smem_raw), s_syst,
-                                             &s_norm, nullptr, nullptr);
+  if (SMEM || (P.cta_split & 1)) {   // (1, 3: measurement knobs)
+    fast_bin_pass<NOBS, NS, SMEM, NOPS, CODES>(P, cx, reinterpret_cast<unsigned*>(smem_raw), s_syst,
+                                               &s_norm, nullptr, nullptr);
+  } else {
+    fast_bin_pass_warp<NOBS, NS, NOPS, CODES>(P, cx);
+    __syncthreads();                    // (profiling stamp below: the CTA's last warp)
+  }
   if (P.xdbg && threadIdx.x == 0) {
     unsigned long long t_;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));

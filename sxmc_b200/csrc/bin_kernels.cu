@@ -184,6 +184,7 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
   // Small fits: give every job whole CTAs (no CTA spans two jobs).  Big fits keep the even
   // split, whose balance is perfect and whose second segment costs nothing in proportion.
   P.aligned = 0;
+  P.cta_split = 0;
   int nonempty = 0;
   for (int j = 0; j < ng; ++j) nonempty += P.prefix[j + 1] > P.prefix[j];
   if (total > 0 && nonempty <= grid && total / ((unsigned long long)grid * FAST_WARPS) < 32) {
@@ -240,6 +241,7 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
       if (grid > max_grid) grid = max_grid;
       build_fast_params(L, g0, ng, (int)grid, P, &total);
       P.xdbg = g_bin_xdbg;
+      P.cta_split = L.cta_split;
       const bool pdl = L.pdl && L.njobs <= FAST_MAX_JOBS;
       if (jk) {
         const int rc = jit_launch_bin(jk, (unsigned)grid, L.smem_bytes, stream, pdl, P);

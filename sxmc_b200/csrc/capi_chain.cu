@@ -98,6 +98,7 @@ static int chain_build_tables(sxmc_chain* c) {
 static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr, bool in_step = false) {
   BinLaunch BL = c->batch[b].launch;
   BL.pdl = in_step && !c->tune.no_pdl;
+  BL.cta_split = c->tune.cta_split;
   SXMC_TRY(launch_bin(BL, c->stream));
   c->launches += 1;
   if (after_bin) SXMC_CUDA(cudaEventRecord(after_bin, c->stream));

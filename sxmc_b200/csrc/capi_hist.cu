@@ -162,6 +162,7 @@ void plan_launch(Batch& b, int n, const Tuning& T) {
   L.jobs_dev = b.dev;
   L.prefix_dev = b.prefix_dev;
   L.njobs = n;
+  L.cta_split = T.cta_split;
   bool uniform = true;
   int max_bins = 0, max_slots = 0;
   bool poly = false;
@@ -317,6 +318,7 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_tune.no_group = (force_generic >> 5) & 1;
   g_tune.no_pdl = (force_generic >> 6) & 1;
   g_tune.no_jit = (force_generic >> 7) & 1;
+  g_tune.cta_split = (force_generic >> 8) & 3;
   return SXMC_OK;
 }
 int sxmc_jit_compile_check(int nobs, int nslots, int smem_hist, int nops, unsigned codes, size_t* cubin_bytes_out) {

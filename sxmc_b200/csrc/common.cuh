@@ -117,6 +117,7 @@ struct FastParams {
   // so no CTA pays the per-segment overhead twice; aligned == 0: even split of all chunks
   unsigned short cta_first[FAST_MAX_JOBS + 1];
   int aligned;
+  int cta_split;                // partition form, 0 in production (Tuning::cta_split, capi_internal.h)
   // profiling hook (sxmc_bin_debug_stamps): [grid][32] %globaltimer stamps, NULL in production.
   // Per CTA: 0 entry, 1 pipeline initialised, 2 first data arrived (warp 0), 3 segments done,
   // 4+3s+{0,1,2} of segment s < 4: parameters resolved / warp 0 out of its chunk loop / merged,

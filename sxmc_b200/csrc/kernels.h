@@ -22,6 +22,7 @@ struct BinLaunch {
   int nobs, nslots;
   int max_total_nbins;
   int blocks_per_sm;         // <=0: occupancy maximum (generic kernel)
+  int cta_split;             // fast kernel partition, see Tuning::cta_split (capi_internal.h)
   bool pdl;                  // fast kernel: programmatic dependent launch on the previous kernel of the stream
   bool jit;                  // the program has no instantiation in the build: NVRTC-compiled kernel (jit.cu)
   int prog_nops;                 // >= 0: compile-time systematic program, < 0: run-time dispatch

@@ -140,7 +140,11 @@ def test_eval_without_points_and_get_samples():
 SMALL = [("A", 0.01), ("B", 0.02), ("C", 0.002), ("D", 0.003)]
 VARIANTS = [("smem", dict(smem_hist_max_bins=56 * 1024)), ("global", dict(smem_hist_max_bins=0)),
             ("dynamic", dict(force_dynamic=True)), ("dynamic_global", dict(force_dynamic=True, smem_hist_max_bins=0)),
-            ("generic", dict(force_generic=True)), ("generic_global", dict(force_generic=True, smem_hist_max_bins=0))]
+            ("generic", dict(force_generic=True)), ("generic_global", dict(force_generic=True, smem_hist_max_bins=0)),
+            # the measurement forms of the fast kernel's partition (kernel_select bits 8-9)
+            ("contiguous", dict(cta_split=1)), ("contiguous_global", dict(cta_split=1, smem_hist_max_bins=0)),
+            ("warp_ranges_global", dict(cta_split=2, smem_hist_max_bins=0)),
+            ("segments_global", dict(cta_split=3, smem_hist_max_bins=0))]
 
 
 @pytest.mark.parametrize("variant", VARIANTS, ids=[v[0] for v in VARIANTS])
