@@ -95,27 +95,47 @@ static int chain_build_tables(sxmc_chain* c) {
 
 // in_step: the launch follows the previous step's lookup kernel in the stream -- its prologue may
 // overlap that kernel's tail (programmatic dependent launch)
-static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr, bool in_step = false) {
+static void chain_p2p_params(sxmc_chain* c, int b, P2PParams& W) {
+  memset(&W, 0, sizeof W);
+  for (int p = 0; p < c->p2p_nranks; ++p) {
+    W.part[p] = (const unsigned*)c->p2p_peer[p];
+    W.flags[p] = (unsigned*)c->p2p_peer[p] + 4 * c->p2p_pitch;
+  }
+  W.sum = c->hist_buf[b];
+  W.sum_offset = (2 + (size_t)b) * c->p2p_pitch;
+  // form 3 (exchange fused into a rank-sharded lookup) applies to steps only: every other
+  // evaluation, and the last step of a call, exchanges whole histograms in the automatic form
+  W.twoshot = (c->tune.p2p_form == 1 || c->tune.p2p_form == 2) ? (c->tune.p2p_form == 2) : (c->p2p_nranks > 2);
+  W.seq = c->p2p_state; W.ticket = c->p2p_state + 1; W.abort_flag = c->p2p_state + 2;
+  W.words = c->hist_words; W.pitch = c->p2p_pitch; W.parity = b;
+  W.peer_timeout_ns = c->p2p_timeout_ns;
+  W.nranks = c->p2p_nranks; W.rank = c->p2p_rank;
+}
+
+// A sharded step may run its exchange inside the lookup launch (nll_sharded_kernels.cu) when the
+// unsharded chain would take the grouped lookup over many bins -- the launch whose partial sums
+// the fused kernel reproduces block for block.
+static bool chain_fused_ok(const sxmc_chain* c) {
+  if (c->p2p_nranks < 2 || !c->mult_dev || c->nsignals > 128) return false;
+  const int form = c->tune.p2p_form;
+  if (form == 1 || form == 2) return false;             // a whole-histogram form was asked for
+  if (c->total_nbins <= 4096 && c->hist_words <= 65536) return false;   // launch_nll: one-block lookup
+  const int g = nll_sharded_logical_grid(c->total_nbins);
+  return g >= c->p2p_nranks && g <= P2P_PARTIALS_MAX;
+}
+
+// fused: the exchange happens inside the lookup launch that follows (chain_nll)
+static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr, bool in_step = false, bool fused = false) {
   BinLaunch BL = c->batch[b].launch;
   BL.pdl = in_step && !c->tune.no_pdl;
   BL.cta_split = c->tune.cta_split;
   SXMC_TRY(launch_bin(BL, c->stream));
   c->launches += 1;
   if (after_bin) SXMC_CUDA(cudaEventRecord(after_bin, c->stream));
+  if (fused) return SXMC_OK;
   if (c->p2p_nranks > 1) {
     P2PParams W;
-    memset(&W, 0, sizeof W);
-    for (int p = 0; p < c->p2p_nranks; ++p) {
-      W.part[p] = (const unsigned*)c->p2p_peer[p];
-      W.flags[p] = (unsigned*)c->p2p_peer[p] + 4 * c->p2p_pitch;
-    }
-    W.sum = c->hist_buf[b];
-    W.sum_offset = (2 + (size_t)b) * c->p2p_pitch;
-    W.twoshot = c->tune.p2p_form ? (c->tune.p2p_form == 2) : (c->p2p_nranks > 2);
-    W.seq = c->p2p_state; W.ticket = c->p2p_state + 1; W.abort_flag = c->p2p_state + 2;
-    W.words = c->hist_words; W.pitch = c->p2p_pitch; W.parity = b;
-    W.peer_timeout_ns = c->p2p_timeout_ns;
-    W.nranks = c->p2p_nranks; W.rank = c->p2p_rank;
+    chain_p2p_params(c, b, W);
     SXMC_TRY(launch_hist_allreduce_p2p(W, c->stream));
     c->launches += 1;
   } else if (c->comm && c->comm->nranks > 1) {
@@ -127,7 +147,22 @@ static int chain_bin(sxmc_chain* c, int b, cudaEvent_t after_bin = nullptr, bool
   return SXMC_OK;
 }
 
-static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut) {
+static int chain_nll(sxmc_chain* c, int b, int mode, bool zero_other, float* lut, bool fused = false) {
+  if (fused) {
+    ShardNllParams Q;
+    memset(&Q, 0, sizeof Q);
+    chain_p2p_params(c, b, Q.W);
+    Q.sigs = c->sigs_dev[b];
+    Q.st = c->st_dev;
+    Q.mult = c->mult_dev;
+    Q.zero_ptr = c->part_buf[1 - b];
+    Q.zero_words = c->hist_words;
+    Q.partials_offset = 4 * c->p2p_pitch + 2 * P2P_MAX_RANKS;
+    Q.ns = c->nsignals; Q.np = c->nparameters; Q.nsources = c->nsources; Q.nbins = c->total_nbins; Q.mode = mode;
+    SXMC_TRY(launch_nll_sharded(Q, !c->tune.no_pdl, c->stream));
+    c->launches += 1;
+    return SXMC_OK;
+  }
   NllLaunch L;
   L.sigs_dev = c->sigs_dev[b];
   L.norms_dev = c->hist_buf[b] + (size_t)c->nsignals * c->total_nbins;
@@ -503,9 +538,10 @@ static int chain_fixed_table(sxmc_chain* c, bool rebin) {
 }
 
 // one MCMC step enqueued on the chain's stream: [bin -> (allreduce)] -> lookup+nll+decide+propose
-static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b) {
-  if (rebin) SXMC_TRY(chain_bin(c, b, nullptr, true));
-  SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));
+static int chain_enqueue_step(sxmc_chain* c, bool rebin, int b, bool fused = false) {
+  fused = fused && rebin;
+  if (rebin) SXMC_TRY(chain_bin(c, b, nullptr, true, fused));
+  SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr, fused));
   return SXMC_OK;
 }
 
@@ -665,9 +701,12 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
     if (c->mode == 2) return rc;     // explicitly requested: report why it cannot run
     cudaGetLastError();              // automatic: fall through to the graph path
   }
+  // Sharded steps run fused (exchange inside a rank-sharded lookup) except the LAST step of the
+  // call, which exchanges whole histograms: bins / norms / nll_at find them where they always were.
+  const bool fused = rebin && chain_fused_ok(c);
   auto plain_step = [&]() -> int {
     const unsigned i = c->steps_done;
-    int rc = chain_enqueue_step(c, rebin, rebin ? (int)((i + 1) & 1) : 0);
+    int rc = chain_enqueue_step(c, rebin, rebin ? (int)((i + 1) & 1) : 0, fused && left > 1);
     if (!rc) { c->steps_done += 1; left -= 1; }
     return rc;
   };
@@ -678,7 +717,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
     SXMC_CUDA(cudaStreamBeginCapture(c->stream, has_comm ? cudaStreamCaptureModeRelaxed
                                                           : cudaStreamCaptureModeThreadLocal));
     int rc = SXMC_OK;
-    for (unsigned k = 0; k < GRAPH_STEPS && !rc; ++k) rc = chain_enqueue_step(c, rebin, rebin ? (int)((k + 1) & 1) : 0);
+    for (unsigned k = 0; k < GRAPH_STEPS && !rc; ++k) rc = chain_enqueue_step(c, rebin, rebin ? (int)((k + 1) & 1) : 0, fused);
     cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
     c->graph_launches = c->launches - before;
     c->launches = before;
@@ -691,7 +730,7 @@ int sxmc_chain_advance(sxmc_chain* c, unsigned nsteps) {
   SXMC_CUDA(cudaEventRecord(c->ev0, c->stream));
   if ((c->mode == 0 || c->mode == 3) && c->graph_exec) {
     if ((c->steps_done & 1u) && left > 0) SXMC_TRY(plain_step());
-    while (left >= GRAPH_STEPS) {
+    while (left >= GRAPH_STEPS + (fused ? 1u : 0u)) {
       SXMC_CUDA(cudaGraphLaunch(c->graph_exec, c->stream));
       c->launches += c->graph_launches;
       c->steps_done += GRAPH_STEPS;
@@ -728,6 +767,7 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
     SXMC_CUDA(cudaMalloc(&c->flush_buf, flush_bytes));
     c->flush_bytes = flush_bytes;
   }
+  const bool fused_ok = rebin && chain_fused_ok(c);
   const unsigned CHUNK = 64;
   if (c->tev.empty()) {
     c->tev.resize(4 * CHUNK);
@@ -742,10 +782,11 @@ int sxmc_chain_advance_timed(sxmc_chain* c, unsigned nsteps, size_t flush_bytes,
       const int b = rebin ? (int)((i + 1) & 1) : 0;
       if (flush_bytes) SXMC_CUDA(cudaMemsetAsync(c->flush_buf, (int)(i & 0xff), flush_bytes, c->stream));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k], c->stream));
-      if (rebin) SXMC_TRY(chain_bin(c, b, c->tev[3 * CHUNK + k], true));
+      const bool fused = fused_ok && !(left == n && k + 1 == n);       // not the call's last step
+      if (rebin) SXMC_TRY(chain_bin(c, b, c->tev[3 * CHUNK + k], true, fused));
       else SXMC_CUDA(cudaEventRecord(c->tev[3 * CHUNK + k], c->stream));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 1], c->stream));
-      SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr));
+      SXMC_TRY(chain_nll(c, b, NLL_MODE_STEP, rebin, nullptr, fused));
       SXMC_CUDA(cudaEventRecord(c->tev[3 * k + 2], c->stream));
       c->steps_done += 1;
     }
@@ -927,7 +968,8 @@ int sxmc_chain_p2p_export(sxmc_chain* c, void* handle64_out) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
   if (!c->p2p_window) {
     c->p2p_pitch = (c->hist_words + 31) & ~(size_t)31;           // 128-byte aligned parities
-    const size_t words = 4 * c->p2p_pitch + 2 * P2P_MAX_RANKS;
+    // ... + [P2P_PARTIALS_MAX] doubles: the partial sums of the fused, rank-sharded lookup
+    const size_t words = 4 * c->p2p_pitch + 2 * P2P_MAX_RANKS + 2 * (size_t)P2P_PARTIALS_MAX;
     SXMC_CUDA(cudaMalloc(&c->p2p_window, sizeof(unsigned) * words));
     SXMC_CUDA(cudaMemset(c->p2p_window, 0, sizeof(unsigned) * words));
     SXMC_CUDA(cudaMalloc(&c->p2p_state, sizeof(unsigned) * 16));      // + 4 x u64 phase clocks

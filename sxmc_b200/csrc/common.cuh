@@ -204,6 +204,22 @@ struct P2PParams {
 };
 
 // One signal as seen by the lookup + event-likelihood kernel.
+struct NllSignal;
+struct ChainState;
+// Arguments of the fused exchange + rank-sharded lookup (nll_sharded_kernels.cu), by value.
+constexpr int P2P_PARTIALS_MAX = 148 * 8;  // doubles per window: one per logical block of the unsharded lookup grid
+struct ShardNllParams {
+  P2PParams W;                  // windows, flags, parity of this step's partial histograms
+  const NllSignal* sigs;        // static per-signal fields (nexpected, bin_volume, n_mc, source_id)
+  ChainState* st;
+  const unsigned* mult;         // events per bin [nbins]
+  unsigned* zero_ptr;           // partial buffer of the next step, cleared here
+  unsigned long long zero_words;
+  unsigned long long partials_offset;   // words from a window's start to its [P2P_PARTIALS_MAX] doubles
+  int ns, np, nsources, nbins, mode;
+  int logical_grid, lb0;        // filled by launch_nll_sharded
+};
+
 struct NllSignal {
   const unsigned* bins;       // histogram of this step
   const unsigned* norm;       // its in-domain count

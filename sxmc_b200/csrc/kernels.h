@@ -97,6 +97,9 @@ void set_nll_xdbg(unsigned long long* dev);   // [1202][8] stamps of the next lo
 int launch_pdf_table(const NllSignal* sigs_dev, const unsigned* norms_dev, int nsignals, int nbins, double* table_dev,
                      cudaStream_t stream);
 int launch_nll(const NllLaunch& L, cudaStream_t stream);
+// the sample-sharded step's exchange fused into a rank-sharded grouped lookup (nll_sharded_kernels.cu)
+int nll_sharded_logical_grid(int nbins);
+int launch_nll_sharded(ShardNllParams Q, bool pdl, cudaStream_t stream);
 
 // standalone MCMC::nll over a materialised lut (src/mcmc.cpp:390-415)
 int launch_nll_lut(const float* lut, size_t ne, size_t ns, const double* pars, size_t npars,

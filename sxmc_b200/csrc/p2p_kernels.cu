@@ -21,34 +21,9 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "grid_sync.cuh"
+#include "p2p_device.cuh"
 
 namespace sxmc {
-
-__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Spin until every peer's flag in this rank's own flag row `base` has reached `seq`.
-__device__ __forceinline__ int wait_peers(const P2PParams& W, const unsigned* base, unsigned seq) {
-  // The peers are other host processes: their skew (a GIL stall, a lazy module load, a graph
-  // instantiation) is bounded in wall-clock time, far above the grid barriers' cycle budget.
-  const unsigned long long t0 = globaltimer_ns();
-  for (int p = 0; p < W.nranks; ++p) {
-    unsigned n = 0;
-    while ((int)(ld_acquire_sys_u32(base + p) - seq) < 0) {
-      if ((++n & 63u) == 0) {
-        if (*(volatile unsigned*)W.abort_flag) return 0;
-        if (globaltimer_ns() - t0 > W.peer_timeout_ns) { atomicExch(W.abort_flag, 1u); return 0; }
-      }
-    }
-  }
-  return 1;
-}
 
 __global__ void __launch_bounds__(256)
 hist_allreduce_p2p_kernel(const __grid_constant__ P2PParams W) {

@@ -27,73 +27,66 @@ def gloo_limits(outdir):
 def nccl_sample_sharded(outdir):
     import torch
     import torch.distributed as dist
-    from sxmc_b200 import _lib, mcmc, sharding, workloads as W
+    from sxmc_b200 import _lib, mcmc, pdfz, sharding, workloads as W
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank, world = dist.get_rank(), dist.get_world_size()
     _lib.check(_lib.lib().sxmc_init(local))
-    fit = W.config_C(0.002)
-    nsteps = 300
     out = {}
 
-    # the unsharded chain, on every rank (same seed => same chain)
-    hists, chain = mcmc.build_fit(fit)
-    chain.set_seed(99, 0)
-    chain.set_mode(3)
-    ls = chain(fit.data, nsteps, 0.1)
-    out.update(single_rows=ls.get_samples().copy(), single_bins=chain.bins(),
-               single_norms=chain.norms(), single_accepted=chain.accepted())
-    chain.close()
-    for h in hists:
-        h.close()
+    def single(fit, nsteps, pre):
+        """the unsharded chain, on every rank (same seed => same chain)"""
+        hists, chain = mcmc.build_fit(fit)
+        chain.set_seed(99, 0)
+        chain.set_mode(3)
+        ls = chain(fit.data, nsteps, 0.1)
+        out.update({pre + "rows": ls.get_samples().copy(), pre + "bins": chain.bins(),
+                    pre + "norms": chain.norms(), pre + "accepted": chain.accepted()})
+        chain.close()
+        for h in hists:
+            h.close()
 
-    # sample-sharded: this rank's slice of every signal, histograms summed over NCCL
-    comm = sharding.Comm(device=local)
-    part = sharding.shard_fit_samples(fit, rank, world)
-    hists, chain = mcmc.build_fit(part)
-    chain.set_seed(99, 0)
-    chain.set_comm(comm.handle)
-    ls = chain(fit.data, nsteps, 0.1)
-    out.update(rows=ls.get_samples().copy(), bins=chain.bins(), norms=chain.norms(),
-               accepted=chain.accepted())
-    chain.close()
-    for h in hists:
-        h.close()
-    torch.cuda.synchronize()
-    dist.barrier()
-    comm.close()
+    def sharded(fit, nsteps, pre, p2p_form=None):
+        """this rank's slice of every signal; histograms summed over NCCL (p2p_form None) or over
+        NVLink peer memory: 0 automatic (the exchange fused into a rank-sharded lookup where the
+        fit allows it), 1 one-shot all-reduce kernel, 2 reduce-scatter + all-gather kernel"""
+        part = sharding.shard_fit_samples(fit, rank, world)
+        comm = None
+        if p2p_form is not None:
+            pdfz.set_bin_tuning(p2p_form=p2p_form)
+        hists, chain = mcmc.build_fit(part)
+        pdfz.set_bin_tuning()
+        chain.set_seed(99, 0)
+        if p2p_form is None:
+            comm = sharding.Comm(device=local)
+            chain.set_comm(comm.handle)
+        else:
+            sharding.connect_p2p(chain, rank, world)
+        ls = chain(fit.data, nsteps, 0.1)
+        out.update({pre + "rows": ls.get_samples().copy(), pre + "bins": chain.bins(),
+                    pre + "norms": chain.norms(), pre + "accepted": chain.accepted()})
+        if p2p_form is not None:
+            nex, aborted = sharding.p2p_status(chain)
+            out.update({pre + "exchanges": nex, pre + "aborted": aborted})
+        torch.cuda.synchronize()
+        dist.barrier()
+        chain.close()
+        for h in hists:
+            h.close()
+        if comm is not None:
+            comm.close()
 
-    # the same over NVLink peer memory: one exchange kernel per step instead of ncclAllReduce
-    hists, chain = mcmc.build_fit(part)
-    chain.set_seed(99, 0)
-    sharding.connect_p2p(chain, rank, world)
-    ls = chain(fit.data, nsteps, 0.1)
-    nex, aborted = sharding.p2p_status(chain)
-    out.update(p2p_rows=ls.get_samples().copy(), p2p_bins=chain.bins(), p2p_norms=chain.norms(),
-               p2p_accepted=chain.accepted(), p2p_exchanges=nex, p2p_aborted=aborted)
-    torch.cuda.synchronize()
-    dist.barrier()
-    chain.close()
-    for h in hists:
-        h.close()
-
-    # ... and its reduce-scatter + all-gather form (what more than two ranks use), forced here
-    from sxmc_b200 import pdfz
-    pdfz.set_bin_tuning(p2p_form=2)
-    hists, chain = mcmc.build_fit(part)
-    chain.set_seed(99, 0)
-    sharding.connect_p2p(chain, rank, world)
-    ls = chain(fit.data, nsteps, 0.1)
-    nex, aborted = sharding.p2p_status(chain)
-    out.update(p2p2_rows=ls.get_samples().copy(), p2p2_bins=chain.bins(), p2p2_norms=chain.norms(),
-               p2p2_accepted=chain.accepted(), p2p2_exchanges=nex, p2p2_aborted=aborted)
-    torch.cuda.synchronize()
-    dist.barrier()
-    chain.close()
-    for h in hists:
-        h.close()
-    pdfz.set_bin_tuning(p2p_form=0)
+    fit = W.config_C(0.002)                      # 5000 bins, 10 signals, one dataset: the fused form applies
+    single(fit, 300, "single_")
+    sharded(fit, 300, "")                        # NCCL
+    sharded(fit, 300, "p2p_", 0)                 # fused exchange + rank-sharded lookup
+    sharded(fit, 300, "p2p1_", 1)                # one-shot all-reduce kernel
+    sharded(fit, 300, "p2p2_", 2)                # reduce-scatter + all-gather kernel
+    # 200 000 bins, 30 signals: the fused lookup's logical grid is capped (two bins per thread)
+    fit = W.config_D(0.002, stress=True)
+    single(fit, 60, "D_single_")
+    sharded(fit, 60, "D_p2p_", 0)
     np.savez(os.path.join(outdir, "sharded_rank%d.npz" % rank), **out)
     dist.destroy_process_group()
 
