@@ -636,7 +636,10 @@ def run_own_arm(args, rank, world, local):
     p2p_phases = None
     if "p2p_us" in r:
         box = gather_objects((r["p2p_us"], r.get("p2p_us_warm")))
-        p2p_phases = {"what": "per rank [wait for every peer's partial, sum, close], device globaltimer",
+        p2p_phases = {"what": "per rank, device globaltimer, us per step: [wait for every peer's partial histogram, "
+                              "sum (fused form: the rank-sharded lookup, until the rank's last block is done), close "
+                              "(second flag round), then block 0 of the fused kernel: peers' counts gathered + constants ready, "
+                              "bins evaluated, block sum, partial sums stored + fenced + ticket]",
                       "timed": [b[0] for b in box], "back_to_back": [b[1] for b in box]}
     step_ms = allreduce_max(r["value_ms"])
     split_ms = allreduce_max(r["step_ms"])

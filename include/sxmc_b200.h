@@ -351,8 +351,9 @@ int sxmc_chain_p2p_connect(sxmc_chain* c, const void* handles, int nranks, int r
 int sxmc_chain_p2p_status(sxmc_chain* c, unsigned* exchanges_out, int* aborted_out);
 /* profiling hook: nanoseconds (device globaltimer), summed over all exchanges so far, the
  * exchange kernel spent [0] publishing its flag and waiting for every peer's partial, [1]
- * summing (until the last block is done), [2] closing the step (two-shot: second flag round) */
-int sxmc_chain_p2p_clocks(sxmc_chain* c, double* ns_out3);
+ * summing (until the last block is done; fused form: the rank-sharded lookup), [2] closing the step
+ * (second flag round); fused form only, block 0: [3] peers' counts gathered and per-signal constants ready, [4] bins evaluated, [5] block sum, [6] partial sums stored everywhere, fenced, ticket taken.  ns_out7: seven doubles. */
+int sxmc_chain_p2p_clocks(sxmc_chain* c, double* ns_out7);
 
 #ifdef __cplusplus
 }

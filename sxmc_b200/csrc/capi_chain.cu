@@ -968,13 +968,13 @@ int sxmc_chain_p2p_export(sxmc_chain* c, void* handle64_out) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
   if (!c->p2p_window) {
     c->p2p_pitch = (c->hist_words + 31) & ~(size_t)31;           // 128-byte aligned parities
-    // ... + [P2P_PARTIALS_MAX] doubles: the partial sums of the fused, rank-sharded lookup
-    const size_t words = 4 * c->p2p_pitch + 2 * P2P_MAX_RANKS + 2 * (size_t)P2P_PARTIALS_MAX;
+    // ... + [P2P_PARTIALS_MAX] x 16 bytes: the tagged partial sums of the fused, rank-sharded lookup
+    const size_t words = 4 * c->p2p_pitch + 2 * P2P_MAX_RANKS + 4 * (size_t)P2P_PARTIALS_MAX;
     SXMC_CUDA(cudaMalloc(&c->p2p_window, sizeof(unsigned) * words));
     SXMC_CUDA(cudaMemset(c->p2p_window, 0, sizeof(unsigned) * words));
-    SXMC_CUDA(cudaMalloc(&c->p2p_state, sizeof(unsigned) * 16));      // + 4 x u64 phase clocks
-    SXMC_CUDA(cudaMemset(c->p2p_state, 0, sizeof(unsigned) * 16));
-    SXMC_CUDA(cudaMallocHost(&c->p2p_state_host, sizeof(unsigned) * 16));
+    SXMC_CUDA(cudaMalloc(&c->p2p_state, sizeof(unsigned) * 32));      // + 8 x u64 phase clocks
+    SXMC_CUDA(cudaMemset(c->p2p_state, 0, sizeof(unsigned) * 32));
+    SXMC_CUDA(cudaMallocHost(&c->p2p_state_host, sizeof(unsigned) * 32));
   }
   cudaIpcMemHandle_t h;
   SXMC_CUDA(cudaIpcGetMemHandle(&h, c->p2p_window));
@@ -1018,14 +1018,14 @@ int sxmc_chain_p2p_status(sxmc_chain* c, unsigned* exchanges_out, int* aborted_o
   return SXMC_OK;
 }
 
-int sxmc_chain_p2p_clocks(sxmc_chain* c, double* ns_out3) {
-  if (!c || !ns_out3) SXMC_INVAL("sxmc_chain_p2p_clocks: NULL argument");
-  ns_out3[0] = ns_out3[1] = ns_out3[2] = 0;
+int sxmc_chain_p2p_clocks(sxmc_chain* c, double* ns_out7) {
+  if (!c || !ns_out7) SXMC_INVAL("sxmc_chain_p2p_clocks: NULL argument");
+  for (int i = 0; i < 7; ++i) ns_out7[i] = 0;
   if (!c->p2p_state) return SXMC_OK;
   SXMC_CUDA(cudaStreamSynchronize(c->stream));
-  SXMC_CUDA(cudaMemcpy(c->p2p_state_host, c->p2p_state, sizeof(unsigned) * 16, cudaMemcpyDeviceToHost));
+  SXMC_CUDA(cudaMemcpy(c->p2p_state_host, c->p2p_state, sizeof(unsigned) * 32, cudaMemcpyDeviceToHost));
   const unsigned long long* clk = reinterpret_cast<const unsigned long long*>(c->p2p_state_host + 4);
-  for (int i = 0; i < 3; ++i) ns_out3[i] = (double)clk[1 + i];
+  for (int i = 0; i < 7; ++i) ns_out7[i] = (double)clk[1 + i];
   return SXMC_OK;
 }
 

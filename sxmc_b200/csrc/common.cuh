@@ -215,7 +215,7 @@ struct ShardNllParams {
   const unsigned* mult;         // events per bin [nbins]
   unsigned* zero_ptr;           // partial buffer of the next step, cleared here
   unsigned long long zero_words;
-  unsigned long long partials_offset;   // words from a window's start to its [P2P_PARTIALS_MAX] doubles
+  unsigned long long partials_offset;   // words from a window's start to its [P2P_PARTIALS_MAX] x {lo, tag, hi, tag}
   int ns, np, nsources, nbins, mode;
   int logical_grid, lb0;        // filled by launch_nll_sharded
 };

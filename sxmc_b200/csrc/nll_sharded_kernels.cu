@@ -7,28 +7,30 @@
 // and the lookup itself is dealt over the ranks:
 //   * the grouped lookup's logical grid -- G blocks of 128 bins, exactly the grid the unsharded
 //     chain launches (launch_nll) -- is cut into N contiguous ranges of blocks, one per rank;
-//   * a physical block has 128 x N threads: thread (t, p) loads peer p's partial counts of the
-//     block's bin t for every signal straight from p's window over NVLink (up to 16 loads in
-//     flight per thread, so the block pays about one NVLink round trip), the N partials meet in
-//     shared memory (integer atomics: order-free), and threads (t, 0) evaluate eval_pdf +
-//     nll_event_chunks for their bin with the arithmetic, the order of additions and the block
-//     reduction of lookup_nll_kernel<128>;
+//   * a physical block (512 threads) gathers the N partial counts of its 128 bins for every
+//     signal straight from the peers' windows over NVLink -- 128-bit loads, all of a thread's loads
+//     (and the in-domain counts) issued before the first is consumed, so the block pays ONE NVLink
+//     round trip -- and adds them up in shared memory (integer atomics: order-free);
+//   * four threads per bin then evaluate eval_pdf's division and nll_event_chunks' product for the
+//     bin's signals, and one of them adds the products in signal order: the arithmetic, the order
+//     of additions and the block reduction of lookup_nll_kernel<128>;
 //   * the block's partial sum goes to slot [logical block] of EVERY rank's partial array (N
-//     stores of 8 bytes instead of an all-gather of the histograms);
-//   * the rank's last block tells every peer "my sums are in place", waits for theirs, totals
-//     the G partials in the order the unsharded kernel's last block uses and finishes the step
-//     (nll_total, jump_decider, pick_new_vector: finish_step2) -- on every rank alike.
+//     tagged stores of 16 bytes instead of an all-gather of the histograms);
+//   * the rank's last block collects the G partial sums as they arrive, totals them in the order the
+//     unsharded kernel's last block uses and finishes the step (nll_total, jump_decider,
+//     pick_new_vector: finish_step2) -- on every rank alike.
 // Every rank therefore takes the decision the unsharded chain takes, bit for bit, for any N
 // (tests/test_sharding.py), and nobody ever holds the summed histograms: a step moves
 // (N-1)/N x 3 MB over NVLink into each rank once, and the replicated lookup is gone.
 //
-// Two flag rounds per step, the same rows of the window the all-reduce kernel uses:
-//   [p][r]      rank r's partial histogram of step s is complete (published after its binning kernel)
-//   [p][8 + r]  rank r has read what it needs of step s and stored its partial sums everywhere
-// Buffer reuse needs nothing more.  A rank clears partial buffer b^1 (for step s+1) during the
-// lookup of step s: its peers read b^1 during step s-1 and said so ([8 + r] = s-1) before this rank
-// left step s-1.  A peer's partial sums of step s+1 cannot arrive before this rank has read those
-// of step s: the peer needs this rank's [p][r] = s+1 first, which this rank's NEXT launch publishes.
+// Synchronisation per step: ONE flag round -- [p][r] = s in the window's flag row the all-reduce
+// kernel uses too: rank r's partial histogram of step s is complete, published after its binning
+// kernel -- and the partial sums themselves, each tagged with s.  A rank that holds all G sums of
+// step s knows every rank has finished reading the partial histograms of step s.  Buffer reuse
+// needs nothing more.  A rank clears partial buffer b^1 (for step s+1) during the lookup of step s:
+// its peers read b^1 during step s-1 and this rank had their sums of s-1 before it left step s-1.  A
+// peer's sums of step s+1 cannot overwrite those of step s unread: the peer needs this rank's
+// [p][r] = s+1 first, which this rank's NEXT launch publishes.
 #include "common.cuh"
 #include "kernels.h"
 #include "nll_device.cuh"
@@ -56,12 +58,16 @@ __device__ __forceinline__ double block_sum128_first_warps(double v, double* s_w
   return t;
 }
 
-__global__ void __launch_bounds__(1024)
+constexpr int SH_THREADS = 512;          // 4 threads per bin of the logical block
+constexpr int SH_GATHER = 16;            // 128-bit peer loads in flight per thread
+
+__global__ void __launch_bounds__(SH_THREADS)
 lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
-  extern __shared__ unsigned s_cnt[];                     // [ns][128] summed counts of the block's bins
+  extern __shared__ double s_dyn[];                       // [ns][128] products, then [ns][128] counts
   __shared__ double s_c[SH_MAX_SIGNALS];
   __shared__ double s_bn[SH_MAX_SIGNALS];
   __shared__ unsigned s_norm[SH_MAX_SIGNALS];
+  __shared__ unsigned s_m[SH_BINS];
   __shared__ double s_warp[SH_BINS / 32];
   __shared__ double s_term[SH_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
   __shared__ int s_ok, s_last;
@@ -70,28 +76,41 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
   __shared__ double s_u, s_bsum;
 
   const P2PParams& W = Q.W;
-  const int tid = threadIdx.x, nthreads = blockDim.x;
-  const int t = tid & (SH_BINS - 1), p = tid / SH_BINS;   // bin of the block, peer
-  const int ns = Q.ns, np = Q.np, nb = Q.nbins;
+  const int tid = threadIdx.x;
+  const int t = tid & (SH_BINS - 1), kq = tid / SH_BINS;  // evaluation: bin of the block, quarter of the signals
+  const int ns = Q.ns, np = Q.np, nb = Q.nbins, nr = W.nranks;
+  double* const s_prod = s_dyn;                                            // [ns][128]
+  unsigned* const s_cnt = reinterpret_cast<unsigned*>(s_dyn + (size_t)ns * SH_BINS);   // [ns][128]
   const int lb = Q.lb0 + blockIdx.x;                      // logical block of the unsharded grid
   const unsigned seq = *W.seq + 1u;
   unsigned long long* const clk = reinterpret_cast<unsigned long long*>(W.seq + 4);
-  unsigned long long t0 = 0;
+  unsigned long long t0 = 0, tph = 0;      // phase clocks of block 0 (clk[4..7], sxmc_chain_p2p_clocks)
+#define SH_PHASE(k)                                                          \
+  do {                                                                       \
+    if (blockIdx.x == 0 && tid == 0) {                                       \
+      const unsigned long long t_ = globaltimer_ns();                        \
+      clk[k] += t_ - tph;                                                    \
+      tph = t_;                                                              \
+    }                                                                        \
+  } while (0)
 
   // ---- prologue independent of this step's histograms (overlaps the binning kernel's tail) ----
-  prefetch_state(F, Q.st, np, tid, nthreads);
+  prefetch_state(F, Q.st, np, tid, SH_THREADS);
   NllSignal my_sig;
   if (tid < ns) my_sig = Q.sigs[tid];
-  for (unsigned long long w = blockIdx.x * (unsigned long long)nthreads + tid; w < Q.zero_words;
-       w += (unsigned long long)gridDim.x * nthreads)
+  const long long gstride = (long long)Q.logical_grid * SH_BINS;
+  long long b0 = (long long)lb * SH_BINS;
+  if (tid < SH_BINS) s_m[tid] = (b0 + tid < nb) ? Q.mult[b0 + tid] : 0u;   // events per bin: static data
+  for (unsigned long long w = blockIdx.x * (unsigned long long)SH_THREADS + tid; w < Q.zero_words;
+       w += (unsigned long long)gridDim.x * SH_THREADS)
     Q.zero_ptr[w] = 0u;                                   // the buffer step s+1 bins into (header)
-  for (int k = tid; k < ns * SH_BINS; k += nthreads) s_cnt[k] = 0u;
+  for (int k = tid; k < ns * SH_BINS; k += SH_THREADS) s_cnt[k] = 0u;
   if (tid < ns) s_norm[tid] = 0u;
   pdl_wait();
   pdl_trigger();
 
   // ---- round 1: my partial is complete (the binning kernel has finished); wait for everyone's ----
-  if (blockIdx.x == 0 && tid < W.nranks) {
+  if (blockIdx.x == 0 && tid < nr) {
     if (tid == 0) t0 = globaltimer_ns();
     __threadfence_system();
     st_release_sys_u32(W.flags[tid] + W.rank, seq);
@@ -102,125 +121,192 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
       const unsigned long long t1 = globaltimer_ns();
       clk[0] = t1;
       clk[1] += t1 - t0;
+      tph = t1;
     }
   }
   __syncthreads();
   const bool ok = s_ok != 0;
   const size_t poff = (size_t)W.parity * W.pitch;
-  const unsigned* part = W.part[p] + poff;
 
   const bool pre_rng = pre_rng_applies(F, Q.mode);
-  if (pre_rng && blockIdx.x == 0 && tid >= nthreads - 32) pre_rng_draw(F, np, tid & 31, Q.st->pre_z, &Q.st->pre_u);
+  if (pre_rng && blockIdx.x == 0 && tid >= SH_THREADS - 32) pre_rng_draw(F, np, tid & 31, Q.st->pre_z, &Q.st->pre_u);
 
-  // in-domain counts: every (signal, peer) pair one load
-  if (ok)
-    for (int k = tid; k < ns * W.nranks; k += nthreads) {
-      const int j = k % ns, q = k / ns;
-      atomicAdd(&s_norm[j], __ldcv(W.part[q] + poff + (size_t)ns * nb + j));
-    }
-  __syncthreads();
-  if (tid < ns) {
-    const int j = tid;
-    const unsigned my_norm = s_norm[j];
-    const float eff = (float)(1.0 * my_norm / my_sig.n_mc);                 // nll_kernels.cpp:105
-    const double rate = __dmul_rn(F.proposed[my_sig.source_id], my_sig.nexpected);
-    s_c[j] = __dmul_rn(rate, (double)eff);
-    s_bn[j] = __dmul_rn((double)my_norm, my_sig.bin_volume);                // pdfz.cpp:417
-    s_term[j] = __dmul_rn(rate, (double)my_norm) / (double)my_sig.n_mc;     // nll_kernels.cpp:167-171
-  }
-  for (int i = tid; i < np; i += nthreads) {                                // nll_kernels.cpp:176-185
-    const double sg = F.sigmas[i];
-    double x2 = 0;
-    if (sg > 0) {
-      const double x = __dadd_rn(F.proposed[i], -F.means[i]) / sg;
-      x2 = __dmul_rn(__dmul_rn(0.5, x), x);
-    }
-    s_term[ns + i] = x2;
-  }
-
-  // ---- the block's bins: bin b of logical block lb, then b + G x 128, ... as the unsharded grid ----
   double sum = 0;
-  const long long gstride = (long long)Q.logical_grid * SH_BINS;
   bool first = true;
-  for (long long b0 = (long long)lb * SH_BINS; b0 < nb; b0 += gstride) {
-    const long long b = b0 + t;
-    if (!first) {
+  for (; b0 < nb; b0 += gstride) {
+    if (!first) {                           // (more than 148 x 8 x 128 bins: several bins per thread)
       __syncthreads();
-      for (int k = tid; k < ns * SH_BINS; k += nthreads) s_cnt[k] = 0u;
+      for (int k = tid; k < ns * SH_BINS; k += SH_THREADS) s_cnt[k] = 0u;
+      if (tid < SH_BINS) s_m[tid] = (b0 + tid < nb) ? Q.mult[b0 + tid] : 0u;
       __syncthreads();
+    }
+    // ---- gather: the peers' counts of the block's 128 bins, every signal, ONE NVLink round trip:
+    // the in-domain counts (first pass) and up to SH_GATHER 128-bit loads per thread are issued
+    // before any of them is consumed.  Item i = (quad of bins, peer, signal), peers fastest after
+    // the quad, so neighbouring warps read from different GPUs.
+    unsigned nrm[2] = {0u, 0u};             // (signal, peer) pairs tid and tid + 512: <= 128 x 8 of them
+    const bool want_norm = first && ok;
+    if (want_norm)
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int k = tid + u * SH_THREADS;
+        if (k < ns * nr) nrm[u] = __ldcv(W.part[k / ns] + poff + (size_t)ns * nb + k % ns);
+      }
+    const int items = 32 * nr * ns;
+    const bool vec = (nb & 3) == 0;
+    if (ok && vec) {
+      for (int i0 = tid; i0 < items; i0 += SH_THREADS * SH_GATHER) {
+        uint4 x[SH_GATHER];
+#pragma unroll
+        for (int u = 0; u < SH_GATHER; ++u) {
+          const int i = i0 + u * SH_THREADS;
+          x[u] = make_uint4(0u, 0u, 0u, 0u);
+          if (i < items) {
+            const int q = i & 31, pj = i >> 5, pp = pj % nr, j = pj / nr;
+            const long long b = b0 + 4 * q;
+            if (b < nb) x[u] = __ldcv(reinterpret_cast<const uint4*>(W.part[pp] + poff + (size_t)j * nb + b));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < SH_GATHER; ++u) {
+          const int i = i0 + u * SH_THREADS;
+          if (i < items) {
+            const int q = i & 31, j = (i >> 5) / nr;
+            unsigned* dst = s_cnt + j * SH_BINS + 4 * q;
+            if (x[u].x) atomicAdd(dst + 0, x[u].x);
+            if (x[u].y) atomicAdd(dst + 1, x[u].y);
+            if (x[u].z) atomicAdd(dst + 2, x[u].z);
+            if (x[u].w) atomicAdd(dst + 3, x[u].w);
+          }
+        }
+      }
+    } else if (ok) {                        // bins per PDF not a multiple of four: 32-bit loads
+      for (int i = tid; i < 128 * nr * ns; i += SH_THREADS) {
+        const int tb = i & 127, pj = i >> 7, pp = pj % nr, j = pj / nr;
+        if (b0 + tb < nb && s_m[tb]) {
+          const unsigned h = __ldcv(W.part[pp] + poff + (size_t)j * nb + b0 + tb);
+          if (h) atomicAdd(s_cnt + j * SH_BINS + tb, h);
+        }
+      }
+    }
+    if (want_norm)
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int k = tid + u * SH_THREADS;
+        if (k < ns * nr) atomicAdd(&s_norm[k % ns], nrm[u]);
+      }
+    __syncthreads();
+    if (first) {
+      if (tid < ns) {
+        const int j = tid;
+        const unsigned my_norm = s_norm[j];
+        const float eff = (float)(1.0 * my_norm / my_sig.n_mc);                 // nll_kernels.cpp:105
+        const double rate = __dmul_rn(F.proposed[my_sig.source_id], my_sig.nexpected);
+        s_c[j] = __dmul_rn(rate, (double)eff);
+        s_bn[j] = __dmul_rn((double)my_norm, my_sig.bin_volume);                // pdfz.cpp:417
+        s_term[j] = __dmul_rn(rate, (double)my_norm) / (double)my_sig.n_mc;     // nll_kernels.cpp:167-171
+      }
+      for (int i = tid; i < np; i += SH_THREADS) {                              // nll_kernels.cpp:176-185
+        const double sg = F.sigmas[i];
+        double x2 = 0;
+        if (sg > 0) {
+          const double x = __dadd_rn(F.proposed[i], -F.means[i]) / sg;
+          x2 = __dmul_rn(__dmul_rn(0.5, x), x);
+        }
+        s_term[ns + i] = x2;
+      }
+      __syncthreads();
+    }
+    SH_PHASE(first ? 4 : 5);
+    // ---- evaluate: the division of eval_pdf and the product of nll_event_chunks for every (signal,
+    // bin) by four threads per bin, then thread (t, 0) adds its bin's products in signal order --
+    // each product is rounded on its own, so the sum is the unsharded kernel's, bit for bit
+    const unsigned m = s_m[t];
+    if (m)
+      for (int j = kq; j < ns; j += SH_THREADS / SH_BINS) {
+        float v = pdf_value(s_cnt[j * SH_BINS + t], s_bn[j]);                    // pdfz.cpp:429-432
+        if (isnan(v)) v = 0.0f;                                                 // nll_kernels.cpp:107
+        s_prod[j * SH_BINS + t] = __dmul_rn(s_c[j], (double)v);
+      }
+    __syncthreads();
+    if (kq == 0 && m) {
+      double sv = 0;
+      for (int j = 0; j < ns; ++j) sv = __dadd_rn(sv, s_prod[j * SH_BINS + t]);
+      if (sv > 0) sum += (double)m * log(sv);
     }
     first = false;
-    const unsigned m = (b < nb) ? Q.mult[b] : 0u;
-    if (ok && m) {
-      constexpr int LW = 16;    // loads in flight per thread (64 registers at 1024 threads)
-      for (int j0 = 0; j0 < ns; j0 += LW) {
-        unsigned h[LW];
-#pragma unroll
-        for (int q = 0; q < LW; ++q) h[q] = (j0 + q < ns) ? __ldcv(part + (size_t)(j0 + q) * nb + b) : 0u;
-#pragma unroll
-        for (int q = 0; q < LW; ++q)
-          if (j0 + q < ns && h[q]) atomicAdd(&s_cnt[(j0 + q) * SH_BINS + t], h[q]);
-      }
-    }
-    __syncthreads();
-    if (p == 0 && m) {
-      double s = 0;
-      for (int j = 0; j < ns; ++j) {
-        float v = pdf_value(s_cnt[j * SH_BINS + t], s_bn[j]);                // pdfz.cpp:429-432
-        if (isnan(v)) v = 0.0f;                                             // nll_kernels.cpp:107
-        s = __dadd_rn(s, __dmul_rn(s_c[j], (double)v));
-      }
-      if (s > 0) sum += (double)m * log(s);
-    }
   }
+  SH_PHASE(5);
   const double bsum = block_sum128_first_warps(sum, s_warp);
+  SH_PHASE(6);
   if (tid == 0) s_bsum = bsum;
   __syncthreads();
-  // the block's partial sum into slot lb of every rank's array
-  if (tid < W.nranks)
-    reinterpret_cast<double*>(const_cast<unsigned*>(W.part[tid]) + Q.partials_offset)[lb] = s_bsum;
-  __syncthreads();
-  if (tid == 0) {
-    __threadfence_system();           // cumulative: the block's peer stores before its ticket
+  // The block's partial sum into slot lb of every rank's array, as two 8-byte words that each carry
+  // half of the double AND the step number (the "LL" idiom of the collective libraries: an aligned
+  // 8-byte store arrives whole, so the reader needs no fence and no separate flag -- a word whose
+  // tag is the step's holds that step's data).
+  if (tid < nr && ok) {
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(s_bsum);
+    unsigned* slot = const_cast<unsigned*>(W.part[tid]) + Q.partials_offset + 4ull * lb;
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(slot), "r"((unsigned)bits), "r"(seq) : "memory");
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(slot + 2), "r"((unsigned)(bits >> 32)), "r"(seq) : "memory");
+  }
+  if (tid == 0) {                     // elects the block that finishes the step; the fences order block 0's
+    __threadfence();                  // pre-drawn random numbers (pre_z, pre_u) before the finisher's loads
     s_last = atomicAdd(W.ticket, 1u) == gridDim.x - 1;
     if (s_last) __threadfence();
   }
+  SH_PHASE(7);
   __syncthreads();
   if (!s_last) return;
 
-  // ---- the rank's last block: round 2, then the step's tail on every rank alike -------------
+  // ---- the rank's last block: collect every logical block's partial sum (own and peers'), total
+  // them in the unsharded kernel's order, finish the step -- on every rank alike.  Holding all G
+  // sums of step s also means every rank is done reading this step's partial histograms (a block
+  // stores its sum after its gather): the buffer-reuse argument of the header.
   unsigned long long t2 = 0;
   if (tid == 0) {
     t2 = globaltimer_ns();
     clk[2] += t2 - *(volatile unsigned long long*)clk;
+    s_ok = ok ? 1 : 0;
   }
-  if (tid < W.nranks) {
-    __threadfence_system();
-    st_release_sys_u32(W.flags[tid] + P2P_MAX_RANKS + W.rank, seq);
+  __syncthreads();
+  const unsigned* slots = W.part[W.rank] + Q.partials_offset;
+  double acc = 0;
+  if (tid < SH_BINS && ok) {
+    const unsigned long long tw = globaltimer_ns();
+    for (int k = tid; k < Q.logical_grid; k += SH_BINS) {
+      unsigned lo, hi, f0, f1, n = 0;
+      for (;;) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(f0) : "l"(slots + 4ull * k) : "memory");
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(hi), "=r"(f1) : "l"(slots + 4ull * k + 2) : "memory");
+        if (f0 == seq && f1 == seq) break;
+        if ((++n & 63u) == 0) {
+          if (*(volatile unsigned*)W.abort_flag) { s_ok = 0; break; }
+          if (globaltimer_ns() - tw > W.peer_timeout_ns) { atomicExch(W.abort_flag, 1u); s_ok = 0; break; }
+        }
+      }
+      acc += __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+    }
   }
+  __syncthreads();
   if (tid == 0) {
-    const int ok2 = wait_peers(W, W.flags[W.rank] + P2P_MAX_RANKS, seq);
-    s_ok = ok && ok2;
     clk[3] += globaltimer_ns() - t2;
     *W.ticket = 0u;
     *W.seq = seq;
   }
-  __syncthreads();
   if (!s_ok) return;                  // timed out: the abort flag is up, the host reports it
-  const double* partials = reinterpret_cast<const double*>(W.part[W.rank] + Q.partials_offset);
-  double acc = 0;
-  if (tid < SH_BINS)
-    for (int k = tid; k < Q.logical_grid; k += SH_BINS) acc += __ldcv(partials + k);
   const double total = block_sum128_first_warps(acc, s_warp);
   if (tid == 0) s_warp[0] = total;
   if (pre_rng) {
-    for (int k = tid; k < np; k += nthreads) s_z[k] = __ldcg(Q.st->pre_z + k);
+    for (int k = tid; k < np; k += SH_THREADS) s_z[k] = __ldcg(Q.st->pre_z + k);
     if (tid == 0) s_u = __ldcg(&Q.st->pre_u);
   }
   __syncthreads();
   if (tid < 64)
     finish_step2(F, Q.st, np, ns, Q.nsources, s_warp[0], Q.mode, s_term, tid & 31, tid >> 5, pre_rng ? s_z : nullptr,
                  pre_rng ? &s_u : nullptr);
+#undef SH_PHASE
 }
 
 // The logical grid of the unsharded grouped lookup over many bins (launch_nll).
@@ -240,11 +326,10 @@ int launch_nll_sharded(ShardNllParams Q, bool pdl, cudaStream_t stream) {
   Q.lb0 = (int)((long long)Q.logical_grid * Q.W.rank / Q.W.nranks);
   const int lb1 = (int)((long long)Q.logical_grid * (Q.W.rank + 1) / Q.W.nranks);
   if (lb1 <= Q.lb0) { set_error("launch_nll_sharded: fewer logical blocks than ranks"); return SXMC_ESTATE; }
-  const size_t smem = sizeof(unsigned) * (size_t)Q.ns * SH_BINS;
-  if (smem > 48 * 1024)
-    SXMC_CUDA(cudaFuncSetAttribute((const void*)lookup_nll_sharded_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  SXMC_CUDA(launch_kernel_pdl(lookup_nll_sharded_kernel, dim3((unsigned)(lb1 - Q.lb0)), dim3((unsigned)(SH_BINS * Q.W.nranks)), smem,
-                              stream, pdl, Q));
+  const size_t smem = (sizeof(double) + sizeof(unsigned)) * (size_t)Q.ns * SH_BINS;
+  // (static + dynamic shared memory pass 48 KB from 17 signals on: always opt in)
+  SXMC_CUDA(cudaFuncSetAttribute((const void*)lookup_nll_sharded_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SXMC_CUDA(launch_kernel_pdl(lookup_nll_sharded_kernel, dim3((unsigned)(lb1 - Q.lb0)), dim3(SH_THREADS), smem, stream, pdl, Q));
   SXMC_CUDA(cudaGetLastError());
   return SXMC_OK;
 }

@@ -136,7 +136,9 @@ def p2p_status(chain):
 
 
 def p2p_clocks(chain):
-    """(wait, sum, close) nanoseconds the exchange kernel has spent so far, summed over exchanges."""
-    out = (C.c_double * 3)()
+    """(wait, sum, close) nanoseconds the exchange has spent so far, summed over steps -- in the fused form
+    "sum" is the rank-sharded lookup; then four more, block 0 of the fused kernel: peers' counts gathered and
+    constants ready / bins evaluated / block sum / partial sums stored, fenced and ticket taken."""
+    out = (C.c_double * 7)()
     check(lib().sxmc_chain_p2p_clocks(chain._c, out))
     return tuple(out)
