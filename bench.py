@@ -98,8 +98,8 @@ def parse_args(argv=None):
                     help="N>1 sample sharding: histogram exchange by the peer-memory kernel or ncclAllReduce")
     ap.add_argument("--p2p", action="store_true", help="(default; kept for old command lines)")
     ap.add_argument("--p2p-form", type=int, default=0,
-                    help="peer-memory exchange: 0 automatic (reduce-scatter + all-gather above 2 ranks), "
-                         "1 one-shot, 2 two-shot")
+                    help="peer-memory exchange: 0 automatic (fused into a rank-sharded lookup kernel where the fit "
+                         "allows it), 1 one-shot all-reduce kernel, 2 reduce-scatter + all-gather kernel")
     ap.add_argument("--flush", default="auto", choices=["auto", "always", "never"],
                     help="L2 flush (256 MiB memset) before every timed step; auto = only when a step "
                          "streams less than 4x the L2")
@@ -157,8 +157,10 @@ def config_for(args, fit, world):
     if sharded:
         par = ("sample sharding: each of the %d GPUs bins 1/%d of every signal's samples, uint32 histograms "
                "summed every step by %s, one chain" %
-               (world, world, "one peer-memory kernel (NVLink P2P loads/stores)" if args.exchange == "p2p"
-                else "ncclAllReduce"))
+               (world, world, ("the lookup kernel itself, which is dealt over the GPUs: it reads its bins' partial counts "
+                               "from every GPU's memory over NVLink and exchanges partial sums, not histograms"
+                               if args.p2p_form in (0, 3) else "one peer-memory all-reduce kernel (NVLink P2P loads/stores)")
+                if args.exchange == "p2p" else "ncclAllReduce"))
     elif world > 1:
         par = "%d independent chains, one per GPU (ensemble sharding), no collective" % world
     else:
@@ -686,23 +688,29 @@ def run_own_arm(args, rank, world, local):
     }
 
     # N > 1: the other exchange on the same sharded samples, nested
+    # (p2p_allreduce: the peer-memory all-reduce kernel + the replicated lookup, i.e. the step without
+    # the fusion; nccl: ncclAllReduce in its place)
     if sharded and not args.no_extra:
-        other = "nccl" if args.exchange == "p2p" else "p2p"
-        try:
-            close_chain(chain, comm)
-            from sxmc_b200 import mcmc, pdfz
-            pdfz.set_bin_tuning(p2p_form=args.p2p_form)
-            _, chain = mcmc.build_fit(fit_local, hists=hists)
-            comm = attach_exchange(chain, other, args, rank, world, local)
-            r2 = measure_chain(fit, fit_local, hists, chain, args, rank, comm, flush, do_e2e=False,
-                               repeats=max(3, r["repeats"] // 3))
-            s2 = allreduce_max(r2["value_ms"])
-            line["exchange_" + other] = {
-                "steps_per_s": K / (s2 * 1e-3), "ms_per_step": s2 / K,
-                "allreduce_ms_per_step": r2["comm_ms"] / K,
-                "chain_back_to_back_steps_per_s": K / (allreduce_max(r2["warm_ms"]) * 1e-3)}
-        except Exception as e:
-            line["exchange_" + other] = {"error": repr(e)}
+        from sxmc_b200 import mcmc, pdfz
+        others = ["nccl", "p2p_allreduce"] if (args.exchange == "p2p" and args.p2p_form in (0, 3)) else \
+                 (["nccl"] if args.exchange == "p2p" else ["p2p"])
+        for other in others:
+            try:
+                close_chain(chain, comm)
+                pdfz.set_bin_tuning(p2p_form=(2 if world > 2 else 1) if other == "p2p_allreduce" else args.p2p_form)
+                _, chain = mcmc.build_fit(fit_local, hists=hists)
+                pdfz.set_bin_tuning()
+                comm = attach_exchange(chain, "p2p" if other == "p2p_allreduce" else other, args, rank, world, local)
+                r2 = measure_chain(fit, fit_local, hists, chain, args, rank, comm, flush, do_e2e=False,
+                                   repeats=max(3, r["repeats"] // 3))
+                s2 = allreduce_max(r2["value_ms"])
+                line["exchange_" + other] = {
+                    "steps_per_s": K / (s2 * 1e-3), "ms_per_step": s2 / K,
+                    "allreduce_ms_per_step": r2["comm_ms"] / K,
+                    "kernels_ms_per_step": {"bin": r2["bin_ms"] / K, "lookup_nll_metropolis": r2["nll_ms"] / K},
+                    "chain_back_to_back_steps_per_s": K / (allreduce_max(r2["warm_ms"]) * 1e-3)}
+            except Exception as e:
+                line["exchange_" + other] = {"error": repr(e)}
     close_chain(chain, comm)
     for h in hists:
         h.close()

@@ -26,7 +26,7 @@ struct Tuning {
   int blocks_per_sm = 0;           // generic kernel: <= 0 occupancy maximum
   int force_generic = 0;           // the per-sample interpreter for everything
   int force_dynamic = 0;           // fast kernel with run-time systematic dispatch only
-  int p2p_form = 0;                // peer-memory all-reduce: 0 automatic (two-shot above 2 ranks), 1 one-shot, 2 two-shot
+  int p2p_form = 0;                // peer-memory exchange: 0 automatic (fused into the rank-sharded lookup where the fit allows it, else two-shot above 2 ranks), 1 one-shot all-reduce kernel, 2 two-shot
   int no_mono = 0;                 // never take the monotone endpoint path (tests)
   int no_jit = 0;                  // programs outside the build's table keep the run-time dispatching kernel
   int cta_split = 0;               // measurement knob of the fast binning kernel: 0 production (chunks dealt to a CTA's warps round robin; global-memory histograms: warps independent of each other), 1 one contiguous range per warp inside per-CTA segments (the round-1 form), 2 global histograms: one contiguous range per warp of the grid, 3 global histograms: per-CTA segments, round robin

@@ -14,9 +14,9 @@
 //   * four threads per bin then evaluate eval_pdf's division and nll_event_chunks' product for the
 //     bin's signals, and one of them adds the products in signal order: the arithmetic, the order
 //     of additions and the block reduction of lookup_nll_kernel<128>;
-//   * the block's partial sum goes to slot [logical block] of EVERY rank's partial array (N
-//     tagged stores of 16 bytes instead of an all-gather of the histograms);
-//   * the rank's last block collects the G partial sums as they arrive, totals them in the order the
+//   * the block's sum goes to slot [logical block] of EVERY rank's partial array (N tagged stores
+//     of 16 bytes instead of an all-gather of the histograms);
+//   * the rank's last block collects the G sums as they arrive, totals them in the order the
 //     unsharded kernel's last block uses and finishes the step (nll_total, jump_decider,
 //     pick_new_vector: finish_step2) -- on every rank alike.
 // Every rank therefore takes the decision the unsharded chain takes, bit for bit, for any N
@@ -31,6 +31,8 @@
 // its peers read b^1 during step s-1 and this rank had their sums of s-1 before it left step s-1.  A
 // peer's sums of step s+1 cannot overwrite those of step s unread: the peer needs this rank's
 // [p][r] = s+1 first, which this rank's NEXT launch publishes.
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "nll_device.cuh"
@@ -38,37 +40,65 @@
 
 namespace sxmc {
 
-constexpr int SH_BINS = 128;             // bins per logical block == threads of lookup_nll_kernel<128>
+constexpr int LB_BINS = 128;             // bins per logical block == threads of lookup_nll_kernel<128>
+constexpr int WARPS_PER_LB = LB_BINS / 32;
+// A physical block stands for one logical block, four threads per bin.  (Measured and dropped:
+// physical blocks of 32 bins -- one warp of the logical block each, four times as many blocks and
+// SMs reading over NVLink, warp sums exchanged: the gather took 15 us instead of 11 at 8 GPUs;
+// profiles/r02_bench_D_sharded_8gpu_fused_v2_32bin_blocks.json.)
+constexpr int PB_BINS = LB_BINS;
+constexpr int PB_THREADS = 4 * PB_BINS;
+constexpr int SH_GATHER = 16;            // 128-bit peer loads in flight per thread
 constexpr int SH_MAX_SIGNALS = 128;
 
-// block_sum<128> (nll_device.cuh) executed by the first four warps of a larger block: the same
-// shuffle tree, the same order over the warp sums.  Result valid on thread 0.
+// one tagged partial sum: {low half, step, high half, step} -- see the store below
+__device__ __forceinline__ void st_tagged(unsigned* slot, double v, unsigned seq) {
+  const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(slot), "r"((unsigned)bits), "r"(seq) : "memory");
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(slot + 2), "r"((unsigned)(bits >> 32)), "r"(seq) : "memory");
+}
+// spin until both halves carry `seq`; false on abort / timeout
+__device__ __forceinline__ bool ld_tagged(const unsigned* slot, unsigned seq, const P2PParams& W,
+                                          unsigned long long t_start, double& v) {
+  unsigned lo, hi, f0, f1, n = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(f0) : "l"(slot) : "memory");
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(hi), "=r"(f1) : "l"(slot + 2) : "memory");
+    if (f0 == seq && f1 == seq) break;
+    if ((++n & 63u) == 0) {
+      if (*(volatile unsigned*)W.abort_flag) return false;
+      if (globaltimer_ns() - t_start > W.peer_timeout_ns) { atomicExch(W.abort_flag, 1u); return false; }
+    }
+  }
+  v = __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+  return true;
+}
+
+// block_sum<128> (nll_device.cuh) executed by the first four warps of a block: the same shuffle
+// tree, the same order over the warp sums.  Result valid on thread 0.
 __device__ __forceinline__ double block_sum128_first_warps(double v, double* s_warp) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (warp < SH_BINS / 32) {
+  if (warp < WARPS_PER_LB) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
   }
   __syncthreads();
-  if (warp < SH_BINS / 32 && lane == 0) s_warp[warp] = v;
+  if (warp < WARPS_PER_LB && lane == 0) s_warp[warp] = v;
   __syncthreads();
   double t = 0;
   if (threadIdx.x == 0)
-    for (int w = 0; w < SH_BINS / 32; ++w) t += s_warp[w];
+    for (int w = 0; w < WARPS_PER_LB; ++w) t += s_warp[w];
   return t;
 }
 
-constexpr int SH_THREADS = 512;          // 4 threads per bin of the logical block
-constexpr int SH_GATHER = 16;            // 128-bit peer loads in flight per thread
-
-__global__ void __launch_bounds__(SH_THREADS)
+__global__ void __launch_bounds__(PB_THREADS)
 lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
-  extern __shared__ double s_dyn[];                       // [ns][128] products, then [ns][128] counts
+  extern __shared__ double s_dyn[];                       // [ns][32] products, then [ns][32] counts
   __shared__ double s_c[SH_MAX_SIGNALS];
   __shared__ double s_bn[SH_MAX_SIGNALS];
   __shared__ unsigned s_norm[SH_MAX_SIGNALS];
-  __shared__ unsigned s_m[SH_BINS];
-  __shared__ double s_warp[SH_BINS / 32];
+  __shared__ unsigned s_m[PB_BINS];
+  __shared__ double s_warp[WARPS_PER_LB];
   __shared__ double s_term[SH_MAX_SIGNALS + SXMC_MAX_PARAMETERS];
   __shared__ int s_ok, s_last;
   __shared__ FinState F;
@@ -77,10 +107,10 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
 
   const P2PParams& W = Q.W;
   const int tid = threadIdx.x;
-  const int t = tid & (SH_BINS - 1), kq = tid / SH_BINS;  // evaluation: bin of the block, quarter of the signals
+  const int t = tid & (PB_BINS - 1), kq = tid / PB_BINS;  // evaluation: bin of the block, quarter of the signals
   const int ns = Q.ns, np = Q.np, nb = Q.nbins, nr = W.nranks;
-  double* const s_prod = s_dyn;                                            // [ns][128]
-  unsigned* const s_cnt = reinterpret_cast<unsigned*>(s_dyn + (size_t)ns * SH_BINS);   // [ns][128]
+  double* const s_prod = s_dyn;                                            // [ns][32]
+  unsigned* const s_cnt = reinterpret_cast<unsigned*>(s_dyn + (size_t)ns * PB_BINS);   // [ns][32]
   const int lb = Q.lb0 + blockIdx.x;                      // logical block of the unsharded grid
   const unsigned seq = *W.seq + 1u;
   unsigned long long* const clk = reinterpret_cast<unsigned long long*>(W.seq + 4);
@@ -95,21 +125,21 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
   } while (0)
 
   // ---- prologue independent of this step's histograms (overlaps the binning kernel's tail) ----
-  prefetch_state(F, Q.st, np, tid, SH_THREADS);
+  prefetch_state(F, Q.st, np, tid, PB_THREADS);
   NllSignal my_sig;
   if (tid < ns) my_sig = Q.sigs[tid];
-  const long long gstride = (long long)Q.logical_grid * SH_BINS;
-  long long b0 = (long long)lb * SH_BINS;
-  if (tid < SH_BINS) s_m[tid] = (b0 + tid < nb) ? Q.mult[b0 + tid] : 0u;   // events per bin: static data
-  for (unsigned long long w = blockIdx.x * (unsigned long long)SH_THREADS + tid; w < Q.zero_words;
-       w += (unsigned long long)gridDim.x * SH_THREADS)
+  const long long gstride = (long long)Q.logical_grid * LB_BINS;
+  long long b0 = (long long)lb * LB_BINS;
+  if (tid < PB_BINS) s_m[tid] = (b0 + tid < nb) ? Q.mult[b0 + tid] : 0u;   // events per bin: static data
+  for (unsigned long long w = blockIdx.x * (unsigned long long)PB_THREADS + tid; w < Q.zero_words;
+       w += (unsigned long long)gridDim.x * PB_THREADS)
     Q.zero_ptr[w] = 0u;                                   // the buffer step s+1 bins into (header)
-  for (int k = tid; k < ns * SH_BINS; k += SH_THREADS) s_cnt[k] = 0u;
+  for (int k = tid; k < ns * PB_BINS; k += PB_THREADS) s_cnt[k] = 0u;
   if (tid < ns) s_norm[tid] = 0u;
   pdl_wait();
   pdl_trigger();
 
-  // ---- round 1: my partial is complete (the binning kernel has finished); wait for everyone's ----
+  // ---- my partial is complete (the binning kernel has finished): say so, wait for everyone's ----
   if (blockIdx.x == 0 && tid < nr) {
     if (tid == 0) t0 = globaltimer_ns();
     __threadfence_system();
@@ -129,50 +159,51 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
   const size_t poff = (size_t)W.parity * W.pitch;
 
   const bool pre_rng = pre_rng_applies(F, Q.mode);
-  if (pre_rng && blockIdx.x == 0 && tid >= SH_THREADS - 32) pre_rng_draw(F, np, tid & 31, Q.st->pre_z, &Q.st->pre_u);
+  if (pre_rng && blockIdx.x == 0 && tid >= PB_THREADS - 32) pre_rng_draw(F, np, tid & 31, Q.st->pre_z, &Q.st->pre_u);
 
   double sum = 0;
   bool first = true;
   for (; b0 < nb; b0 += gstride) {
     if (!first) {                           // (more than 148 x 8 x 128 bins: several bins per thread)
       __syncthreads();
-      for (int k = tid; k < ns * SH_BINS; k += SH_THREADS) s_cnt[k] = 0u;
-      if (tid < SH_BINS) s_m[tid] = (b0 + tid < nb) ? Q.mult[b0 + tid] : 0u;
+      for (int k = tid; k < ns * PB_BINS; k += PB_THREADS) s_cnt[k] = 0u;
+      if (tid < PB_BINS) s_m[tid] = (b0 + tid < nb) ? Q.mult[b0 + tid] : 0u;
       __syncthreads();
     }
-    // ---- gather: the peers' counts of the block's 128 bins, every signal, ONE NVLink round trip:
+    // ---- gather: the peers' counts of the block's 32 bins, every signal, ONE NVLink round trip:
     // the in-domain counts (first pass) and up to SH_GATHER 128-bit loads per thread are issued
     // before any of them is consumed.  Item i = (quad of bins, peer, signal), peers fastest after
-    // the quad, so neighbouring warps read from different GPUs.
-    unsigned nrm[2] = {0u, 0u};             // (signal, peer) pairs tid and tid + 512: <= 128 x 8 of them
+    // the quad, so neighbouring groups of lanes read from different GPUs.
+    constexpr int NRM = SH_MAX_SIGNALS * P2P_MAX_RANKS / PB_THREADS;     // (signal, peer) pairs per thread
+    unsigned nrm[NRM];
     const bool want_norm = first && ok;
     if (want_norm)
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int k = tid + u * SH_THREADS;
-        if (k < ns * nr) nrm[u] = __ldcv(W.part[k / ns] + poff + (size_t)ns * nb + k % ns);
+      for (int u = 0; u < NRM; ++u) {
+        const int k = tid + u * PB_THREADS;
+        nrm[u] = (k < ns * nr) ? __ldcv(W.part[k / ns] + poff + (size_t)ns * nb + k % ns) : 0u;
       }
-    const int items = 32 * nr * ns;
-    const bool vec = (nb & 3) == 0;
-    if (ok && vec) {
-      for (int i0 = tid; i0 < items; i0 += SH_THREADS * SH_GATHER) {
+    constexpr int QUADS = PB_BINS / 4;
+    const int items = QUADS * nr * ns;
+    if (ok && (nb & 3) == 0) {
+      for (int i0 = tid; i0 < items; i0 += PB_THREADS * SH_GATHER) {
         uint4 x[SH_GATHER];
 #pragma unroll
         for (int u = 0; u < SH_GATHER; ++u) {
-          const int i = i0 + u * SH_THREADS;
+          const int i = i0 + u * PB_THREADS;
           x[u] = make_uint4(0u, 0u, 0u, 0u);
           if (i < items) {
-            const int q = i & 31, pj = i >> 5, pp = pj % nr, j = pj / nr;
+            const int q = i % QUADS, pj = i / QUADS, pp = pj % nr, j = pj / nr;
             const long long b = b0 + 4 * q;
             if (b < nb) x[u] = __ldcv(reinterpret_cast<const uint4*>(W.part[pp] + poff + (size_t)j * nb + b));
           }
         }
 #pragma unroll
         for (int u = 0; u < SH_GATHER; ++u) {
-          const int i = i0 + u * SH_THREADS;
+          const int i = i0 + u * PB_THREADS;
           if (i < items) {
-            const int q = i & 31, j = (i >> 5) / nr;
-            unsigned* dst = s_cnt + j * SH_BINS + 4 * q;
+            const int q = i % QUADS, j = (i / QUADS) / nr;
+            unsigned* dst = s_cnt + j * PB_BINS + 4 * q;
             if (x[u].x) atomicAdd(dst + 0, x[u].x);
             if (x[u].y) atomicAdd(dst + 1, x[u].y);
             if (x[u].z) atomicAdd(dst + 2, x[u].z);
@@ -181,32 +212,32 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
         }
       }
     } else if (ok) {                        // bins per PDF not a multiple of four: 32-bit loads
-      for (int i = tid; i < 128 * nr * ns; i += SH_THREADS) {
-        const int tb = i & 127, pj = i >> 7, pp = pj % nr, j = pj / nr;
+      for (int i = tid; i < PB_BINS * nr * ns; i += PB_THREADS) {
+        const int tb = i % PB_BINS, pj = i / PB_BINS, pp = pj % nr, j = pj / nr;
         if (b0 + tb < nb && s_m[tb]) {
           const unsigned h = __ldcv(W.part[pp] + poff + (size_t)j * nb + b0 + tb);
-          if (h) atomicAdd(s_cnt + j * SH_BINS + tb, h);
+          if (h) atomicAdd(s_cnt + j * PB_BINS + tb, h);
         }
       }
     }
     if (want_norm)
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int k = tid + u * SH_THREADS;
+      for (int u = 0; u < NRM; ++u) {
+        const int k = tid + u * PB_THREADS;
         if (k < ns * nr) atomicAdd(&s_norm[k % ns], nrm[u]);
       }
     __syncthreads();
     if (first) {
-      if (tid < ns) {
-        const int j = tid;
+      for (int j = tid; j < ns; j += PB_THREADS) {
+        const NllSignal sg = (j == tid) ? my_sig : Q.sigs[j];
         const unsigned my_norm = s_norm[j];
-        const float eff = (float)(1.0 * my_norm / my_sig.n_mc);                 // nll_kernels.cpp:105
-        const double rate = __dmul_rn(F.proposed[my_sig.source_id], my_sig.nexpected);
+        const float eff = (float)(1.0 * my_norm / sg.n_mc);                     // nll_kernels.cpp:105
+        const double rate = __dmul_rn(F.proposed[sg.source_id], sg.nexpected);
         s_c[j] = __dmul_rn(rate, (double)eff);
-        s_bn[j] = __dmul_rn((double)my_norm, my_sig.bin_volume);                // pdfz.cpp:417
-        s_term[j] = __dmul_rn(rate, (double)my_norm) / (double)my_sig.n_mc;     // nll_kernels.cpp:167-171
+        s_bn[j] = __dmul_rn((double)my_norm, sg.bin_volume);                    // pdfz.cpp:417
+        s_term[j] = __dmul_rn(rate, (double)my_norm) / (double)sg.n_mc;         // nll_kernels.cpp:167-171
       }
-      for (int i = tid; i < np; i += SH_THREADS) {                              // nll_kernels.cpp:176-185
+      for (int i = tid; i < np; i += PB_THREADS) {                              // nll_kernels.cpp:176-185
         const double sg = F.sigmas[i];
         double x2 = 0;
         if (sg > 0) {
@@ -223,34 +254,29 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
     // each product is rounded on its own, so the sum is the unsharded kernel's, bit for bit
     const unsigned m = s_m[t];
     if (m)
-      for (int j = kq; j < ns; j += SH_THREADS / SH_BINS) {
-        float v = pdf_value(s_cnt[j * SH_BINS + t], s_bn[j]);                    // pdfz.cpp:429-432
+      for (int j = kq; j < ns; j += PB_THREADS / PB_BINS) {
+        float v = pdf_value(s_cnt[j * PB_BINS + t], s_bn[j]);                    // pdfz.cpp:429-432
         if (isnan(v)) v = 0.0f;                                                 // nll_kernels.cpp:107
-        s_prod[j * SH_BINS + t] = __dmul_rn(s_c[j], (double)v);
+        s_prod[j * PB_BINS + t] = __dmul_rn(s_c[j], (double)v);
       }
     __syncthreads();
     if (kq == 0 && m) {
       double sv = 0;
-      for (int j = 0; j < ns; ++j) sv = __dadd_rn(sv, s_prod[j * SH_BINS + t]);
+      for (int j = 0; j < ns; ++j) sv = __dadd_rn(sv, s_prod[j * PB_BINS + t]);
       if (sv > 0) sum += (double)m * log(sv);
     }
     first = false;
   }
   SH_PHASE(5);
-  const double bsum = block_sum128_first_warps(sum, s_warp);
-  SH_PHASE(6);
+  const double bsum = block_sum128_first_warps(sum, s_warp);      // threads (t, 0) are the first four warps
   if (tid == 0) s_bsum = bsum;
   __syncthreads();
-  // The block's partial sum into slot lb of every rank's array, as two 8-byte words that each carry
-  // half of the double AND the step number (the "LL" idiom of the collective libraries: an aligned
-  // 8-byte store arrives whole, so the reader needs no fence and no separate flag -- a word whose
-  // tag is the step's holds that step's data).
-  if (tid < nr && ok) {
-    const unsigned long long bits = (unsigned long long)__double_as_longlong(s_bsum);
-    unsigned* slot = const_cast<unsigned*>(W.part[tid]) + Q.partials_offset + 4ull * lb;
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(slot), "r"((unsigned)bits), "r"(seq) : "memory");
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(slot + 2), "r"((unsigned)(bits >> 32)), "r"(seq) : "memory");
-  }
+  SH_PHASE(6);
+  // The block's sum into slot lb of every rank's array, as two 8-byte words that each carry half of
+  // the double AND the step number (the "LL" idiom of the collective libraries: an aligned 8-byte
+  // store arrives whole, so the reader needs no fence and no separate flag -- a word whose tag is
+  // the step's holds that step's data).
+  if (tid < nr && ok) st_tagged(const_cast<unsigned*>(W.part[tid]) + Q.partials_offset + 4ull * lb, s_bsum, seq);
   if (tid == 0) {                     // elects the block that finishes the step; the fences order block 0's
     __threadfence();                  // pre-drawn random numbers (pre_z, pre_u) before the finisher's loads
     s_last = atomicAdd(W.ticket, 1u) == gridDim.x - 1;
@@ -260,10 +286,9 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
   __syncthreads();
   if (!s_last) return;
 
-  // ---- the rank's last block: collect every logical block's partial sum (own and peers'), total
-  // them in the unsharded kernel's order, finish the step -- on every rank alike.  Holding all G
-  // sums of step s also means every rank is done reading this step's partial histograms (a block
-  // stores its sum after its gather): the buffer-reuse argument of the header.
+  // ---- the rank's last block: collect every logical block's sum (own and peers'), total them in
+  // the unsharded kernel's order, finish the step -- on every rank alike.  Holding all sums of step s also means every rank is done reading this
+  // step's partial histograms (a block stores its sum after its gather): the header's argument.
   unsigned long long t2 = 0;
   if (tid == 0) {
     t2 = globaltimer_ns();
@@ -271,24 +296,41 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
     s_ok = ok ? 1 : 0;
   }
   __syncthreads();
+  // every thread fetches a batch of slots at once (most have arrived), spins only on the late ones
   const unsigned* slots = W.part[W.rank] + Q.partials_offset;
-  double acc = 0;
-  if (tid < SH_BINS && ok) {
+  double* const s_val = s_dyn;                            // [G] (the launch sized the dynamic array for it)
+  const int nslots = Q.logical_grid;
+  if (ok) {
     const unsigned long long tw = globaltimer_ns();
-    for (int k = tid; k < Q.logical_grid; k += SH_BINS) {
-      unsigned lo, hi, f0, f1, n = 0;
-      for (;;) {
-        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(f0) : "l"(slots + 4ull * k) : "memory");
-        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(hi), "=r"(f1) : "l"(slots + 4ull * k + 2) : "memory");
-        if (f0 == seq && f1 == seq) break;
-        if ((++n & 63u) == 0) {
-          if (*(volatile unsigned*)W.abort_flag) { s_ok = 0; break; }
-          if (globaltimer_ns() - tw > W.peer_timeout_ns) { atomicExch(W.abort_flag, 1u); s_ok = 0; break; }
+    constexpr int BATCH = 8;
+    bool good = true;
+    for (int k0 = tid; k0 < nslots && good; k0 += PB_THREADS * BATCH) {
+      uint4 x[BATCH];
+#pragma unroll
+      for (int u = 0; u < BATCH; ++u) {
+        const int k = k0 + u * PB_THREADS;
+        x[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (k < nslots)
+          asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(x[u].x), "=r"(x[u].y), "=r"(x[u].z), "=r"(x[u].w) : "l"(slots + 4ull * k) : "memory");
+      }
+#pragma unroll
+      for (int u = 0; u < BATCH; ++u) {
+        const int k = k0 + u * PB_THREADS;
+        if (k < nslots && good) {
+          double v;
+          if (x[u].y == seq && x[u].w == seq) v = __longlong_as_double((long long)(((unsigned long long)x[u].z << 32) | x[u].x));
+          else good = ld_tagged(slots + 4ull * k, seq, W, tw, v);
+          s_val[k] = v;
         }
       }
-      acc += __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
     }
+    if (!good) s_ok = 0;
   }
+  __syncthreads();
+  double acc = 0;
+  if (s_ok && tid < LB_BINS)
+    for (int k = tid; k < Q.logical_grid; k += LB_BINS) acc += s_val[k];
   __syncthreads();
   if (tid == 0) {
     clk[3] += globaltimer_ns() - t2;
@@ -299,7 +341,7 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
   const double total = block_sum128_first_warps(acc, s_warp);
   if (tid == 0) s_warp[0] = total;
   if (pre_rng) {
-    for (int k = tid; k < np; k += SH_THREADS) s_z[k] = __ldcg(Q.st->pre_z + k);
+    for (int k = tid; k < np; k += PB_THREADS) s_z[k] = __ldcg(Q.st->pre_z + k);
     if (tid == 0) s_u = __ldcg(&Q.st->pre_u);
   }
   __syncthreads();
@@ -311,7 +353,7 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
 
 // The logical grid of the unsharded grouped lookup over many bins (launch_nll).
 int nll_sharded_logical_grid(int nbins) {
-  int grid = (nbins + SH_BINS - 1) / SH_BINS;
+  int grid = (nbins + LB_BINS - 1) / LB_BINS;
   if (grid > 148 * 8) grid = 148 * 8;
   return grid;
 }
@@ -323,13 +365,15 @@ int launch_nll_sharded(ShardNllParams Q, bool pdl, cudaStream_t stream) {
   }
   Q.logical_grid = nll_sharded_logical_grid(Q.nbins);
   if (Q.logical_grid > P2P_PARTIALS_MAX) { set_error("launch_nll_sharded: logical grid exceeds the window's partial array"); return SXMC_ESTATE; }
+  // this rank's contiguous range of logical blocks
   Q.lb0 = (int)((long long)Q.logical_grid * Q.W.rank / Q.W.nranks);
   const int lb1 = (int)((long long)Q.logical_grid * (Q.W.rank + 1) / Q.W.nranks);
   if (lb1 <= Q.lb0) { set_error("launch_nll_sharded: fewer logical blocks than ranks"); return SXMC_ESTATE; }
-  const size_t smem = (sizeof(double) + sizeof(unsigned)) * (size_t)Q.ns * SH_BINS;
+  size_t smem = (sizeof(double) + sizeof(unsigned)) * (size_t)Q.ns * PB_BINS;
+  smem = std::max(smem, sizeof(double) * (size_t)Q.logical_grid);                    // the finisher's slot values
   // (static + dynamic shared memory pass 48 KB from 17 signals on: always opt in)
   SXMC_CUDA(cudaFuncSetAttribute((const void*)lookup_nll_sharded_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  SXMC_CUDA(launch_kernel_pdl(lookup_nll_sharded_kernel, dim3((unsigned)(lb1 - Q.lb0)), dim3(SH_THREADS), smem, stream, pdl, Q));
+  SXMC_CUDA(launch_kernel_pdl(lookup_nll_sharded_kernel, dim3((unsigned)(lb1 - Q.lb0)), dim3(PB_THREADS), smem, stream, pdl, Q));
   SXMC_CUDA(cudaGetLastError());
   return SXMC_OK;
 }
