@@ -93,7 +93,7 @@ __device__ __forceinline__ double block_sum128_first_warps(double v, double* s_w
 
 __global__ void __launch_bounds__(PB_THREADS)
 lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
-  extern __shared__ double s_dyn[];                       // [ns][32] products, then [ns][32] counts
+  extern __shared__ double s_dyn[];                       // [ns][128] products, then [ns][128] counts
   __shared__ double s_c[SH_MAX_SIGNALS];
   __shared__ double s_bn[SH_MAX_SIGNALS];
   __shared__ unsigned s_norm[SH_MAX_SIGNALS];
@@ -109,8 +109,8 @@ lookup_nll_sharded_kernel(const __grid_constant__ ShardNllParams Q) {
   const int tid = threadIdx.x;
   const int t = tid & (PB_BINS - 1), kq = tid / PB_BINS;  // evaluation: bin of the block, quarter of the signals
   const int ns = Q.ns, np = Q.np, nb = Q.nbins, nr = W.nranks;
-  double* const s_prod = s_dyn;                                            // [ns][32]
-  unsigned* const s_cnt = reinterpret_cast<unsigned*>(s_dyn + (size_t)ns * PB_BINS);   // [ns][32]
+  double* const s_prod = s_dyn;                                            // [ns][128]
+  unsigned* const s_cnt = reinterpret_cast<unsigned*>(s_dyn + (size_t)ns * PB_BINS);   // [ns][128]
   const int lb = Q.lb0 + blockIdx.x;                      // logical block of the unsharded grid
   const unsigned seq = *W.seq + 1u;
   unsigned long long* const clk = reinterpret_cast<unsigned long long*>(W.seq + 4);
