@@ -373,17 +373,30 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     const unsigned long long ca = rr ? (t0 - jbeg) + (unsigned)warp : (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
     const unsigned long long cb = rr ? (tend - jbeg) : (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
 
-    auto issue = [&](unsigned long long c, unsigned slot) {   // lane 0 only
-      const unsigned bar = my_bar0 + 8u * slot;
-      const unsigned dst = my_stage0 + slot * stage_bytes;
+    // (stage, parity) of chunk `it` kept as counters: it % S and it / S would be two integer
+    // divisions per chunk in a kernel that is short of issue slots
+    unsigned slot = it % (unsigned)S, par = (it / (unsigned)S) & 1u;
+    // lane 0's issue cursor: the next chunk to request and its byte offset inside every column
+    unsigned long long ci = ca, ci_off = ca * col_bytes;
+    const unsigned long long step_bytes = (unsigned long long)cstep * col_bytes;
+    auto issue = [&](unsigned sl) {   // lane 0 only
+      const unsigned bar = my_bar0 + 8u * sl;
+      const unsigned dst = my_stage0 + sl * stage_bytes;
       mbar_expect_tx(bar, stage_bytes);
 #pragma unroll
-      for (int k = 0; k < NS; ++k) bulk_g2s(dst + k * col_bytes, col[k] + c * col_bytes, col_bytes, bar);
+      for (int k = 0; k < NS; ++k) bulk_g2s(dst + k * col_bytes, col[k] + ci_off, col_bytes, bar);
+      ci += cstep;
+      ci_off += step_bytes;
     };
     // first thing in the segment: get the copies going (everything they need is in the
     // constant bank); the parameter loads and the histogram clear overlap with them
-    if (lane == 0 && !reuse)
-      for (unsigned i = 0; i < (unsigned)S && ca + i * cstep < cb; ++i) issue(ca + i * cstep, (it + i) % (unsigned)S);
+    if (lane == 0 && !reuse) {
+      unsigned sl = slot;
+      for (unsigned i = 0; i < (unsigned)S && ci < cb; ++i) {
+        issue(sl);
+        if (++sl == (unsigned)S) sl = 0;
+      }
+    }
 
     // Programmatic dependent launch: everything above (barriers, the first bulk copies of the
     // sample columns) ran while the previous kernel of the stream -- the step before's lookup --
@@ -426,8 +439,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     acc.cnt = 0;
 #pragma unroll 1
     for (unsigned long long c = ca; c < cb; c += cstep, ++it) {
-      const unsigned slot = it % (unsigned)S;
-      mbar_wait(my_bar0 + 8u * slot, (it / (unsigned)S) & 1u);
+      mbar_wait(my_bar0 + 8u * slot, par);
       if (xseg == 0 && c == ca) BIN_XDBG(2, threadIdx.x == 0);
       const unsigned src = my_stage0 + slot * stage_bytes + (unsigned)lane * 16u;
 #pragma unroll 1
@@ -459,7 +471,8 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
         run_push4<SMEM>(acc, bq, hist, geo.total_nbins);
       }
       __syncwarp();                       // every lane has read the stage before it is refilled
-      if (lane == 0 && !reuse && c + (unsigned)S * cstep < cb) issue(c + (unsigned)S * cstep, slot);
+      if (lane == 0 && !reuse && ci < cb) issue(slot);
+      if (++slot == (unsigned)S) { slot = 0; par ^= 1u; }
     }
     run_flush<SMEM>(acc, hist, geo.total_nbins);
     BIN_DBG(2);
@@ -572,7 +585,7 @@ __device__ __forceinline__ void fast_bin_pass_warp(const FastParams& P, const Fa
     if (lane == 0 && wnorm) atomicAdd(P.job[jc].norm, wnorm);
     acc.norm = 0; acc.cur = -1; acc.cnt = 0;
   };
-  unsigned it = 0;
+  unsigned it = 0, slot = 0, par = 0;      // (stage, parity) as counters, not it % S and it / S
 #pragma unroll 1
   for (unsigned long long tc = t0; tc < t1; tc += tstep, ++it) {
     if (tc >= jc_end) {                                // this warp enters a (new) signal
@@ -596,8 +609,7 @@ __device__ __forceinline__ void fast_bin_pass_warp(const FastParams& P, const Fa
       }
       gbins = job.bins;
     }
-    const unsigned slot = it % (unsigned)S;
-    mbar_wait(my_bar0 + 8u * slot, (it / (unsigned)S) & 1u);
+    mbar_wait(my_bar0 + 8u * slot, par);
     if (xd && it == 0 && threadIdx.x == 0) {
       unsigned long long t_;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
@@ -634,6 +646,7 @@ __device__ __forceinline__ void fast_bin_pass_warp(const FastParams& P, const Fa
     }
     __syncwarp();                       // every lane has read the stage before it is refilled
     if (lane == 0 && ti < t1) issue(slot);
+    if (++slot == (unsigned)S) { slot = 0; par ^= 1u; }
   }
   close_job();
   if (xd && lane == 0) {
