@@ -162,6 +162,25 @@ int sxmc_nll_eval(const float* lut_dev, size_t nevents, size_t nsignals,
                   const double* nexpected_dev, const unsigned* n_mc_dev,
                   const short* source_id_dev, const unsigned* norms_dev,
                   double* nll_out_host, double* event_sum_out_host);
+/* The same operation for callers that must not allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * A multi-block variant of the kernel behind sxmc_nll_eval whose scratch (per-block
+ * partial sums + a ticket, 9.5 KB) is a file-scope device array every GPU that loads the library holds
+ * until exit; the call issues one 256-byte cudaMemsetAsync and one kernel on `cuda_stream` (a
+ * cudaStream_t; NULL = the default stream), calls no cudaMalloc / cudaFree / allocating routine and does
+ * not synchronise.  All pointers are DEVICE pointers, the output too: out2_dev[0] = nll, out2_dev[1] =
+ * the event sum, valid once the stream reaches that point.  Limits (beyond them: SXMC_EINVAL with a
+ * message, nothing launched): nsignals <= 128, nparameters <= SXMC_MAX_PARAMETERS, nevents <= 2^31.
+ * The scratch is shared by every call on a device and keeps the last call's contents (the ticket is
+ * cleared at the start of each call): calls that OVERLAP on the GPU race -- serialise them on one
+ * stream or with events.  Same arithmetic as sxmc_nll_eval per event; the event sum is reduced over more
+ * blocks, so the two agree to rounding (<= 1e-12 relative), not bit for bit. */
+int sxmc_nll_eval_noalloc(const float* lut_dev, size_t nevents, size_t nsignals,
+                          const double* pars_dev, size_t nparameters, size_t nsources,
+                          const double* means_dev, const double* sigmas_dev,
+                          const double* nexpected_dev, const unsigned* n_mc_dev,
+                          const short* source_id_dev, const unsigned* norms_dev,
+                          double* out2_dev, void* cuda_stream);
 
 /* ---- MCMC (src/mcmc.h:36-138) ------------------------------------------------------- */
 typedef struct {

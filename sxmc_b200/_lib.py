@@ -80,6 +80,8 @@ SYMBOLS = {
     "sxmc_jit_compile_check": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, C.POINTER(_SIZE)]),
     "sxmc_nll_eval": (C.c_int, [c_vp, _SIZE, _SIZE, c_vp, _SIZE, _SIZE, c_vp, c_vp, c_vp, c_vp,
                                 c_vp, c_vp, c_dp, c_dp]),
+    "sxmc_nll_eval_noalloc": (C.c_int, [c_vp, _SIZE, _SIZE, c_vp, _SIZE, _SIZE, c_vp, c_vp, c_vp, c_vp,
+                                        c_vp, c_vp, c_vp, c_vp]),
     "sxmc_chain_create": (C.c_int, [C.POINTER(ChainConfig), C.POINTER(c_vp)]),
     "sxmc_chain_destroy": (C.c_int, [c_vp]),
     "sxmc_chain_set_seed": (C.c_int, [c_vp, C.c_uint64, C.c_uint64]),
