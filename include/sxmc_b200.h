@@ -124,8 +124,11 @@ int sxmc_hist_prepare(sxmc_hist* h);
  * bits 8-9 = how the fast binning kernel deals its chunks (0 production: a CTA's range dealt to its
  * warps round robin, global-memory histograms with warps independent of each other; 1 one contiguous
  * range per warp inside per-CTA segments; 2 global histograms, one contiguous range per warp of the
- * grid; 3 global histograms by per-CTA segments) -- used by the parity tests and measurements to
- * cover every path. */
+ * grid; 3 global histograms by per-CTA segments), bits 10-11 = pipeline chunks of the fast binning
+ * kernel (0 automatic: four rows per chunk and 12 warps for launches that stream >= 1 GiB into
+ * global-memory histograms of <= 65536 bins, two rows and 16 warps otherwise; 1 always two rows;
+ * 2 four rows wherever two such stages fit) -- used by the parity tests and measurements to cover
+ * every path. */
 int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int kernel_select);
 /* device time (ms) of the last batched binning launch / last nll launch, from CUDA events
  * recorded on the launching stream when timing is enabled. */

@@ -279,6 +279,7 @@ int plan_chain_batch(const BinLaunch& L0, int nchains, BatchPlan* plan) {
   if (nchains > sms) { set_error("chain batch: more chains than SMs"); return SXMC_EINVAL; }
   for (int group = BATCH_MAX_GROUP; group >= 1; group >>= 1) {
     BinLaunch L = L0;
+    L.nwarps = FAST_WARPS;        // the batch kernel runs full CTAs; its pipeline is re-planned below
     if (!bin_fast_plan(L.nslots, group * L.max_total_nbins, BK_STATIC_RESERVE, &L.rows_per_stage, &L.nstages,
                        &L.stage_off, &L.smem_bytes))
       continue;

@@ -369,9 +369,10 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
     // this warp's chunks ca, ca + cstep, ... < cb of the job (chunk c starts at byte c * col_bytes)
     const unsigned long long n = tend - t0;
     const bool rr = P.cta_split != 1;   // chunks dealt to the warps round robin (1: contiguous, measurement)
-    const unsigned cstep = rr ? FAST_WARPS : 1u;
-    const unsigned long long ca = rr ? (t0 - jbeg) + (unsigned)warp : (t0 - jbeg) + n * (unsigned)warp / FAST_WARPS;
-    const unsigned long long cb = rr ? (tend - jbeg) : (t0 - jbeg) + n * (unsigned)(warp + 1) / FAST_WARPS;
+    const unsigned NW = (unsigned)P.nwarps;   // == blockDim.x / 32
+    const unsigned cstep = rr ? NW : 1u;
+    const unsigned long long ca = rr ? (t0 - jbeg) + (unsigned)warp : (t0 - jbeg) + n * (unsigned)warp / NW;
+    const unsigned long long cb = rr ? (tend - jbeg) : (t0 - jbeg) + n * (unsigned)(warp + 1) / NW;
 
     // (stage, parity) of chunk `it` kept as counters: it % S and it / S would be two integer
     // divisions per chunk in a kernel that is short of issue slots
@@ -411,7 +412,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
       sr.onep = __dadd_rn(1.0, sr.c0);
     }
     if (SMEM)
-      for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) s_hist[b] = 0;
+      for (int b = threadIdx.x; b < geo.total_nbins; b += blockDim.x) s_hist[b] = 0;
     __syncthreads();
     BIN_DBG(1);
     if (xseg < 4) BIN_XDBG(4 + 3 * xseg, threadIdx.x == 0);
@@ -490,7 +491,7 @@ __device__ __forceinline__ void fast_bin_pass(const FastParams& P, FastCtx& cx, 
       *s_norm = 0u;
     }
     if (SMEM) {
-      for (int b = threadIdx.x; b < geo.total_nbins; b += FAST_THREADS) {
+      for (int b = threadIdx.x; b < geo.total_nbins; b += blockDim.x) {
         const unsigned cnt = s_hist[b];
         if (cnt) atomicAdd(job_bins + b, cnt);
       }
@@ -533,9 +534,9 @@ __device__ __forceinline__ void fast_bin_pass_warp(const FastParams& P, const Fa
   if (P.cta_split == 0) {
     t0 = total * blockIdx.x / gridDim.x + (unsigned)warp;
     t1 = total * (blockIdx.x + 1ull) / gridDim.x;
-    tstep = FAST_WARPS;
+    tstep = (unsigned)P.nwarps;
   } else {
-    const unsigned long long nw = (unsigned long long)gridDim.x * FAST_WARPS, w = (unsigned long long)blockIdx.x * FAST_WARPS + warp;
+    const unsigned long long nw = (unsigned long long)gridDim.x * P.nwarps, w = (unsigned long long)blockIdx.x * P.nwarps + warp;
     t0 = total * w / nw;
     t1 = total * (w + 1ull) / nw;
     tstep = 1;

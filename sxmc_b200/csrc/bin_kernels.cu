@@ -144,6 +144,31 @@ bool bin_fast_plan(int nslots, int hist_bins, size_t static_reserve, int* R_out,
   return false;
 }
 
+// The same with chunks of FOUR rows for launches that stream a gigabyte or more: per chunk a warp
+// spends ~130 instructions on pipeline bookkeeping (barrier wait, expect-tx, one bulk copy per column,
+// cursor) whatever the chunk holds, and the kernel is short of issue slots, not of bytes in flight
+// -- 2 stages of 4 rows keep as many bytes in flight as 3-4 stages of 2.  16 warps when two such
+// stages fit beside the histogram, else 12 (D's four columns: 12 x 2 x 4 x 4 x 512 B = 192 KB;
+// measured 299 -> 275 us per step on a power-capped box, where the ~13 % fewer instructions also mean
+// higher clocks; plan_launch says where it is taken; profiles/r02_bin_chunk_rows_ab.txt).
+bool bin_fast_plan_big(int nslots, int hist_bins, size_t static_reserve, int* nwarps_out, int* R_out, int* S_out,
+                       unsigned* stage_off_out, size_t* smem_out) {
+  const size_t limit = 227 * 1024 - static_reserve;
+  const size_t hist = ((size_t)hist_bins * sizeof(unsigned) + 127) & ~(size_t)127;
+  if (hist >= limit) return false;
+  const int R = 4;
+  for (int nw = FAST_WARPS; nw >= 12; nw -= 4) {
+    const size_t per_stage = (size_t)nw * nslots * R * 512;
+    int S = (int)((limit - hist) / per_stage);
+    if (S > 3) S = 3;
+    if (S >= 2) {
+      *nwarps_out = nw; *R_out = R; *S_out = S; *stage_off_out = (unsigned)hist; *smem_out = hist + per_stage * S;
+      return true;
+    }
+  }
+  return false;
+}
+
 static int g_num_sms = 0;
 static int num_sms() {
   if (!g_num_sms) {
@@ -163,6 +188,7 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
   }
   P.geo.total_nbins = L.max_total_nbins;
   P.R = L.rows_per_stage; P.S = L.nstages; P.stage_off = L.stage_off; P.njobs = ng;
+  P.nwarps = L.nwarps > 0 ? L.nwarps : FAST_WARPS;
   unsigned long long total = 0;
   P.prefix[0] = 0;
   for (int j = 0; j < ng; ++j) {
@@ -187,7 +213,7 @@ void build_fast_params(const BinLaunch& L, int g0, int ng, int grid, FastParams&
   P.cta_split = 0;
   int nonempty = 0;
   for (int j = 0; j < ng; ++j) nonempty += P.prefix[j + 1] > P.prefix[j];
-  if (total > 0 && nonempty <= grid && total / ((unsigned long long)grid * FAST_WARPS) < 32) {
+  if (total > 0 && nonempty <= grid && total / ((unsigned long long)grid * P.nwarps) < 32) {
     int cta[FAST_MAX_JOBS];
     int used = 0;
     for (int j = 0; j < ng; ++j) {
@@ -237,7 +263,8 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
       if (total == 0) continue;
       // one persistent CTA per SM; at least one chunk per warp
       unsigned long long grid = (unsigned long long)num_sms();
-      const unsigned long long max_grid = (total + FAST_WARPS - 1) / FAST_WARPS;
+      const unsigned nwarps = (unsigned)(L.nwarps > 0 ? L.nwarps : FAST_WARPS);
+      const unsigned long long max_grid = (total + nwarps - 1) / nwarps;
       if (grid > max_grid) grid = max_grid;
       build_fast_params(L, g0, ng, (int)grid, P, &total);
       P.xdbg = g_bin_xdbg;
@@ -247,7 +274,7 @@ int launch_bin(const BinLaunch& L, cudaStream_t stream) {
         const int rc = jit_launch_bin(jk, (unsigned)grid, L.smem_bytes, stream, pdl, P);
         if (rc) return rc;
       } else {
-        SXMC_CUDA(launch_kernel_pdl(fk, dim3((unsigned)grid), dim3(FAST_THREADS), L.smem_bytes, stream, pdl, P));
+        SXMC_CUDA(launch_kernel_pdl(fk, dim3((unsigned)grid), dim3(nwarps * 32u), L.smem_bytes, stream, pdl, P));
       }
     }
     return SXMC_OK;

@@ -154,6 +154,15 @@ int fill_job(sxmc_hist* h, BinJob& job, unsigned* bins, unsigned* norm, const do
   return SXMC_OK;
 }
 
+// Four-row chunks (bin_fast_plan_big) are taken where they were measured to win: launches that stream
+// a gigabyte or more into global-memory histograms of moderate size -- workload D on one GPU, 299 ->
+// 275 us per step.  Not below (half of D: 153.0 -> 154.6 us, an eighth: 58.3 -> 61.1), not with a
+// shared-memory histogram (C: 195 -> 205 us: two stages of four rows pipeline worse than four of two
+// at 16 warps), not with 200 000 bins (311 -> 322 us: 12 warps hide the reductions' latency worse).
+// profiles/r02_bin_chunk_rows_ab.txt
+static const unsigned long long BIG_CHUNK_MIN_BYTES = 1ull << 30;
+static const int BIG_CHUNK_MAX_BINS = 65536;
+
 // Decide the launch shape for a filled batch of n jobs.
 void plan_launch(Batch& b, int n, const Tuning& T) {
   BinLaunch& L = b.launch;
@@ -195,6 +204,18 @@ void plan_launch(Batch& b, int n, const Tuning& T) {
       L.smem_hist = false;
       bin_fast_plan(max_slots, 0, BIN_STATIC_RESERVE, &L.rows_per_stage, &L.nstages, &L.stage_off,
                     &L.smem_bytes);
+    }
+    L.nwarps = FAST_WARPS;
+    // launches that stream hundreds of megabytes: chunks of four rows (bin_fast_plan_big)
+    unsigned long long stream_bytes = 0;
+    for (int j = 0; j < n; ++j) stream_bytes += b.host[j].nwtiles * (unsigned long long)WT_SAMPLES * 4ull * max_slots;
+    const bool want_big = T.chunk_form == 2 || (T.chunk_form == 0 && !L.smem_hist && stream_bytes >= BIG_CHUNK_MIN_BYTES &&
+                                                max_bins <= BIG_CHUNK_MAX_BINS);
+    if (want_big) {
+      int nw = 0, R = 0, S = 0; unsigned off = 0; size_t sm = 0;
+      if (bin_fast_plan_big(max_slots, L.smem_hist ? max_bins : 0, BIN_STATIC_RESERVE, &nw, &R, &S, &off, &sm)) {
+        L.nwarps = nw; L.rows_per_stage = R; L.nstages = S; L.stage_off = off; L.smem_bytes = sm;
+      }
     }
     // every job of a fast launch uses the same slot count (columns it does not need are
     // simply re-reads of observable 0)
@@ -319,6 +340,7 @@ int sxmc_set_bin_tuning(int smem_hist_max_bins, int blocks_per_sm, int force_gen
   g_tune.no_pdl = (force_generic >> 6) & 1;
   g_tune.no_jit = (force_generic >> 7) & 1;
   g_tune.cta_split = (force_generic >> 8) & 3;
+  g_tune.chunk_form = (force_generic >> 10) & 3;
   return SXMC_OK;
 }
 int sxmc_jit_compile_check(int nobs, int nslots, int smem_hist, int nops, unsigned codes, size_t* cubin_bytes_out) {

@@ -30,6 +30,7 @@ struct Tuning {
   int no_mono = 0;                 // never take the monotone endpoint path (tests)
   int no_jit = 0;                  // programs outside the build's table keep the run-time dispatching kernel
   int cta_split = 0;               // measurement knob of the fast binning kernel: 0 production (chunks dealt to a CTA's warps round robin; global-memory histograms: warps independent of each other), 1 one contiguous range per warp inside per-CTA segments (the round-1 form), 2 global histograms: one contiguous range per warp of the grid, 3 global histograms: per-CTA segments, round robin
+  int chunk_form = 0;              // fast binning pipeline: 0 automatic (four-row chunks for launches of >= 1 GiB into global-memory histograms of <= 65536 bins), 1 always two-row chunks, 2 four-row chunks wherever they fit (measurement knob)
   int no_pdl = 0;                  // steps without programmatic dependent launch (measurement knob)
   int no_group = 0;                // lookup: never group the events by bin (the multi-dataset form, on request)
   long long persistent_max_bytes = 64ll << 20;   // steps streaming less than this run persistent

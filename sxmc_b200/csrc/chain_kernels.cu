@@ -244,6 +244,7 @@ int launch_chain_persistent(const BinLaunch& L0, const PersistParams& Q, cudaStr
     return SXMC_ESTATE;
   }
   BinLaunch L = L0;
+  L.nwarps = FAST_WARPS;          // the persistent kernel runs full CTAs; its pipeline is re-planned below
   // its own shared-memory plan: the chain state and the signal tables take static space
   L.smem_hist = L0.smem_hist &&
                 bin_fast_plan(L.nslots, L.max_total_nbins, PK_STATIC_RESERVE, &L.rows_per_stage,

@@ -118,6 +118,7 @@ struct FastParams {
   unsigned short cta_first[FAST_MAX_JOBS + 1];
   int aligned;
   int cta_split;                // partition form, 0 in production (Tuning::cta_split, capi_internal.h)
+  int nwarps;                   // warps of the CTA the launch runs with (<= FAST_WARPS): tiles are dealt over these
   // profiling hook (sxmc_bin_debug_stamps): [grid][32] %globaltimer stamps, NULL in production.
   // Per CTA: 0 entry, 1 pipeline initialised, 2 first data arrived (warp 0), 3 segments done,
   // 4+3s+{0,1,2} of segment s < 4: parameters resolved / warp 0 out of its chunk loop / merged,

@@ -193,7 +193,7 @@ int jit_launch_bin(void* fn, unsigned grid, size_t smem_bytes, cudaStream_t stre
   CUlaunchConfig cfg;
   std::memset(&cfg, 0, sizeof cfg);
   cfg.gridDimX = grid; cfg.gridDimY = 1; cfg.gridDimZ = 1;
-  cfg.blockDimX = FAST_THREADS; cfg.blockDimY = 1; cfg.blockDimZ = 1;
+  cfg.blockDimX = (unsigned)P.nwarps * 32u; cfg.blockDimY = 1; cfg.blockDimZ = 1;
   cfg.sharedMemBytes = (unsigned)smem_bytes;
   cfg.hStream = (CUstream)stream;
   CUlaunchAttribute at[1];

@@ -28,6 +28,7 @@ struct BinLaunch {
   int prog_nops;                 // >= 0: compile-time systematic program, < 0: run-time dispatch
   unsigned prog_codes;
   int rows_per_stage, nstages;   // fast kernel pipeline shape
+  int nwarps;                    // fast kernel: warps per CTA (0 = FAST_WARPS)
   unsigned stage_off;            // byte offset of the stages in dynamic shared memory
   size_t smem_bytes;
   double lower[3], upper[3], scale[3];
@@ -47,6 +48,8 @@ struct EvalPdfJob {
 
 bool bin_fast_supported(int nobs, int nslots);
 bool bin_fast_has_program(int nobs, int nslots, int nops, unsigned codes);
+bool bin_fast_plan_big(int nslots, int hist_bins, size_t static_reserve, int* nwarps_out, int* R_out, int* S_out,
+                       unsigned* stage_off_out, size_t* smem_out);
 bool bin_fast_plan(int nslots, int hist_bins, size_t static_reserve, int* R_out, int* S_out,
                    unsigned* stage_off_out, size_t* smem_out);
 constexpr size_t BIN_STATIC_RESERVE = 4096;   // static shared memory of bin_fast_kernel

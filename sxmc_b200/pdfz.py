@@ -271,6 +271,6 @@ def eval_hists_host(hists, params, param_offset, want_pdf=True):
 
 
 def set_bin_tuning(smem_hist_max_bins=-1, blocks_per_sm=0, force_generic=False,
-                   force_dynamic=False, no_monotone=False, p2p_form=0, no_grouped_lookup=False, no_pdl=False, no_jit=False, cta_split=False):
-    sel = (1 if force_generic else 0) | (2 if force_dynamic else 0) | (4 if no_monotone else 0) | ((int(p2p_form) & 3) << 3) | (32 if no_grouped_lookup else 0) | (64 if no_pdl else 0) | (128 if no_jit else 0) | ((int(cta_split) & 3) << 8)
+                   force_dynamic=False, no_monotone=False, p2p_form=0, no_grouped_lookup=False, no_pdl=False, no_jit=False, cta_split=False, chunk_form=0):
+    sel = (1 if force_generic else 0) | (2 if force_dynamic else 0) | (4 if no_monotone else 0) | ((int(p2p_form) & 3) << 3) | (32 if no_grouped_lookup else 0) | (64 if no_pdl else 0) | (128 if no_jit else 0) | ((int(cta_split) & 3) << 8) | ((int(chunk_form) & 3) << 10)
     _check(lib().sxmc_set_bin_tuning(smem_hist_max_bins, blocks_per_sm, sel))

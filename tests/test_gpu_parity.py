@@ -144,7 +144,11 @@ VARIANTS = [("smem", dict(smem_hist_max_bins=56 * 1024)), ("global", dict(smem_h
             # the measurement forms of the fast kernel's partition (kernel_select bits 8-9)
             ("contiguous", dict(cta_split=1)), ("contiguous_global", dict(cta_split=1, smem_hist_max_bins=0)),
             ("warp_ranges_global", dict(cta_split=2, smem_hist_max_bins=0)),
-            ("segments_global", dict(cta_split=3, smem_hist_max_bins=0))]
+            ("segments_global", dict(cta_split=3, smem_hist_max_bins=0)),
+            # four-row chunks (what launches of >= 384 MB take) forced onto the small cases, and the
+            # two-row form
+            ("four_row_chunks", dict(chunk_form=2)), ("four_row_chunks_global", dict(chunk_form=2, smem_hist_max_bins=0)),
+            ("two_row_chunks", dict(chunk_form=1))]
 
 
 @pytest.mark.parametrize("variant", VARIANTS, ids=[v[0] for v in VARIANTS])
