@@ -373,8 +373,10 @@ def test_programs_outside_the_build_table_run_nvrtc_compiled_and_bit_exact(case)
     for sig in fit.signals:
         sig.systematics = list(range(len(fit.systematics)))
     out = {}
-    for jit in (True, False):
-        pdfz.set_bin_tuning(no_jit=not jit)
+    # (True, 2): the NVRTC-compiled kernel launched in the four-row-chunk form (12-warp CTAs for D's
+    # four columns) that gigabyte launches take
+    for jit, chunk_form in ((True, 0), (False, 0), (True, 2)):
+        pdfz.set_bin_tuning(no_jit=not jit, chunk_form=chunk_form)
         hists, chain = mcmc.build_fit(fit)
         chain.set_data(fit.data)
         assert chain.bin_kernel_kind() == (3 if jit else 1)
@@ -388,12 +390,13 @@ def test_programs_outside_the_build_table_run_nvrtc_compiled_and_bit_exact(case)
             assert abs(nll - want) <= NLL_RTOL * abs(want)
         chain.set_seed(7, 0)
         chain.set_mode(1)
-        out[jit] = chain(fit.data, 200, 0.1).get_samples()
+        out[(jit, chunk_form)] = chain(fit.data, 200, 0.1).get_samples()
         chain.close()
         for h in hists:
             h.close()
     pdfz.set_bin_tuning()
-    assert out[True].shape[0] > 0 and out[True].tobytes() == out[False].tobytes()
+    assert out[(True, 0)].shape[0] > 0
+    assert out[(True, 0)].tobytes() == out[(False, 0)].tobytes() == out[(True, 2)].tobytes()
 
 
 def test_pdfz_group_ragged_batch_matches_oracle():
