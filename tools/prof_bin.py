@@ -87,7 +87,8 @@ def main():
     print("  CTA entry                 %s" % q(r["entry"]))
     print("  pipeline initialised      %s" % q(r["init"]))
     print("  first data in smem        %s" % q(r["first_data"]))
-    print("  seg 0 parameters resolved %s" % q(r["seg0_params"]))
+    if (r["seg0_params"] > -1e6).all():      # (the per-warp pass of global-histogram launches has no segments: stamp unset)
+        print("  seg 0 parameters resolved %s" % q(r["seg0_params"]))
     print("  segments per CTA          %s" % q(r["nseg"]))
     two = r["nseg"] >= 2
     if two.any():
