@@ -18,6 +18,8 @@ OBJ = {"bin_kernels.o": [r"bin_fast_kernelILi3ELi4ELb1ELi3E", r"bin_fast_kernelI
                          r"bin_fast_kernelILi3ELi4ELb0ELi3E", r"bin_generic_kernelILb1E"],
        "nll_kernels.o": [r"lookup_nll_kernelILi128E", r"lookup_nll_kernelILi256E", r"pdf_table_kernel"],
        "p2p_kernels.o": [r"hist_allreduce_p2p_kernel"],
+       "nll_sharded_kernels.o": [r"lookup_nll_sharded_kernel"],
+       "noalloc_kernels.o": [r"nll_lut_noalloc_kernel"],
        "batch_mono_kernels.o": [r"chain_batch_mono_kernel"]}
 WATCH = ["UBLKCP", "UTMALDG", "SYNCS", "LDS.128", "LDS", "LDG", "LDC", "STS", "ATOMS", "ATOMG", "RED", "BAR",
          "DADD", "DMUL", "DFMA", "DSETP", "F2F", "F2I", "I2F", "MUFU", "FFMA", "HMMA", "UTCHMMA", "IMAD", "SEL",
