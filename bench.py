@@ -428,6 +428,8 @@ def measure_chain(fit, fit_local, hists, chain, args, rank, comm, flush, do_e2e=
     out["steps_run"] = 2 * Wm + 2 * R * K
     out["rows"] = int(ls.get_samples().shape[0])
     out["path"] = {1: "graph", 2: "persistent", 4: "monotone"}.get(chain.last_path(), chain.last_path())
+    out["bin_plan"] = dict(chain.bin_plan(), kernel={0: "interpreter", 1: "run-time dispatch", 2: "program of the build",
+                                                      3: "NVRTC-compiled program"}[chain.bin_kernel_kind()])
 
     # (3) e2e through the public call with host buffers
     if do_e2e:
@@ -679,6 +681,7 @@ def run_own_arm(args, rank, world, local):
         "roofline": roofline_object(fit, r, K, peak, peak_src, share,
                                     ncu_traffic(args.workload) if (args.scale == 1.0 and share == 1) else None),
         "kernels_ms_per_step": {"bin": r["bin_ms"] / K, "lookup_nll_metropolis": r["nll_ms"] / K},
+        "bin_plan": r["bin_plan"],
         "chain_back_to_back": {"value": nchains * K / (warm_ms * 1e-3), "unit": UNIT,
                                "ms_per_step": warm_ms / K, "path": r["path"],
                                "note": "production form: chain.advance(K), steps back to back (monotone / "

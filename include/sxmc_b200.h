@@ -244,6 +244,10 @@ int sxmc_chain_last_comm_ms(sxmc_chain* c, float* ms_out);
  * (multi-coefficient systematics, > 3 observables), 1 fast kernel with run-time dispatch of the systematics,
  * 2 fast kernel with a compile-time program of the build's table, 3 the same compiled for this fit by NVRTC */
 int sxmc_chain_bin_kernel_kind(sxmc_chain* c, int* kind_out);
+/* The pipeline shape the chain's binning launch was planned with (no reference counterpart; reported by
+ * bench.py and checked by the parity tests): warps per CTA, 512-byte rows per pipeline chunk, stages per
+ * warp, and whether the histograms are privatised in shared memory.  Zeros for the interpreter. */
+int sxmc_chain_bin_plan(sxmc_chain* c, int* nwarps_out, int* rows_per_chunk_out, int* nstages_out, int* smem_hist_out);
 /* device time (ms) of THIS chain's last evaluate-only pass (sxmc_chain_nll_at) while
  * sxmc_enable_kernel_timing is on; -1 before the first */
 int sxmc_chain_last_kernel_ms(sxmc_chain* c, float* bin_ms, float* nll_ms);

@@ -107,6 +107,7 @@ SYMBOLS = {
     "sxmc_chain_set_mode": (C.c_int, [c_vp, C.c_int]),
     "sxmc_chain_last_comm_ms": (C.c_int, [c_vp, c_fp]),
     "sxmc_chain_bin_kernel_kind": (C.c_int, [c_vp, C.POINTER(C.c_int)]),
+    "sxmc_chain_bin_plan": (C.c_int, [c_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "sxmc_chain_last_kernel_ms": (C.c_int, [c_vp, c_fp, c_fp]),
     "sxmc_chain_last_path": (C.c_int, [c_vp, C.POINTER(C.c_int)]),
     "sxmc_chain_phase_stamps": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_uint64)]),

@@ -855,6 +855,17 @@ int sxmc_chain_bin_kernel_kind(sxmc_chain* c, int* kind_out) {
   return SXMC_OK;
 }
 
+int sxmc_chain_bin_plan(sxmc_chain* c, int* nwarps_out, int* rows_per_chunk_out, int* nstages_out, int* smem_hist_out) {
+  if (!c) SXMC_INVAL("sxmc_chain_bin_plan: NULL chain");
+  if (!c->have_data) { set_error("sxmc_chain_bin_plan: no data set (the launch is planned with the data)"); return SXMC_ESTATE; }
+  const BinLaunch& L = c->batch[0].launch;
+  if (nwarps_out) *nwarps_out = L.fast ? (L.nwarps > 0 ? L.nwarps : FAST_WARPS) : 0;
+  if (rows_per_chunk_out) *rows_per_chunk_out = L.fast ? L.rows_per_stage : 0;
+  if (nstages_out) *nstages_out = L.fast ? L.nstages : 0;
+  if (smem_hist_out) *smem_hist_out = L.smem_hist ? 1 : 0;
+  return SXMC_OK;
+}
+
 int sxmc_chain_read_trace(sxmc_chain* c, double* nll_trace_out, double* proposed_out, unsigned nsteps) {
   if (!c->nll_trace_dev || nsteps > c->trace_steps) { set_error("trace was not enabled for that many steps"); return SXMC_ESTATE; }
   if (nll_trace_out) SXMC_CUDA(cudaMemcpy(nll_trace_out, c->nll_trace_dev, sizeof(double) * nsteps, cudaMemcpyDeviceToHost));

@@ -224,6 +224,13 @@ class MCMC:
         _check(lib().sxmc_chain_bin_kernel_kind(self._c, C.byref(v)))
         return v.value
 
+    def bin_plan(self):
+        """Pipeline shape of the binning launch: warps per CTA, rows per chunk, stages per warp, histogram in
+        shared memory (sxmc_chain_bin_plan)."""
+        v = [C.c_int(0) for _ in range(4)]
+        _check(lib().sxmc_chain_bin_plan(self._c, *[C.byref(x) for x in v]))
+        return {"warps": v[0].value, "rows_per_chunk": v[1].value, "stages": v[2].value, "smem_hist": bool(v[3].value)}
+
     def last_path(self):
         """1 graph / stream launches, 2 persistent kernel, 4 monotone edge-search kernel"""
         v = C.c_int(0)

@@ -582,6 +582,12 @@ def test_full_size_bit_exact_against_oracle_and_reference_digests(name):
     assert [float(v) for v in pars] == gold["pars"]
     hists, chain = mcmc.build_fit(fit)
     chain.set_data(fit.data)
+    # the launch shapes these sizes take (capi_hist.cu plan_launch): C privatised histograms and
+    # two-row chunks on 16 warps; D four-row chunks on 12 warps; the 200 000-bin D two-row chunks
+    want_plan = {"Cfull": dict(warps=16, rows_per_chunk=2, stages=4, smem_hist=True),
+                 "Dfull": dict(warps=12, rows_per_chunk=4, stages=2, smem_hist=False),
+                 "Dstress": dict(warps=16, rows_per_chunk=2, stages=3, smem_hist=False)}[name]
+    assert chain.bin_plan() == want_plan and chain.bin_kernel_kind() == 2
     nll, ev = chain.nll(pars)
     bins, norms, lut = chain.bins(), chain.norms(), chain.lut()
     # the compiled reference's output (tests/golden/make_ref_fixtures.py --full)
